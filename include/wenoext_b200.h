@@ -1,0 +1,233 @@
+/* wenoext_b200 — C ABI of the B200-native WENOEXT reconstruction hot path.
+ *
+ * Drop-in boundary for the per-timestep work of
+ *   WENOUpwindFit<Type>::correction()    libWENOEXT/WENOUpwindFit/WENOUpwindFit.C:212-290
+ *   WENOUpwindFit01<Type>::correction()  libWENOEXT/WENOUpwindFit01/WENOUpwindFit01.C:215-292
+ * and everything they call per step (WENOCoeff::getWENOPol/calcCoeff/calcWeight/
+ * collectData, sumFlux, coupledRiemannSolver, swapData, calcLimiter).
+ * All citations are relative to the reference tree (WENO-OF/WENOEXT @ 78907ff).
+ *
+ * Plain pointers and sizes only. Every function returns 0 on success and a
+ * non-zero code otherwise; wenoext_last_error() gives the message. There is no
+ * CPU fallback: calls that need the GPU fail when none is present.
+ */
+#ifndef WENOEXT_B200_H
+#define WENOEXT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WENOEXT_OK 0
+#define WENOEXT_ERR_INVALID 1   /* bad argument / inconsistent plan */
+#define WENOEXT_ERR_CUDA 2      /* CUDA runtime error or no device */
+#define WENOEXT_ERR_NCCL 3      /* NCCL unavailable or failed */
+#define WENOEXT_ERR_SETUP 4     /* host setup (WENOBase stand-in) failed */
+
+/* WENOBase::Cell (WENOBase.H:62-67) */
+#define WENOEXT_CELL_LOCAL (-1)
+#define WENOEXT_CELL_DELETED (-4)
+#define WENOEXT_CELL_EMPTY (-10)
+
+/* fvPatch kinds the path distinguishes (WENOUpwindFit.C:433, :478, :493) */
+#define WENOEXT_PATCH_GENERIC 0   /* not coupled: zero correction */
+#define WENOEXT_PATCH_PROCESSOR 1 /* processorFvPatch, nbr = neighbour rank */
+#define WENOEXT_PATCH_CYCLIC 2    /* cyclicFvPatch, nbr = neighbour patch index */
+#define WENOEXT_PATCH_EMPTY 3     /* emptyFvPatch */
+
+/* scheme selector: TypeName("WENOUpwindFit") WENOUpwindFit.H:156,
+ *                  TypeName("WENOUpwindFit01") WENOUpwindFit01.H:149 */
+#define WENOEXT_SCHEME_UPWINDFIT 0
+#define WENOEXT_SCHEME_UPWINDFIT01 1
+
+#define WENOEXT_MEM_HOST 0
+#define WENOEXT_MEM_DEVICE 1
+
+typedef struct wenoext_patch {
+    int32_t type;  /* WENOEXT_PATCH_* */
+    int32_t start; /* patch.start(): first face index */
+    int32_t size;
+    int32_t nbr;   /* neighbour rank (processor) / neighbour patch (cyclic) / -1 */
+} wenoext_patch;
+
+/* The immutable per-(mesh, order) data WENOBase owns, flattened to CSR.
+ * Each member names the WENOBase accessor it replaces (WENOBase.H:319-397).
+ * All pointers are HOST pointers; wenoext_plan_create copies what it needs. */
+typedef struct wenoext_plan_desc {
+    int32_t polOrder;       /* WENOUpwindFit.H:207 */
+    int32_t nDvt;           /* degreesOfFreedom(), WENOBase.C:1130-1140 */
+    int32_t dim[3];         /* dimList()[cell] (same for all cells, WENOBase.C:1147-1154) */
+    int32_t nCells, nFaces, nInternalFaces;
+    const int32_t* owner;         /* mesh.owner()      [nFaces] */
+    const int32_t* neighbour;     /* mesh.neighbour()  [nInternalFaces] */
+    const int32_t* cellFaceStart; /* mesh.cells() CSR  [nCells+1] */
+    const int32_t* cellFaces;
+    int32_t nPatches;
+    const wenoext_patch* patches; /* mesh.boundary() */
+
+    /* stencilsID()[cell][stencil][j] and cellToProcMap()[cell][stencil][j]:
+     * cellStencilStart[cell] .. cellStencilStart[cell+1] are the cell's stencil
+     * slots IN LIST ORDER (deleted ones included: one entry, value -4; an empty
+     * cell has -10 in entry 0 of stencil 0, WENOCoeff.C:333).
+     * Entry 0 of a live stencil is the cell itself (WENOBase.C:976-979). */
+    int64_t nStencils;
+    const int64_t* cellStencilStart;  /* [nCells+1] */
+    const int64_t* stencilEntryStart; /* [nStencils+1] */
+    const int32_t* stencilsID;
+    const int32_t* cellToProcMap; /* may be NULL: every entry local */
+
+    /* LSmatrix()[cell][stencil](): nDvt x (stencil size-1), row-major, UNPADDED.
+     * stencilMatrix[s] indexes the de-duplicated pool (matrixDB.H:136-139);
+     * -1 for deleted stencils. */
+    const int32_t* stencilMatrix; /* [nStencils] */
+    int32_t nUniqueMatrices;
+    const int64_t* matrixStart; /* [nUniqueMatrices+1] offsets into matrixData */
+    const int32_t* matrixCols;  /* [nUniqueMatrices] */
+    const double* matrixData;
+
+    const double* B;           /* B()[cell], row-major nDvt x nDvt   [nCells] */
+    const double* intBasTrans; /* intBasTrans()[face][0|1](n,m,l), cubes of
+                                  (polOrder+1)^3, List3D.H:238        [nFaces][2] */
+    const double* refFacAr;    /* refFacAr()[face]                    [nFaces] */
+
+    /* halo lists, indexed by processor id, length nProcs (WENOBase.H:122-138) */
+    int32_t nProcs, myProc;
+    const int32_t* sendProcList;    /* -1: nothing to send */
+    const int32_t* receiveProcList; /* -1: nothing to receive */
+    const int32_t* receiveHaloSize;
+    const int64_t* sendHaloStart;   /* CSR over sendHaloCellIDList() [nProcs+1] */
+    const int32_t* sendHaloCellID;
+
+    /* optional: for each boundary face (index face - nInternalFaces) of a
+     * coupled patch, where the cell on the other side lives: a local cell id
+     * (cyclic) or nCells + haloOffset(proc) + haloId (processor); -1 otherwise.
+     * Lets the bounded limiter form patchNeighbourField() (WENOUpwindFit.C:130)
+     * from the halo buffer. NULL: pass patchNbrField to wenoext_correction. */
+    const int32_t* patchNbrCell;
+} wenoext_plan_desc;
+
+typedef struct wenoext_plan wenoext_plan;
+
+typedef struct wenoext_plan_info {
+    int64_t nCells, nFaces, nInternalFaces, nCoupledFaces;
+    int64_t nLiveStencils, nHaloCells;
+    int64_t nInteriorCells;     /* cells with no halo entry in any stencil */
+    int64_t recordBytes;        /* device bytes of the per-cell records */
+    int64_t maxRecordBytes;
+    /* SURVEY.md 8(d) algorithmic bytes of one correction() call, split so the
+     * caller can add the per-component terms:
+     *   bytes(C) = algBytesFixed + C * algBytesPerComp                       */
+    int64_t algBytesFixed;
+    int64_t algBytesPerComp;
+    int64_t algFlopsPerComp;
+} wenoext_plan_info;
+
+const char* wenoext_last_error(void);
+/* number of CUDA devices visible; 0 without a GPU (never fails) */
+int wenoext_device_count(void);
+
+/* Flatten + upload (once). Replaces the WENOBase::instance() lookup done in
+ * WENOCoeff's constructor (WENOCoeff.C:53-99, WENOBase.H:281-294). */
+int wenoext_plan_create(const wenoext_plan_desc* desc, int device, wenoext_plan** out);
+int wenoext_plan_destroy(wenoext_plan* plan);
+int wenoext_plan_get_info(const wenoext_plan* plan, wenoext_plan_info* info);
+
+/* WENODict run-time factors p, dm, epsilon (WENOCoeff.C:87-89; defaults 4, 1000,
+ * 1e-40). p is truncated to unsigned as WENOCoeff.H:149 does. */
+int wenoext_set_params(wenoext_plan* plan, double p, double dm, double epsilon);
+/* 1 (default): reproduce WENOUpwindFit01.C:125 (intBasTrans()[cellI][1]); 0: use
+ * the face index. */
+int wenoext_set_fit01_bug_compat(wenoext_plan* plan, int on);
+
+/* NCCL plumbing for the two exchanges (collectData, WENOCoeff.C:224-296 and
+ * swapData, WENOUpwindFit.C:326-385). libnccl is dlopen'ed on first use. */
+int wenoext_nccl_unique_id(char id[128]);
+int wenoext_attach_nccl(wenoext_plan* plan, const char id[128], int rank, int nRanks);
+
+/* correction(vf): one call = one reference correction() (halo exchange, fused
+ * coefficient/weight/face kernel, coupled patches, limiter).
+ *   vf            [nCells][nComp]            vf.internalField(), AoS
+ *   faceFlux      [nFaces]                   faceFlux_ (internal faces, then patches)
+ *   patchNbrField [nFaces-nInternalFaces][nComp] patchNeighbourField() values on
+ *                 coupled patch faces; may be NULL if desc.patchNbrCell was given
+ *                 or bounded == 0
+ *   corr          [nFaces][nComp] out: tsfP incl. boundaryField (zero on
+ *                 non-coupled patches)
+ * memKind: WENOEXT_MEM_HOST (pageable or pinned; staged inside) or _DEVICE.
+ * stream: cudaStream_t (NULL = default stream). Host buffers: returns after the
+ * result is in `corr`. Device buffers: stream-ordered, returns immediately. */
+int wenoext_correction(wenoext_plan* plan, int scheme, int bounded, int nComp,
+                       const double* vf, const double* faceFlux, const double* patchNbrField,
+                       double* corr, int memKind, void* stream);
+
+/* Same, plus the interpolated face value psi_upwind + correction on internal
+ * faces (what surfaceInterpolationScheme::interpolate forms from weights() and
+ * correction()); faceValue [nInternalFaces][nComp], device or host like corr. */
+int wenoext_interpolate(wenoext_plan* plan, int scheme, int bounded, int nComp,
+                        const double* vf, const double* faceFlux, const double* patchNbrField,
+                        double* corr, double* faceValue, int memKind, void* stream);
+
+/* In-process ranks (several plans in one process, on one or more GPUs; used by
+ * the single-GPU tests of the multi-rank path): plans[r] must have myProc == r.
+ * Exchanges become device-to-device copies; drive them with the split-phase
+ * calls: _begin on every rank, then _exchange on every rank, then _end on every
+ * rank (device pointers, nComp <= 3). With NCCL attached, wenoext_correction
+ * runs the same three phases back to back. */
+int wenoext_attach_local(wenoext_plan** plans, int nRanks);
+int wenoext_correction_begin(wenoext_plan* plan, int scheme, int bounded, int nComp,
+                             const double* vf, const double* faceFlux,
+                             const double* patchNbrField, double* corr, void* stream);
+int wenoext_correction_exchange(wenoext_plan* plan);
+int wenoext_correction_end(wenoext_plan* plan);
+
+/* Number of this library's kernel launches issued by the last correction call. */
+int wenoext_last_launch_count(const wenoext_plan* plan);
+/* CUDA-event time (ms) of the fused cell kernel(s) in the last call made with
+ * timing enabled; <0 if timing is off. */
+int wenoext_enable_kernel_timing(wenoext_plan* plan, int on);
+double wenoext_last_kernel_ms(const wenoext_plan* plan);
+
+/* ---------------------------------------------------------------------------
+ * Host setup stand-in (WENOBase::WENOBase, WENOBase.C:674-938) on generated box
+ * meshes, because OpenFOAM is not available to run the reference's own setup.
+ * Produces a wenoext_plan_desc. Runs once, on the host.
+ * ------------------------------------------------------------------------- */
+typedef struct wenoext_box_spec {
+    int32_t n[3];
+    double lo[3], hi[3];
+    int32_t sideType[6]; /* xlo,xhi,ylo,yhi,zlo,zhi: WENOEXT_PATCH_GENERIC/EMPTY/CYCLIC */
+    int32_t tetSplit;    /* 0 hexes, 6 = every hex split into 6 tets */
+    int32_t nProc[3];    /* `decomposePar simple` block decomposition */
+} wenoext_box_spec;
+
+typedef struct wenoext_setup_params {
+    int32_t polOrder;
+    double extendRatio;      /* WENODict, default 2.5 */
+    int32_t bestConditioned; /* default 0 */
+    double maxCondition;     /* default 1e-5 */
+    int32_t checkCondition;  /* default 1 */
+    int32_t nThreads;        /* 0 = all */
+    int32_t useClassCache;   /* 1: translation-invariant cell classes computed once */
+} wenoext_setup_params;
+
+typedef struct wenoext_setup wenoext_setup;
+
+int wenoext_setup_box(const wenoext_box_spec* box, const wenoext_setup_params* prm,
+                      int32_t myProc, wenoext_setup** out);
+int wenoext_setup_destroy(wenoext_setup* s);
+/* Pointers in `desc` stay valid until wenoext_setup_destroy. */
+int wenoext_setup_desc(wenoext_setup* s, wenoext_plan_desc* desc);
+/* distributeStencils (WENOBase.C:334-407): what this rank requests from `proc`
+ * (processor-local cell ids there), and the owner-side setter. */
+int wenoext_setup_halo_request(wenoext_setup* s, int32_t proc, const int32_t** ids, int64_t* n);
+int wenoext_setup_set_send_halo(wenoext_setup* s, int32_t proc, const int32_t* ids, int64_t n);
+/* mesh geometry for building synthetic fields: C() [nCells][3], Sf() [nFaces][3] */
+int wenoext_setup_geometry(wenoext_setup* s, const double** cellCentres,
+                           const double** faceAreaVec);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WENOEXT_B200_H */

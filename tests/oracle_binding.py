@@ -1,0 +1,135 @@
+"""ctypes binding of the CPU oracle (oracle/). Test infrastructure: only tests/,
+__graft_entry__.smoke() and bench.py's CPU legs may import this."""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "libweno_oracle.so")
+BLAZE_SO = os.path.join(ROOT, "oracle", "_ref", "libweno_oracle_blaze.so")
+
+vp = C.c_void_p
+_dp = lambda a: a.ctypes.data_as(vp) if a is not None else None  # noqa: E731
+
+
+def _f64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Oracle:
+    """variant: 'c' (plain C, double), 'ld' (long double accumulation), 'blaze'
+    (reference's vendored Blaze for the three matrix products)."""
+
+    def __init__(self, variant="c"):
+        self.variant = variant
+        self.L = C.CDLL(ORACLE_SO)
+        pre = "weno_oracle_ld" if variant == "ld" else "weno_oracle"
+        self._pol = getattr(self.L, pre + "_getWENOPol")
+        self._A = getattr(self.L, pre + "_phaseA")
+        self._B = getattr(self.L, pre + "_phaseB")
+        self._pol.argtypes = [vp, C.c_int, C.c_double, C.c_double, C.c_double, vp, vp, vp]
+        self._A.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+        self._B.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
+        self.BL = None
+        if variant == "blaze":
+            self.BL = C.CDLL(BLAZE_SO)
+            self.BL.weno_oracle_blaze_create.restype = vp
+            self.BL.weno_oracle_blaze_create.argtypes = [vp]
+            self.BL.weno_oracle_blaze_destroy.argtypes = [vp]
+            self.BL.weno_oracle_blaze_getWENOPol.argtypes = [vp, C.c_int, C.c_double, C.c_double,
+                                                             C.c_double, vp, vp, vp]
+            self.BL.weno_oracle_blaze_getWENOPol_range.argtypes = [
+                vp, C.c_int, C.c_double, C.c_double, C.c_double, vp, vp, vp, C.c_int, C.c_int]
+        self._handles = {}
+
+    def _blaze_handle(self, case):
+        k = id(case.desc)
+        if k not in self._handles:
+            self._handles[k] = (self.BL.weno_oracle_blaze_create(C.addressof(case.desc)), case)
+        return self._handles[k][0]
+
+    def getWENOPol(self, case, vf, halo=None, p=4.0, dm=1000.0, eps=1e-40):
+        vf = _f64(vf)
+        nComp = 1 if vf.ndim == 1 else vf.shape[1]
+        halo = _f64(halo)
+        cw = np.zeros((case.nCells, case.nDvt, nComp))
+        if self.variant == "blaze":
+            rc = self.BL.weno_oracle_blaze_getWENOPol(self._blaze_handle(case), nComp, p, dm, eps,
+                                                      _dp(vf), _dp(halo), _dp(cw))
+        else:
+            rc = self._pol(C.addressof(case.desc), nComp, p, dm, eps, _dp(vf), _dp(halo), _dp(cw))
+        assert rc == 0
+        return cw
+
+    def phaseA(self, case, faceFlux, cw):
+        nComp = cw.shape[2]
+        corr = np.zeros((case.nFaces, nComp))
+        ud = np.zeros((max(case.nFaces - case.nInternalFaces, 1), nComp))
+        rc = self._A(C.addressof(case.desc), nComp, _dp(_f64(faceFlux)), _dp(cw), _dp(corr), _dp(ud))
+        assert rc == 0
+        return corr, ud
+
+    def phaseB(self, case, scheme, bounded, vf, faceFlux, cw, corr, pnf=None, recv=None,
+               bugCompat=1):
+        nComp = cw.shape[2]
+        vf = _f64(vf)
+        rc = self._B(C.addressof(case.desc), scheme, int(bounded), nComp, bugCompat, _dp(vf),
+                     _dp(_f64(faceFlux)), _dp(cw), _dp(_f64(pnf)), _dp(_f64(recv)), _dp(corr))
+        assert rc == 0
+        return corr
+
+    def correction(self, case, scheme, bounded, vf, faceFlux, p=4.0, dm=1000.0, eps=1e-40,
+                   bugCompat=1):
+        """Serial correction(); returns [nFaces] or [nFaces][nComp] like vf."""
+        vf = _f64(vf)
+        cw = self.getWENOPol(case, vf, None, p, dm, eps)
+        corr, ud = self.phaseA(case, faceFlux, cw)
+        self.phaseB(case, scheme, bounded, vf, faceFlux, cw, corr, None, ud, bugCompat)
+        return corr[:, 0] if vf.ndim == 1 else corr
+
+
+def correction_multirank(orc, cases, scheme, bounded, vfs, fluxes, p=4.0, dm=1000.0, eps=1e-40,
+                         bugCompat=1):
+    """In-process emulation of an MPI run of the reference: collectData
+    (WENOCoeff.C:224-296), per-rank getWENOPol, swapData (WENOUpwindFit.C:326-385),
+    per-rank second half + limiter. `cases` already had exchange_halo_lists()."""
+    R = len(cases)
+    vfs = [_f64(v).reshape(c.nCells, -1) for v, c in zip(vfs, cases)]
+    nComp = vfs[0].shape[1]
+    halos = []
+    for r, c in enumerate(cases):
+        segs = []
+        for q in range(R):
+            n = c.desc.receiveHaloSize[q]
+            if n:
+                send_ids = _send_list(cases[q], r)
+                assert len(send_ids) == n
+                segs.append(vfs[q][send_ids])
+        halos.append(np.concatenate(segs) if segs else np.zeros((0, nComp)))
+    cws, corrs, uds = [], [], []
+    for r, c in enumerate(cases):
+        cw = orc.getWENOPol(c, vfs[r], halos[r], p, dm, eps)
+        corr, ud = orc.phaseA(c, fluxes[r], cw)
+        cws.append(cw), corrs.append(corr), uds.append(ud)
+    outs = []
+    for r, c in enumerate(cases):
+        nI = c.nInternalFaces
+        recv = np.zeros_like(uds[r])
+        pnf = np.zeros_like(uds[r])
+        for (ptype, start, size, nbr) in c.patches:
+            if ptype != 1 or size == 0:
+                continue
+            q = cases[nbr]
+            (qs,) = [ps for (pt, ps, pz, pn) in q.patches if pt == 1 and pn == r]
+            recv[start - nI:start - nI + size] = uds[nbr][qs - q.nInternalFaces:qs - q.nInternalFaces + size]
+            pnf[start - nI:start - nI + size] = vfs[nbr][q.owner[qs:qs + size]]
+        outs.append(orc.phaseB(c, scheme, bounded, vfs[r], fluxes[r], cws[r], corrs[r], pnf, recv,
+                               bugCompat))
+    return outs
+
+
+def _send_list(case, to):
+    d = case.desc
+    a, b = d.sendHaloStart[to], d.sendHaloStart[to + 1]
+    return np.array([d.sendHaloCellID[i] for i in range(a, b)], dtype=np.int64)

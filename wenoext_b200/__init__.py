@@ -1,0 +1,345 @@
+"""wenoext_b200 — B200-native WENOEXT reconstruction hot path (host-side mirror).
+
+Python mirror of the reference's plugin interface for this one path, on top of
+the C ABI in include/wenoext_b200.h:
+
+  reference (OpenFOAM plugin)                         here
+  ------------------------------------------------    ---------------------------
+  WENOBase::instance(mesh, polOrder)                  WENOBase.instance(case)
+    libWENOEXT/WENOBase/WENOBase.H:281-294
+  WENOUpwindFit<Type>(mesh, faceFlux, Istream)        WENOUpwindFit(case, faceFlux, "2 1")
+    libWENOEXT/WENOUpwindFit/WENOUpwindFit.H:198-211
+  weights(vf) / corrected() / correction(vf)          same names, same meaning
+    WENOUpwindFit.H:223-242
+  WENOUpwindFit01<Type>(mesh, faceFlux, Istream)      WENOUpwindFit01(case, faceFlux, "3")
+    libWENOEXT/WENOUpwindFit01/WENOUpwindFit01.H:183-201
+  system/WENODict: p, dm, epsilon                     case.WENODict
+    libWENOEXT/WENOBase/WENOCoeff.C:87-89
+
+All arithmetic happens in libwenoext_b200.so (hand-written sm_100a CUDA). Nothing
+here computes a correction on the CPU and nothing imports oracle/.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import (MEM_DEVICE, MEM_HOST, PATCH_CYCLIC, PATCH_EMPTY, PATCH_GENERIC,
+                    PATCH_PROCESSOR, SCHEME_UPWINDFIT, SCHEME_UPWINDFIT01, WenoextError, check,
+                    lib)
+
+__all__ = ["BoxCase", "WENOBase", "Plan", "WENOUpwindFit", "WENOUpwindFit01", "WenoextError",
+           "exchange_halo_lists", "PATCH_GENERIC", "PATCH_PROCESSOR", "PATCH_CYCLIC", "PATCH_EMPTY"]
+
+
+def _np_view(ptr, shape, dtype):
+    n = int(np.prod(shape))
+    if n == 0 or not ptr:
+        return np.zeros(shape, dtype=dtype)
+    ctype = {np.int32: C.c_int32, np.int64: C.c_int64, np.float64: C.c_double}[dtype]
+    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(n,))
+    return arr.reshape(shape)
+
+
+class BoxCase:
+    """A generated box case: mesh + the WENOBase preprocessing output.
+
+    Stand-in for an OpenFOAM case directory (blockMesh box + constant/WENOBase<N>),
+    because OpenFOAM is not available here. The preprocessing is the host C++
+    restatement of WENOBase::WENOBase (wenoext_b200/csrc/setup/), run once.
+    """
+
+    def __init__(self, n, order, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0),
+                 sides=(0, 0, 0, 0, 0, 0), nProc=(1, 1, 1), myProc=0, tetSplit=0,
+                 extendRatio=2.5, bestConditioned=False, maxCondition=1e-5, checkCondition=True,
+                 nThreads=0, useClassCache=True, WENODict=None):
+        L = lib()
+        box = _capi.BoxSpec()
+        box.n[:] = list(n)
+        box.lo[:] = list(lo)
+        box.hi[:] = list(hi)
+        box.sideType[:] = list(sides)
+        box.tetSplit = tetSplit
+        box.nProc[:] = list(nProc)
+        prm = _capi.SetupParams(order, extendRatio, int(bestConditioned), maxCondition,
+                                int(checkCondition), nThreads, int(useClassCache))
+        h = C.c_void_p()
+        check(L.wenoext_setup_box(C.byref(box), C.byref(prm), myProc, C.byref(h)))
+        self._h = h
+        self.order = order
+        self.nProcs = int(np.prod(nProc))
+        self.myProc = myProc
+        # WENODict run-time factors and their defaults (WENOCoeff.C:41-48, :87-89)
+        self.WENODict = {"p": 4.0, "dm": 1000.0, "epsilon": 1e-40}
+        if WENODict:
+            self.WENODict.update(WENODict)
+        self._refresh()
+
+    def _refresh(self):
+        L = lib()
+        self.desc = _capi.PlanDesc()
+        check(L.wenoext_setup_desc(self._h, C.byref(self.desc)))
+        d = self.desc
+        self.nCells, self.nFaces, self.nInternalFaces = d.nCells, d.nFaces, d.nInternalFaces
+        self.nDvt = d.nDvt
+        self.owner = _np_view(d.owner, (d.nFaces,), np.int32)
+        self.neighbour = _np_view(d.neighbour, (d.nInternalFaces,), np.int32)
+        self.patches = [(d.patches[i].type, d.patches[i].start, d.patches[i].size, d.patches[i].nbr)
+                        for i in range(d.nPatches)]
+        css = _np_view(d.cellStencilStart, (d.nCells + 1,), np.int64)
+        ses = _np_view(d.stencilEntryStart, (d.nStencils + 1,), np.int64)
+        nEnt = int(ses[-1])
+        self.stencilsID = _np_view(d.stencilsID, (nEnt,), np.int32)
+        # Cell::empty cells get zero correction (WENOCoeff.C:333)
+        self.emptyCells = self.stencilsID[ses[css[:-1]]] == _capi.CELL_EMPTY
+        cc, sf = _capi.f64p(), _capi.f64p()
+        check(L.wenoext_setup_geometry(self._h, C.byref(cc), C.byref(sf)))
+        self.C = _np_view(cc, (d.nCells, 3), np.float64)       # mesh.C()
+        self.Sf = _np_view(sf, (d.nFaces, 3), np.float64)      # mesh.Sf()
+
+    def halo_request(self, proc):
+        ids, n = _capi.i32p(), C.c_int64()
+        check(lib().wenoext_setup_halo_request(self._h, proc, C.byref(ids), C.byref(n)))
+        return _np_view(ids, (n.value,), np.int32).copy()
+
+    def set_send_halo(self, proc, ids):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        check(lib().wenoext_setup_set_send_halo(self._h, proc, ids.ctypes.data_as(_capi.i32p),
+                                                ids.size))
+        self._refresh()
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().wenoext_setup_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def exchange_halo_lists(cases):
+    """distributeStencils (WENOBase.C:334-407) for in-process ranks: hand every
+    rank's request list to the owner rank."""
+    for r, cr in enumerate(cases):
+        for p, cp in enumerate(cases):
+            if p != r:
+                cp.set_send_halo(r, cr.halo_request(p))
+
+
+def exchange_halo_lists_distributed(case):
+    """Same, one process per rank, lists shipped with torch.distributed."""
+    import torch.distributed as dist
+
+    req = [case.halo_request(p).tolist() for p in range(case.nProcs)]
+    allreq = [None] * case.nProcs
+    dist.all_gather_object(allreq, req)
+    for p in range(case.nProcs):
+        if p != case.myProc:
+            case.set_send_halo(p, np.asarray(allreq[p][case.myProc], dtype=np.int32))
+
+
+class Plan:
+    """Device plan (wenoext_plan): owns all device memory of one (mesh, order)."""
+
+    def __init__(self, desc, device=0):
+        self._h = C.c_void_p()
+        self.device = device
+        check(lib().wenoext_plan_create(C.byref(desc), device, C.byref(self._h)))
+        self.info = _capi.PlanInfo()
+        check(lib().wenoext_plan_get_info(self._h, C.byref(self.info)))
+        self.nCells, self.nFaces = int(self.info.nCells), int(self.info.nFaces)
+        self.nInternalFaces = int(self.info.nInternalFaces)
+
+    def set_params(self, p=4.0, dm=1000.0, epsilon=1e-40):
+        check(lib().wenoext_set_params(self._h, p, dm, epsilon))
+
+    def set_fit01_bug_compat(self, on):
+        check(lib().wenoext_set_fit01_bug_compat(self._h, int(on)))
+
+    def attach_nccl(self, uid, rank, nRanks):
+        check(lib().wenoext_attach_nccl(self._h, uid, rank, nRanks))
+
+    def alg_bytes(self, nComp):
+        return int(self.info.algBytesFixed + nComp * self.info.algBytesPerComp)
+
+    def enable_kernel_timing(self, on=True):
+        check(lib().wenoext_enable_kernel_timing(self._h, int(on)))
+
+    def last_kernel_ms(self):
+        return lib().wenoext_last_kernel_ms(self._h)
+
+    def last_launch_count(self):
+        return lib().wenoext_last_launch_count(self._h)
+
+    @staticmethod
+    def _ptr(x):
+        """(pointer, memKind, keepalive) of a numpy array or a torch tensor."""
+        if x is None:
+            return None, None, None
+        if isinstance(x, np.ndarray):
+            a = np.ascontiguousarray(x, dtype=np.float64)
+            return a.ctypes.data, MEM_HOST, a
+        # torch tensor
+        t = x.contiguous()
+        if t.dtype.is_floating_point and t.element_size() != 8:
+            raise WenoextError("fields must be float64 (the path computes in fp64)")
+        return t.data_ptr(), (MEM_DEVICE if t.is_cuda else MEM_HOST), t
+
+    def correction(self, scheme, bounded, vf, faceFlux, patchNbrField=None, out=None,
+                   faceValue=None, stream=None):
+        """wenoext_correction / wenoext_interpolate through the C ABI.
+
+        numpy arrays are HOST buffers (copies happen inside the call); torch CUDA
+        tensors are used in place on `stream` (default: torch's current stream)."""
+        nComp = 1 if vf.ndim == 1 else int(vf.shape[1])
+        pv, kind, kv = self._ptr(vf)
+        pf, kindf, kf = self._ptr(faceFlux)
+        pn, _, kn = self._ptr(patchNbrField)
+        if kind != kindf:
+            raise WenoextError("vf and faceFlux must live in the same memory space")
+        shape = (self.nFaces,) if vf.ndim == 1 else (self.nFaces, nComp)
+        if out is None:
+            if kind == MEM_HOST and isinstance(vf, np.ndarray):
+                out = np.empty(shape, dtype=np.float64)
+            else:
+                import torch
+                out = torch.empty(shape, dtype=torch.float64, device=vf.device)
+        po, kindo, ko = self._ptr(out)
+        if kindo != kind:
+            raise WenoextError("out must live in the same memory space as vf")
+        st = 0
+        if kind == MEM_DEVICE:
+            import torch
+            st = (stream if stream is not None else torch.cuda.current_stream(vf.device)).cuda_stream
+        if faceValue is not None:
+            pfv, _, kfv = self._ptr(faceValue)
+            check(lib().wenoext_interpolate(self._h, scheme, int(bounded), nComp, pv, pf, pn, po,
+                                            pfv, kind, st))
+        else:
+            check(lib().wenoext_correction(self._h, scheme, int(bounded), nComp, pv, pf, pn, po,
+                                           kind, st))
+        return out
+
+    def destroy(self):
+        if self._h:
+            lib().wenoext_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+class WENOBase:
+    """Process-wide registry of device plans, the counterpart of the reference's
+    singleton `WENOBase::instance(mesh, polOrder)` (WENOBase.H:281-294). OpenFOAM
+    constructs a new scheme object on every fvm::div call, so the expensive state
+    must not live in the scheme. Keyed by (case, order, device)
+    instead of "first caller wins"."""
+
+    _plans = {}
+
+    @classmethod
+    def instance(cls, case, device=0):
+        key = (id(case), case.order, device)
+        if key not in cls._plans:
+            plan = Plan(case.desc, device)
+            cls._plans[key] = (plan, case)
+        return cls._plans[key][0]
+
+    @classmethod
+    def clear(cls):
+        for plan, _ in cls._plans.values():
+            plan.destroy()
+        cls._plans.clear()
+
+
+def _tokens(spec):
+    if isinstance(spec, str):
+        return spec.split()
+    if isinstance(spec, (list, tuple)):
+        return [str(s) for s in spec]
+    return [str(spec)]
+
+
+def _read_bool(tok):
+    # OpenFOAM readBool accepts 0/1, true/false, on/off, yes/no
+    t = tok.lower()
+    if t in ("1", "true", "on", "yes", "y", "t"):
+        return True
+    if t in ("0", "false", "off", "no", "n", "f", "none"):
+        return False
+    raise WenoextError(f"bad bool token '{tok}'")
+
+
+class WENOUpwindFit:
+    """`Gauss WENOUpwindFit <order> <bounded>` (README.md:93-99 of the reference).
+
+    Mirrors WENOUpwindFit<Type> (WENOUpwindFit.H:57-243): constructed from the mesh,
+    the face flux and the scheme tokens; weights() is pure upwind, corrected() is
+    true, correction(vf) is the explicit high-order correction per face."""
+
+    typeName = "WENOUpwindFit"
+    _scheme = SCHEME_UPWINDFIT
+
+    def __init__(self, case, faceFlux, spec, device=0):
+        tok = _tokens(spec)
+        self.polOrder_ = int(float(tok[0]))            # readScalar(is), WENOUpwindFit.H:207
+        self.limFac_ = self._read_limiter(tok)         # readBool(is),   WENOUpwindFit.H:208
+        if self.polOrder_ != case.order:
+            raise WenoextError(f"case was preprocessed for order {case.order}, "
+                               f"scheme asks for {self.polOrder_}")
+        self.mesh_ = case
+        self.faceFlux_ = faceFlux
+        self.plan_ = WENOBase.instance(case, device)
+        wd = case.WENODict
+        self.plan_.set_params(wd["p"], wd["dm"], wd["epsilon"])
+
+    @staticmethod
+    def _read_limiter(tok):
+        if len(tok) < 2:
+            raise WenoextError("WENOUpwindFit needs '<order> <bounded>'")
+        return _read_bool(tok[1])
+
+    def weights(self, vf=None):
+        """pos(faceFlux_) (WENOUpwindFit.H:223-229); pos(0) == 1 in OpenFOAM."""
+        f = self.faceFlux_
+        if isinstance(f, np.ndarray):
+            return (f >= 0).astype(np.float64)
+        return (f >= 0).to(f.dtype)
+
+    def corrected(self):
+        return True
+
+    def correction(self, vf, patchNbrField=None, out=None):
+        return self.plan_.correction(self._scheme, self.limFac_, vf, self.faceFlux_,
+                                     patchNbrField, out=out)
+
+    def interpolate(self, vf, patchNbrField=None):
+        """Internal-face values weights*vf_P + (1-weights)*vf_N + correction, formed
+        on the device (what surfaceInterpolationScheme::interpolate returns)."""
+        nComp = 1 if vf.ndim == 1 else int(vf.shape[1])
+        nI = self.mesh_.nInternalFaces
+        shape = (nI,) if vf.ndim == 1 else (nI, nComp)
+        if isinstance(vf, np.ndarray):
+            fv = np.empty(shape, dtype=np.float64)
+        else:
+            import torch
+            fv = torch.empty(shape, dtype=torch.float64, device=vf.device)
+        corr = self.plan_.correction(self._scheme, self.limFac_, vf, self.faceFlux_,
+                                     patchNbrField, faceValue=fv)
+        return fv, corr
+
+
+class WENOUpwindFit01(WENOUpwindFit):
+    """`Gauss WENOUpwindFit01 <order>`: always limited to [0, 1]
+    (WENOUpwindFit01.H:169-201, WENOUpwindFit01.C:37-212)."""
+
+    typeName = "WENOUpwindFit01"
+    _scheme = SCHEME_UPWINDFIT01
+
+    @staticmethod
+    def _read_limiter(tok):
+        return True

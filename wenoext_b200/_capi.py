@@ -1,0 +1,120 @@
+"""ctypes binding of include/wenoext_b200.h (the C-ABI drop-in boundary).
+
+No torch types cross this boundary: plain pointers and sizes only. The library
+must exist in-tree (built by `python -m wenoext_b200.build`); there is no
+fallback of any kind when it is missing.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libwenoext_b200.so")
+
+# constants of include/wenoext_b200.h
+CELL_LOCAL, CELL_DELETED, CELL_EMPTY = -1, -4, -10
+PATCH_GENERIC, PATCH_PROCESSOR, PATCH_CYCLIC, PATCH_EMPTY = 0, 1, 2, 3
+SCHEME_UPWINDFIT, SCHEME_UPWINDFIT01 = 0, 1
+MEM_HOST, MEM_DEVICE = 0, 1
+
+i32p = C.POINTER(C.c_int32)
+i64p = C.POINTER(C.c_int64)
+f64p = C.POINTER(C.c_double)
+
+
+class Patch(C.Structure):
+    _fields_ = [("type", C.c_int32), ("start", C.c_int32), ("size", C.c_int32), ("nbr", C.c_int32)]
+
+
+class PlanDesc(C.Structure):
+    _fields_ = [
+        ("polOrder", C.c_int32), ("nDvt", C.c_int32), ("dim", C.c_int32 * 3),
+        ("nCells", C.c_int32), ("nFaces", C.c_int32), ("nInternalFaces", C.c_int32),
+        ("owner", i32p), ("neighbour", i32p), ("cellFaceStart", i32p), ("cellFaces", i32p),
+        ("nPatches", C.c_int32), ("patches", C.POINTER(Patch)),
+        ("nStencils", C.c_int64), ("cellStencilStart", i64p), ("stencilEntryStart", i64p),
+        ("stencilsID", i32p), ("cellToProcMap", i32p),
+        ("stencilMatrix", i32p), ("nUniqueMatrices", C.c_int32), ("matrixStart", i64p),
+        ("matrixCols", i32p), ("matrixData", f64p),
+        ("B", f64p), ("intBasTrans", f64p), ("refFacAr", f64p),
+        ("nProcs", C.c_int32), ("myProc", C.c_int32),
+        ("sendProcList", i32p), ("receiveProcList", i32p), ("receiveHaloSize", i32p),
+        ("sendHaloStart", i64p), ("sendHaloCellID", i32p),
+        ("patchNbrCell", i32p),
+    ]
+
+
+class PlanInfo(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in (
+        "nCells", "nFaces", "nInternalFaces", "nCoupledFaces", "nLiveStencils", "nHaloCells",
+        "nInteriorCells", "recordBytes", "maxRecordBytes", "algBytesFixed", "algBytesPerComp",
+        "algFlopsPerComp")]
+
+
+class BoxSpec(C.Structure):
+    _fields_ = [("n", C.c_int32 * 3), ("lo", C.c_double * 3), ("hi", C.c_double * 3),
+                ("sideType", C.c_int32 * 6), ("tetSplit", C.c_int32), ("nProc", C.c_int32 * 3)]
+
+
+class SetupParams(C.Structure):
+    _fields_ = [("polOrder", C.c_int32), ("extendRatio", C.c_double),
+                ("bestConditioned", C.c_int32), ("maxCondition", C.c_double),
+                ("checkCondition", C.c_int32), ("nThreads", C.c_int32),
+                ("useClassCache", C.c_int32)]
+
+
+# every symbol include/wenoext_b200.h declares: name -> (restype, argtypes)
+vp = C.c_void_p
+SYMBOLS = {
+    "wenoext_last_error": (C.c_char_p, []),
+    "wenoext_device_count": (C.c_int, []),
+    "wenoext_plan_create": (C.c_int, [C.POINTER(PlanDesc), C.c_int, C.POINTER(vp)]),
+    "wenoext_plan_destroy": (C.c_int, [vp]),
+    "wenoext_plan_get_info": (C.c_int, [vp, C.POINTER(PlanInfo)]),
+    "wenoext_set_params": (C.c_int, [vp, C.c_double, C.c_double, C.c_double]),
+    "wenoext_set_fit01_bug_compat": (C.c_int, [vp, C.c_int]),
+    "wenoext_nccl_unique_id": (C.c_int, [C.c_char_p]),
+    "wenoext_attach_nccl": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
+    "wenoext_correction": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
+    "wenoext_interpolate": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp]),
+    "wenoext_attach_local": (C.c_int, [C.POINTER(vp), C.c_int]),
+    "wenoext_correction_begin": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+    "wenoext_correction_exchange": (C.c_int, [vp]),
+    "wenoext_correction_end": (C.c_int, [vp]),
+    "wenoext_last_launch_count": (C.c_int, [vp]),
+    "wenoext_enable_kernel_timing": (C.c_int, [vp, C.c_int]),
+    "wenoext_last_kernel_ms": (C.c_double, [vp]),
+    "wenoext_setup_box": (C.c_int, [C.POINTER(BoxSpec), C.POINTER(SetupParams), C.c_int32, C.POINTER(vp)]),
+    "wenoext_setup_destroy": (C.c_int, [vp]),
+    "wenoext_setup_desc": (C.c_int, [vp, C.POINTER(PlanDesc)]),
+    "wenoext_setup_halo_request": (C.c_int, [vp, C.c_int32, C.POINTER(i32p), C.POINTER(C.c_int64)]),
+    "wenoext_setup_set_send_halo": (C.c_int, [vp, C.c_int32, i32p, C.c_int64]),
+    "wenoext_setup_geometry": (C.c_int, [vp, C.POINTER(f64p), C.POINTER(f64p)]),
+}
+
+_lib = None
+
+
+class WenoextError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libwenoext_b200.so; raise if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise WenoextError(
+                f"{LIB_PATH} is missing: build it with `python -m wenoext_b200.build` "
+                "(wenoext_b200 has no CPU or eager fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise WenoextError(f"wenoext error {rc}: {lib().wenoext_last_error().decode()}")

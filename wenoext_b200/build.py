@@ -1,0 +1,72 @@
+"""Build the in-tree native libraries.
+
+  libwenoext_b200.so   product: host setup (C++), device plan + kernels (CUDA, sm_100a), C ABI
+  oracle/libweno_oracle.so, oracle/_ref/libweno_oracle_blaze.so   checker (tests only)
+
+nvcc cross-compiles sm_100a without a GPU. Run as `python -m wenoext_b200.build`.
+"""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "wenoext_b200", "csrc")
+LIB = os.path.join(ROOT, "wenoext_b200", "libwenoext_b200.so")
+
+CU_SOURCES = ["kernels.cu", "plan.cu"]
+CPP_SOURCES = [
+    "capi_setup.cpp",
+    "setup/polymesh.cpp",
+    "setup/geometry_weno.cpp",
+    "setup/svd.cpp",
+    "setup/weno_setup.cpp",
+    "setup/box_fast.cpp",
+]
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def _all_deps():
+    deps = []
+    for base, _, files in os.walk(CSRC):
+        deps += [os.path.join(base, f) for f in files if f.endswith((".cu", ".cpp", ".h"))]
+    deps.append(os.path.join(ROOT, "include", "wenoext_b200.h"))
+    return deps
+
+
+def build_product(force=False, verbose=False):
+    if not force and not _newer(LIB, _all_deps()):
+        return LIB
+    objdir = os.path.join(ROOT, "build", "obj")
+    os.makedirs(objdir, exist_ok=True)
+    objs = []
+    common = ["-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include")]
+    for src in CU_SOURCES + CPP_SOURCES:
+        obj = os.path.join(objdir, src.replace("/", "_") + ".o")
+        cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo"] + common
+        if src.endswith(".cu"):
+            cmd += ["-Xptxas", "-v"] if verbose else []
+        cmd += ["-c", os.path.join(CSRC, src), "-o", obj]
+        subprocess.run(cmd, check=True)
+        objs.append(obj)
+    cmd = ["nvcc", "-shared", "-o", LIB] + objs + ["-lpthread", "-ldl", "-cudart", "static"]
+    subprocess.run(cmd, check=True)
+    return LIB
+
+
+def build_oracle(force=False):
+    odir = os.path.join(ROOT, "oracle")
+    subprocess.run(["make", "-C", odir] + (["-B"] if force else []), check=True,
+                   stdout=subprocess.DEVNULL)
+    return os.path.join(odir, "libweno_oracle.so")
+
+
+if __name__ == "__main__":
+    force = "--force" in sys.argv
+    print(build_product(force=force, verbose="-v" in sys.argv))
+    print(build_oracle(force=force))

@@ -1,0 +1,963 @@
+// Device plan creation (flatten + upload + on-device record expansion) and the
+// per-call orchestration of correction(). See include/wenoext_b200.h.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/wenoext_b200.h"
+#include "device_plan.h"
+#include "plan_internal.h"
+
+namespace wenoext {
+
+thread_local std::string g_lastError;
+
+void setError(const std::string& s) { g_lastError = s; }
+
+#define CUDA_TRY(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t _e = (expr);                                                         \
+        if (_e != cudaSuccess) {                                                         \
+            setError(std::string(#expr) + ": " + cudaGetErrorString(_e));                \
+            return WENOEXT_ERR_CUDA;                                                     \
+        }                                                                                \
+    } while (0)
+
+namespace {
+
+template <class T>
+int upload(T** dptr, const T* h, size_t n) {
+    *dptr = nullptr;
+    if (n == 0) return 0;
+    CUDA_TRY(cudaMalloc((void**)dptr, n * sizeof(T)));
+    CUDA_TRY(cudaMemcpy(*dptr, h, n * sizeof(T), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+struct ExpandArgs {
+    int32_t nCells, nFaces, nInternalFaces, K, cube;
+    const int64_t* recOff;
+    const int32_t *cellNSt, *cellTotN, *cellNFc;
+    const int64_t *cellStencilStart, *stencilEntryStart;
+    const int32_t *stencilsID, *cellToProcMap, *stencilMatrix;
+    const int64_t* matrixStart;
+    const int32_t* matrixCols;
+    const double* matrixData;
+    const double *B, *intBasTrans, *refFacAr;
+    const int32_t *owner, *neighbour, *cellFaceStart, *cellFaces;
+    const int32_t* bfPatchType;  // [nBnd]
+    const int32_t* bfNbrCell;    // [nBnd] or null
+    const int64_t* haloOff;      // [nProcs]
+    const int32_t* enumIdx;      // [K] cube index of coefficient k
+    unsigned char* records;
+    uint8_t* cellHasHalo;
+};
+
+// One warp per cell: copies the de-duplicated matrices and the per-cell / per-face
+// setup data into the cell's record (bitwise copies, so parity is unaffected).
+__global__ void expand_records_kernel(const ExpandArgs a) {
+    const int cell = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (cell >= a.nCells) return;
+    const int K = a.K;
+    unsigned char* rec = a.records + a.recOff[cell];
+    const int nSt = a.cellNSt[cell], totN = a.cellTotN[cell], nFc = a.cellNFc[cell];
+    double* Amat = reinterpret_cast<double*>(rec + sizeof(RecHeader));
+    double* Bm = Amat + (size_t)K * totN;
+    double* faceD = Bm + K * K;
+    double* quirk = faceD + (size_t)nFc * (K + 1);
+    int32_t* Ns = reinterpret_cast<int32_t*>(quirk + K);
+    int32_t* idx = Ns + nSt;
+    int32_t* faceI = idx + totN;
+    bool halo = false;
+    if (nSt > 0) {
+        int live = 0, eOff = 0;
+        for (int64_t s = a.cellStencilStart[cell]; s < a.cellStencilStart[cell + 1]; ++s) {
+            const int m = a.stencilMatrix[s];
+            if (m < 0) continue;
+            const int N = a.matrixCols[m];
+            const double* src = a.matrixData + a.matrixStart[m];
+            double* dst = Amat + (size_t)K * eOff;
+            for (int i = lane; i < K * N; i += 32) dst[i] = src[i];
+            const int64_t e0 = a.stencilEntryStart[s];
+            for (int j = lane; j < N; j += 32) {
+                const int32_t id = a.stencilsID[e0 + 1 + j];
+                const int32_t pm = a.cellToProcMap ? a.cellToProcMap[e0 + 1 + j] : -1;
+                int32_t flat = id;
+                if (pm >= 0) {
+                    flat = a.nCells + (int32_t)a.haloOff[pm] + id;
+                    halo = true;
+                }
+                idx[eOff + j] = flat;
+            }
+            if (lane == 0) Ns[live] = N;
+            live++;
+            eOff += N;
+        }
+    }
+    for (int i = lane; i < K * K; i += 32) Bm[i] = a.B[(size_t)cell * K * K + i];
+    for (int k = lane; k < K; k += 32)
+        quirk[k] = cell < a.nFaces ? a.intBasTrans[((size_t)cell * 2 + 1) * a.cube + a.enumIdx[k]] : 0.0;
+    int fOut = 0;
+    for (int i = a.cellFaceStart[cell]; i < a.cellFaceStart[cell + 1]; ++i) {
+        const int f = a.cellFaces[i];
+        int side = 0, other = -1, type = FACE_INTERNAL;
+        if (f < a.nInternalFaces) {
+            if (a.owner[f] == cell) {
+                other = a.neighbour[f];
+            } else {
+                side = 1;
+                other = a.owner[f];
+            }
+        } else {
+            type = a.bfPatchType[f - a.nInternalFaces];
+            if (type < 0) continue;
+            other = a.bfNbrCell ? a.bfNbrCell[f - a.nInternalFaces] : -1;
+        }
+        double* fd = faceD + (size_t)fOut * (K + 1);
+        for (int k = lane; k < K; k += 32)
+            fd[k] = a.intBasTrans[((size_t)f * 2 + side) * a.cube + a.enumIdx[k]];
+        if (lane == 0) {
+            fd[K] = a.refFacAr[f];
+            faceI[fOut * 3 + 0] = f;
+            faceI[fOut * 3 + 1] = other;
+            faceI[fOut * 3 + 2] = side | (type << FACE_TYPE_SHIFT);
+        }
+        fOut++;
+    }
+    halo = __any_sync(0xffffffffu, halo);
+    if (lane == 0) {
+        RecHeader h;
+        h.nSt = nSt;
+        h.nFc = nFc;
+        h.totN = totN;
+        h.flags = halo ? 1 : 0;
+        *reinterpret_cast<RecHeader*>(rec) = h;
+        a.cellHasHalo[cell] = halo ? 1 : 0;
+    }
+}
+
+size_t recordBytes(int K, int nSt, int totN, int nFc) {
+    size_t b = sizeof(RecHeader);
+    b += ((size_t)K * totN + (size_t)K * K + (size_t)nFc * (K + 1) + K) * 8;
+    b += ((size_t)nSt + totN + (size_t)nFc * 3) * 4;
+    return (b + 15) / 16 * 16;
+}
+
+}  // namespace
+}  // namespace wenoext
+
+using namespace wenoext;
+
+static int validateDesc(const wenoext_plan_desc* d) {
+    if (!d) {
+        setError("desc is NULL");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (d->nDvt <= 0 || d->nCells <= 0 || d->nFaces < d->nInternalFaces || d->nInternalFaces < 0) {
+        setError("desc: bad sizes");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (!d->owner || !d->cellFaceStart || !d->cellFaces || !d->cellStencilStart ||
+        !d->stencilEntryStart || !d->stencilsID || !d->stencilMatrix || !d->matrixStart ||
+        !d->matrixCols || !d->matrixData || !d->B || !d->intBasTrans || !d->refFacAr) {
+        setError("desc: required array is NULL");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (d->nInternalFaces > 0 && !d->neighbour) {
+        setError("desc: neighbour is NULL");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (d->nProcs > 1 && (!d->sendProcList || !d->receiveProcList || !d->receiveHaloSize ||
+                          !d->sendHaloStart || !d->cellToProcMap)) {
+        setError("desc: parallel plan needs halo lists and cellToProcMap");
+        return WENOEXT_ERR_INVALID;
+    }
+    return 0;
+}
+
+extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoext_plan** out) {
+    if (!out) {
+        setError("out is NULL");
+        return WENOEXT_ERR_INVALID;
+    }
+    *out = nullptr;
+    if (int rc = validateDesc(d)) return rc;
+    int nDev = 0;
+    if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0) {
+        setError("no CUDA device: wenoext_b200 has no CPU fallback");
+        return WENOEXT_ERR_CUDA;
+    }
+    CUDA_TRY(cudaSetDevice(device));
+    wenoext_plan* P = new wenoext_plan();
+    P->device = device;
+    CUDA_TRY(cudaDeviceGetAttribute(&P->nSM, cudaDevAttrMultiProcessorCount, device));
+    CUDA_TRY(cudaDeviceGetAttribute(&P->smemLimit, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    const int K = d->nDvt;
+    P->polOrder = d->polOrder;
+    P->K = K;
+    P->nCells = d->nCells;
+    P->nFaces = d->nFaces;
+    P->nInt = d->nInternalFaces;
+    P->nBnd = d->nFaces - d->nInternalFaces;
+    P->nProcs = d->nProcs > 0 ? d->nProcs : 1;
+    P->myProc = d->myProc;
+    P->patches.assign(d->patches, d->patches + d->nPatches);
+    if (const char* e = getenv("WENOEXT_WARPS")) P->cfgWarps = atoi(e);
+    if (const char* e = getenv("WENOEXT_SLOTS")) P->cfgSlots = atoi(e);
+    if (const char* e = getenv("WENOEXT_GRID")) P->cfgGrid = atoi(e);
+
+    // coefficient enumeration: n-outer, m, l-inner (WENOUpwindFit.C:304-319)
+    const int s1 = d->polOrder + 1;
+    std::vector<int32_t> enumIdx;
+    for (int n = 0; n <= d->dim[0]; ++n)
+        for (int m = 0; m <= d->dim[1]; ++m)
+            for (int l = 0; l <= d->dim[2]; ++l)
+                if ((n + m + l) <= d->polOrder && (n + m + l) > 0)
+                    enumIdx.push_back(n * s1 * s1 + m * s1 + l);
+    if ((int)enumIdx.size() != K) {
+        setError("desc: nDvt does not match polOrder/dim");
+        delete P;
+        return WENOEXT_ERR_INVALID;
+    }
+
+    // boundary-face tables
+    std::vector<int32_t> bfType(std::max(P->nBnd, 1), -1), bfPartner(std::max(P->nBnd, 1), -1);
+    int64_t nCoupled = 0;
+    for (const auto& pt : P->patches) {
+        if (pt.type != WENOEXT_PATCH_PROCESSOR && pt.type != WENOEXT_PATCH_CYCLIC) continue;
+        for (int i = 0; i < pt.size; ++i) {
+            const int bf = pt.start + i - P->nInt;
+            if (pt.type == WENOEXT_PATCH_PROCESSOR) {
+                bfType[bf] = FACE_PROCESSOR;
+                P->hasProcessor = true;
+            } else {
+                bfType[bf] = FACE_CYCLIC;
+                bfPartner[bf] = P->patches[pt.nbr].start + i;
+            }
+            nCoupled++;
+        }
+    }
+    P->hasCoupled = nCoupled > 0;
+    P->hasNbrCell = d->patchNbrCell != nullptr;
+
+    // halo offsets
+    P->haloOff.assign(P->nProcs + 1, 0);
+    P->sendOff.assign(P->nProcs + 1, 0);
+    P->sendProcList.assign(P->nProcs, -1);
+    P->receiveProcList.assign(P->nProcs, -1);
+    if (P->nProcs > 1) {
+        for (int p = 0; p < P->nProcs; ++p) {
+            P->haloOff[p + 1] = P->haloOff[p] + d->receiveHaloSize[p];
+            P->sendOff[p + 1] = d->sendHaloStart[p + 1];
+            P->sendProcList[p] = d->sendProcList[p];
+            P->receiveProcList[p] = d->receiveProcList[p];
+        }
+    }
+    P->nHaloTotal = P->haloOff[P->nProcs];
+    P->nSendTotal = P->sendOff[P->nProcs];
+
+    // per-cell record sizes
+    const int nC = d->nCells;
+    std::vector<int32_t> cellNSt(nC), cellTotN(nC), cellNFc(nC);
+    std::vector<int64_t> recOff(nC + 1, 0);
+    int64_t algFixed = 0, flopsPerComp = 0, nLive = 0;
+    for (int c = 0; c < nC; ++c) {
+        int nSt = 0, totN = 0;
+        const int64_t s0 = d->cellStencilStart[c], sE = d->cellStencilStart[c + 1];
+        const bool empty = d->stencilsID[d->stencilEntryStart[s0]] == WENOEXT_CELL_EMPTY;
+        if (!empty)
+            for (int64_t s = s0; s < sE; ++s) {
+                const int m = d->stencilMatrix[s];
+                if (m < 0 || d->stencilsID[d->stencilEntryStart[s]] == WENOEXT_CELL_DELETED) continue;
+                const int N = d->matrixCols[m];
+                if (d->stencilEntryStart[s + 1] - d->stencilEntryStart[s] != N + 1) {
+                    setError("desc: stencil size does not match its matrix columns");
+                    delete P;
+                    return WENOEXT_ERR_INVALID;
+                }
+                nSt++;
+                totN += N;
+            }
+        int nFc = 0;
+        for (int i = d->cellFaceStart[c]; i < d->cellFaceStart[c + 1]; ++i) {
+            const int f = d->cellFaces[i];
+            if (f < P->nInt || bfType[f - P->nInt] >= 0) nFc++;
+        }
+        if (nSt > 32) {
+            setError("more than 32 stencils in a cell is not supported");
+            delete P;
+            return WENOEXT_ERR_INVALID;
+        }
+        cellNSt[c] = nSt;
+        cellTotN[c] = totN;
+        cellNFc[c] = nFc;
+        recOff[c + 1] = recOff[c] + (int64_t)recordBytes(K, nSt, totN, nFc);
+        P->maxRecordBytes = std::max(P->maxRecordBytes, recOff[c + 1] - recOff[c]);
+        P->maxTotN = std::max(P->maxTotN, totN);
+        P->maxSt = std::max(P->maxSt, nSt);
+        P->maxFc = std::max(P->maxFc, nFc);
+        nLive += nSt;
+        if (nSt > 0) algFixed += (int64_t)8 * K * totN + 8 * K * K + 4 * totN;
+        flopsPerComp += (int64_t)2 * K * totN + (int64_t)nSt * (2 * K * K + 2 * K) + 2 * nSt * K;
+    }
+    P->maxSt = std::max(P->maxSt, 1);
+    P->maxFc = std::max(P->maxFc, 1);
+    P->maxTotN = std::max(P->maxTotN, 1);
+    P->recordBytesTotal = recOff[nC];
+    const int64_t nWritten = (int64_t)P->nInt + nCoupled;
+    algFixed += nWritten * (8 * K + 24);
+    flopsPerComp += nWritten * 2 * K;
+
+    // upload the flat setup arrays (temporary) and expand on the device
+    ExpandArgs ea{};
+    ea.nCells = nC;
+    ea.nFaces = d->nFaces;
+    ea.nInternalFaces = d->nInternalFaces;
+    ea.K = K;
+    ea.cube = s1 * s1 * s1;
+    std::vector<void*> temps;
+    auto up = [&](auto** dp, const auto* h, size_t n) {
+        int rc = upload(dp, h, n);
+        if (!rc && *dp) temps.push_back((void*)*dp);
+        return rc;
+    };
+    int rc = 0;
+    int64_t* dRecOff = nullptr;
+    int32_t *dNSt, *dTotN, *dNFc, *dSID, *dC2P = nullptr, *dSM, *dMC, *dNei = nullptr, *dCFS, *dCF,
+                                  *dEnum, *dBfNbr = nullptr;
+    int64_t *dCSS, *dSES, *dMS, *dHaloOff;
+    double *dMD, *dB, *dIBT, *dRFA;
+    const int64_t nEntries = d->stencilEntryStart[d->nStencils];
+    rc = rc ? rc : upload(&dRecOff, recOff.data(), recOff.size());
+    rc = rc ? rc : up(&dNSt, cellNSt.data(), (size_t)nC);
+    rc = rc ? rc : up(&dTotN, cellTotN.data(), (size_t)nC);
+    rc = rc ? rc : up(&dNFc, cellNFc.data(), (size_t)nC);
+    rc = rc ? rc : up(&dCSS, d->cellStencilStart, (size_t)nC + 1);
+    rc = rc ? rc : up(&dSES, d->stencilEntryStart, (size_t)d->nStencils + 1);
+    rc = rc ? rc : up(&dSID, d->stencilsID, (size_t)nEntries);
+    if (d->cellToProcMap) rc = rc ? rc : up(&dC2P, d->cellToProcMap, (size_t)nEntries);
+    rc = rc ? rc : up(&dSM, d->stencilMatrix, (size_t)d->nStencils);
+    rc = rc ? rc : up(&dMS, d->matrixStart, (size_t)d->nUniqueMatrices + 1);
+    rc = rc ? rc : up(&dMC, d->matrixCols, (size_t)d->nUniqueMatrices);
+    rc = rc ? rc : up(&dMD, d->matrixData, (size_t)d->matrixStart[d->nUniqueMatrices]);
+    rc = rc ? rc : up(&dB, d->B, (size_t)nC * K * K);
+    rc = rc ? rc : up(&dIBT, d->intBasTrans, (size_t)d->nFaces * 2 * ea.cube);
+    rc = rc ? rc : up(&dRFA, d->refFacAr, (size_t)d->nFaces);
+    rc = rc ? rc : upload(&P->owner, d->owner, (size_t)d->nFaces);
+    if (d->nInternalFaces) rc = rc ? rc : up(&dNei, d->neighbour, (size_t)d->nInternalFaces);
+    rc = rc ? rc : up(&dCFS, d->cellFaceStart, (size_t)nC + 1);
+    rc = rc ? rc : up(&dCF, d->cellFaces, (size_t)d->cellFaceStart[nC]);
+    rc = rc ? rc : upload(&P->bfPatchType, bfType.data(), bfType.size());
+    rc = rc ? rc : upload(&P->bfPartner, bfPartner.data(), bfPartner.size());
+    if (d->patchNbrCell && P->nBnd > 0)
+        rc = rc ? rc : upload(&P->bfNbrCell, d->patchNbrCell, (size_t)P->nBnd);
+    dBfNbr = P->bfNbrCell;
+    rc = rc ? rc : up(&dHaloOff, P->haloOff.data(), P->haloOff.size());
+    rc = rc ? rc : up(&dEnum, enumIdx.data(), enumIdx.size());
+    if (P->nSendTotal > 0) rc = rc ? rc : upload(&P->sendIds, d->sendHaloCellID, (size_t)P->nSendTotal);
+    uint8_t* dHasHalo = nullptr;
+    if (!rc) {
+        cudaError_t e = cudaMalloc((void**)&P->records, (size_t)P->recordBytesTotal);
+        if (e == cudaSuccess) e = cudaMalloc((void**)&dHasHalo, (size_t)nC);
+        if (e != cudaSuccess) {
+            setError(std::string("cudaMalloc(records): ") + cudaGetErrorString(e));
+            rc = WENOEXT_ERR_CUDA;
+        }
+    }
+    if (!rc) {
+        P->recOff = dRecOff;
+        ea.recOff = dRecOff;
+        ea.cellNSt = dNSt;
+        ea.cellTotN = dTotN;
+        ea.cellNFc = dNFc;
+        ea.cellStencilStart = dCSS;
+        ea.stencilEntryStart = dSES;
+        ea.stencilsID = dSID;
+        ea.cellToProcMap = dC2P;
+        ea.stencilMatrix = dSM;
+        ea.matrixStart = dMS;
+        ea.matrixCols = dMC;
+        ea.matrixData = dMD;
+        ea.B = dB;
+        ea.intBasTrans = dIBT;
+        ea.refFacAr = dRFA;
+        ea.owner = P->owner;
+        ea.neighbour = dNei;
+        ea.cellFaceStart = dCFS;
+        ea.cellFaces = dCF;
+        ea.bfPatchType = P->bfPatchType;
+        ea.bfNbrCell = dBfNbr;
+        ea.haloOff = dHaloOff;
+        ea.enumIdx = dEnum;
+        ea.records = P->records;
+        ea.cellHasHalo = dHasHalo;
+        const int64_t threads = (int64_t)nC * 32;
+        expand_records_kernel<<<(unsigned)((threads + 255) / 256), 256>>>(ea);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) {
+            setError(std::string("expand_records_kernel: ") + cudaGetErrorString(e));
+            rc = WENOEXT_ERR_CUDA;
+        }
+    }
+    // interior / boundary cell lists (overlap of the halo exchange)
+    if (!rc) {
+        std::vector<uint8_t> hasHalo(nC);
+        cudaMemcpy(hasHalo.data(), dHasHalo, (size_t)nC, cudaMemcpyDeviceToHost);
+        std::vector<int32_t> li, lb;
+        for (int c = 0; c < nC; ++c) (hasHalo[c] ? lb : li).push_back(c);
+        P->nInterior = (int32_t)li.size();
+        P->nBoundaryCells = (int32_t)lb.size();
+        if (P->nBoundaryCells > 0) {
+            rc = rc ? rc : upload(&P->cellListInterior, li.data(), li.size());
+            rc = rc ? rc : upload(&P->cellListBoundary, lb.data(), lb.size());
+        }
+    }
+    for (void* t : temps) cudaFree(t);
+    if (dHasHalo) cudaFree(dHasHalo);
+    if (rc) {
+        wenoext_plan_destroy(P);
+        return rc;
+    }
+    cudaEventCreateWithFlags(&P->evA, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&P->evB, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&P->evC, cudaEventDisableTiming);
+    cudaEventCreate(&P->evT0);
+    cudaEventCreate(&P->evT1);
+    cudaEventCreate(&P->evT2);
+    cudaEventCreate(&P->evT3);
+    wenoext_plan_info& I = P->info;
+    I.nCells = nC;
+    I.nFaces = d->nFaces;
+    I.nInternalFaces = d->nInternalFaces;
+    I.nCoupledFaces = nCoupled;
+    I.nLiveStencils = nLive;
+    I.nHaloCells = P->nHaloTotal;
+    I.nInteriorCells = P->nInterior;
+    I.recordBytes = P->recordBytesTotal;
+    I.maxRecordBytes = P->maxRecordBytes;
+    I.algBytesFixed = algFixed;
+    I.algBytesPerComp = (int64_t)8 * nC + 8 * nWritten;
+    I.algFlopsPerComp = flopsPerComp;
+    *out = P;
+    return 0;
+}
+
+extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
+    if (!P) return 0;
+    cudaSetDevice(P->device);
+    void* ptrs[] = {P->records, P->recOff, P->cellListInterior, P->cellListBoundary, P->owner,
+                    P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
+                    P->recvPatch, P->thetaPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (P->comm) {
+        if (NcclApi* n = ncclApi()) n->CommDestroy(P->comm);
+    }
+    if (P->commStream) cudaStreamDestroy(P->commStream);
+    cudaEvent_t evs[] = {P->evA, P->evB, P->evC, P->evT0, P->evT1, P->evT2, P->evT3};
+    for (cudaEvent_t e : evs)
+        if (e) cudaEventDestroy(e);
+    delete P;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// NCCL (dlopen)
+// ---------------------------------------------------------------------------
+namespace wenoext {
+NcclApi* ncclApi() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api.handle ? &api : nullptr;
+    tried = true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+        api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (api.handle) break;
+    }
+    if (!api.handle) {
+        setError(std::string("cannot dlopen libnccl: ") + dlerror());
+        return nullptr;
+    }
+    auto sym = [&](const char* n) { return dlsym(api.handle, n); };
+    api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+    api.Send = (decltype(api.Send))sym("ncclSend");
+    api.Recv = (decltype(api.Recv))sym("ncclRecv");
+    api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
+    api.GroupEnd = (decltype(api.GroupEnd))sym("ncclGroupEnd");
+    api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+    if (!api.GetUniqueId || !api.CommInitRank || !api.Send || !api.Recv || !api.GroupStart ||
+        !api.GroupEnd) {
+        setError("libnccl is missing required symbols");
+        dlclose(api.handle);
+        api.handle = nullptr;
+        return nullptr;
+    }
+    return &api;
+}
+}  // namespace wenoext
+
+#define NCCL_TRY(api, expr)                                                               \
+    do {                                                                                  \
+        int _r = (expr);                                                                  \
+        if (_r != 0) {                                                                    \
+            setError(std::string(#expr) + ": " +                                          \
+                     ((api)->GetErrorString ? (api)->GetErrorString(_r) : "nccl error")); \
+            return WENOEXT_ERR_NCCL;                                                      \
+        }                                                                                 \
+    } while (0)
+
+extern "C" int wenoext_nccl_unique_id(char id[128]) {
+    NcclApi* n = ncclApi();
+    if (!n) return WENOEXT_ERR_NCCL;
+    NCCL_TRY(n, n->GetUniqueId(id));
+    return 0;
+}
+
+extern "C" int wenoext_attach_nccl(wenoext_plan* P, const char id[128], int rank, int nRanks) {
+    if (!P || !id) {
+        setError("attach_nccl: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (rank != P->myProc || nRanks != P->nProcs) {
+        setError("attach_nccl: rank/nRanks do not match the plan's myProc/nProcs");
+        return WENOEXT_ERR_INVALID;
+    }
+    NcclApi* n = ncclApi();
+    if (!n) return WENOEXT_ERR_NCCL;
+    CUDA_TRY(cudaSetDevice(P->device));
+    NcclId nid;
+    memcpy(nid.internal, id, 128);
+    NCCL_TRY(n, n->CommInitRank(&P->comm, nRanks, nid, rank));
+    CUDA_TRY(cudaStreamCreateWithFlags(&P->commStream, cudaStreamNonBlocking));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// small accessors
+// ---------------------------------------------------------------------------
+extern "C" const char* wenoext_last_error(void) { return g_lastError.c_str(); }
+
+extern "C" int wenoext_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int wenoext_plan_get_info(const wenoext_plan* P, wenoext_plan_info* info) {
+    if (!P || !info) {
+        setError("plan_get_info: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    *info = P->info;
+    return 0;
+}
+
+extern "C" int wenoext_set_params(wenoext_plan* P, double p, double dm, double epsilon) {
+    if (!P || !(p >= 0)) {
+        setError("set_params: bad argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    P->p = p;
+    P->dm = dm;
+    P->eps = epsilon;
+    return 0;
+}
+
+extern "C" int wenoext_set_fit01_bug_compat(wenoext_plan* P, int on) {
+    if (!P) return WENOEXT_ERR_INVALID;
+    P->bugCompat = on ? 1 : 0;
+    return 0;
+}
+
+extern "C" int wenoext_last_launch_count(const wenoext_plan* P) { return P ? P->lastLaunches : 0; }
+
+extern "C" int wenoext_enable_kernel_timing(wenoext_plan* P, int on) {
+    if (!P) return WENOEXT_ERR_INVALID;
+    P->timing = on != 0;
+    P->lastKernelMs = -1.0;
+    return 0;
+}
+
+extern "C" double wenoext_last_kernel_ms(const wenoext_plan* P) {
+    if (!P || !P->timing) return -1.0;
+    float a = 0, b = 0;
+    if (cudaEventElapsedTime(&a, P->evT0, P->evT1) != cudaSuccess) return -1.0;
+    if (P->timedTwo && cudaEventElapsedTime(&b, P->evT2, P->evT3) != cudaSuccess) return -1.0;
+    return (double)a + (double)b;
+}
+
+// ---------------------------------------------------------------------------
+// correction(): three stream-ordered phases. With NCCL (one process per GPU)
+// a rank runs them back to back; with in-process peers (wenoext_attach_local)
+// the caller runs phase k on every rank before phase k+1.
+//   phase 0  pack values [+ pack halo, post exchange #1, interior cells]
+//   phase 1  [halo arrives] boundary cells (or all cells when serial)
+//            [post exchange #2: coupled-patch values, swapData]
+//   phase 2  coupled patches: received values, cyclic copy, patch limiter
+// ---------------------------------------------------------------------------
+static int ensureBuf(double** p, size_t* cap, size_t n) {
+    if (*cap >= n && *p) return 0;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    CUDA_TRY(cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(double)));
+    *cap = n;
+    return 0;
+}
+
+static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, cudaEvent_t t0,
+                       cudaEvent_t t1) {
+    if (nWork <= 0) return 0;
+    const wenoext_call& c = P->call;
+    CellKernelArgs a{};
+    a.records = P->records;
+    a.recOff = P->recOff;
+    a.cellList = list;
+    a.nWork = nWork;
+    a.K = P->K;
+    a.nComp = c.nComp;
+    a.c0 = c.c0;
+    a.VS = c.VS;
+    a.vals = P->vals;
+    a.flux = c.flux;
+    a.corr = c.corr;
+    a.faceValue = c.fv;
+    a.thetaPatch = (c.scheme == WENOEXT_SCHEME_UPWINDFIT01 && P->hasProcessor) ? P->thetaPatch : nullptr;
+    a.nInternalFaces = P->nInt;
+    a.scheme = c.scheme;
+    a.bounded = c.bounded;
+    a.bugCompat = P->bugCompat;
+    a.pExp = (uint32_t)P->p;  // WENOCoeff.H:149: double -> unsigned
+    a.dm = P->dm;
+    a.eps = P->eps;
+    a.maxTotN = P->maxTotN;
+    a.maxSt = P->maxSt;
+    a.maxFc = P->maxFc;
+    a.slotBytes = (int)((P->maxRecordBytes + 127) / 128 * 128);
+    // shared-memory budget: ring slots + per-warp scratch
+    // as many consumer warps (cells in compute) as leave at least warps+1 ring slots
+    int warps = P->cfgWarps > 0 ? P->cfgWarps : 8;
+    int slots = 0;
+    for (; warps >= 1; --warps) {
+        const size_t fixed =
+            cellKernelSmemBytes(P->K, c.CB, 0, a.slotBytes, a.maxTotN, a.maxSt, a.maxFc, warps) + 256;
+        slots = (size_t)P->smemLimit > fixed
+                    ? (int)(((size_t)P->smemLimit - fixed) / ((size_t)a.slotBytes + 16))
+                    : 0;
+        if (slots >= warps + 1 || (warps == 1 && slots >= 1)) break;
+    }
+    if (warps < 1) warps = 1;
+    if (P->cfgSlots > 0) slots = std::min(slots, P->cfgSlots);
+    if (slots < 1) {
+        setError("cell record does not fit in shared memory (polynomial order too high)");
+        return WENOEXT_ERR_INVALID;
+    }
+    slots = std::min(slots, 64);
+    a.nSlots = slots;
+    a.nConsumerWarps = warps;
+    const size_t smem = cellKernelSmemBytes(P->K, c.CB, slots, a.slotBytes, a.maxTotN, a.maxSt,
+                                            a.maxFc, warps);
+    const int nTiles = (nWork + 31) / 32;
+    int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);
+    if (P->timing && t0) cudaEventRecord(t0, c.st);
+    launchCellKernel(a, c.CB, grid, smem, c.st);
+    if (P->timing && t1) cudaEventRecord(t1, c.st);
+    P->lastLaunches++;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int phase0(wenoext_plan* P) {
+    const wenoext_call& c = P->call;
+    const bool parallel = P->nProcs > 1;
+    launchPackValues(c.vf, P->nCells, c.nComp, c.c0, c.CB, c.VS, P->vals, c.st);
+    P->lastLaunches++;
+    P->timedTwo = false;
+    if (!parallel) return 0;
+    if (P->nSendTotal > 0) {
+        launchPackHalo(P->vals, c.VS, P->sendIds, P->nSendTotal, P->sendBuf, c.st);
+        P->lastLaunches++;
+    }
+    CUDA_TRY(cudaEventRecord(P->evA, c.st));
+    if (P->comm) {
+        NcclApi* n = ncclApi();
+        CUDA_TRY(cudaStreamWaitEvent(P->commStream, P->evA, 0));
+        NCCL_TRY(n, n->GroupStart());
+        for (int p = 0; p < P->nProcs; ++p) {
+            const int64_t ns = P->sendOff[p + 1] - P->sendOff[p];
+            const int64_t nr = P->haloOff[p + 1] - P->haloOff[p];
+            if (P->sendProcList[p] != -1 && ns > 0)
+                NCCL_TRY(n, n->Send(P->sendBuf + P->sendOff[p] * c.VS, (size_t)ns * c.VS, 8, p,
+                                    P->comm, P->commStream));
+            if (P->receiveProcList[p] != -1 && nr > 0)
+                NCCL_TRY(n, n->Recv(P->vals + ((size_t)P->nCells + P->haloOff[p]) * c.VS,
+                                    (size_t)nr * c.VS, 8, p, P->comm, P->commStream));
+        }
+        NCCL_TRY(n, n->GroupEnd());
+        CUDA_TRY(cudaEventRecord(P->evB, P->commStream));
+    }
+    // interior cells overlap the exchange (the reference waits first, WENOCoeff.C:295)
+    return launchCells(P, P->cellListInterior, P->nInterior, P->evT0, P->evT1);
+}
+
+static int phase1(wenoext_plan* P) {
+    const wenoext_call& c = P->call;
+    const bool parallel = P->nProcs > 1;
+    if (!parallel) {
+        if (int rc = launchCells(P, nullptr, P->nCells, P->evT0, P->evT1)) return rc;
+    } else {
+        if (P->comm) {
+            CUDA_TRY(cudaStreamWaitEvent(c.st, P->evB, 0));
+        } else {
+            // in-process peers: pull my halo segments out of the owners' send buffers
+            for (int p = 0; p < P->nProcs; ++p) {
+                const int64_t nr = P->haloOff[p + 1] - P->haloOff[p];
+                if (P->receiveProcList[p] == -1 || nr == 0) continue;
+                wenoext_plan* Q = P->localPeers[p];
+                CUDA_TRY(cudaStreamWaitEvent(c.st, Q->evA, 0));
+                CUDA_TRY(cudaMemcpyAsync(P->vals + ((size_t)P->nCells + P->haloOff[p]) * c.VS,
+                                         Q->sendBuf + Q->sendOff[P->myProc] * c.VS,
+                                         (size_t)nr * c.VS * 8, cudaMemcpyDeviceToDevice, c.st));
+            }
+        }
+        P->timedTwo = P->nInterior > 0 && P->nBoundaryCells > 0;
+        if (int rc = launchCells(P, P->cellListBoundary, P->nBoundaryCells,
+                                 P->nInterior > 0 ? P->evT2 : P->evT0,
+                                 P->nInterior > 0 ? P->evT3 : P->evT1))
+            return rc;
+    }
+    if (P->hasProcessor) {
+        CUDA_TRY(cudaEventRecord(P->evC, c.st));
+        if (P->comm) {
+            // swapData (WENOUpwindFit.C:326-385): whole patch arrays, both directions
+            NcclApi* n = ncclApi();
+            NCCL_TRY(n, n->GroupStart());
+            for (const auto& pt : P->patches) {
+                if (pt.type != WENOEXT_PATCH_PROCESSOR || pt.size == 0) continue;
+                NCCL_TRY(n, n->Send(c.corr + (size_t)pt.start * c.nComp, (size_t)pt.size * c.nComp, 8,
+                                    pt.nbr, P->comm, c.st));
+                NCCL_TRY(n, n->Recv(P->recvPatch + (size_t)(pt.start - P->nInt) * c.nComp,
+                                    (size_t)pt.size * c.nComp, 8, pt.nbr, P->comm, c.st));
+            }
+            NCCL_TRY(n, n->GroupEnd());
+        }
+    }
+    return 0;
+}
+
+static int phase2(wenoext_plan* P) {
+    const wenoext_call& c = P->call;
+    if (!P->hasCoupled) return 0;
+    if (P->hasProcessor && !P->comm) {
+        for (const auto& pt : P->patches) {
+            if (pt.type != WENOEXT_PATCH_PROCESSOR || pt.size == 0) continue;
+            wenoext_plan* Q = P->localPeers[pt.nbr];
+            const wenoext_patch* qp = nullptr;
+            for (const auto& x : Q->patches)
+                if (x.type == WENOEXT_PATCH_PROCESSOR && x.nbr == P->myProc) qp = &x;
+            if (!qp || qp->size != pt.size) {
+                setError("local exchange: processor patches do not match");
+                return WENOEXT_ERR_INVALID;
+            }
+            CUDA_TRY(cudaStreamWaitEvent(c.st, Q->evC, 0));
+            CUDA_TRY(cudaMemcpyAsync(P->recvPatch + (size_t)(pt.start - P->nInt) * c.nComp,
+                                     Q->call.corr + (size_t)qp->start * c.nComp,
+                                     (size_t)pt.size * c.nComp * 8, cudaMemcpyDeviceToDevice, c.st));
+        }
+    }
+    PatchKernelArgs a{};
+    a.nBnd = P->nBnd;
+    a.nInternalFaces = P->nInt;
+    a.nComp = c.nComp;
+    a.bfPatchType = P->bfPatchType;
+    a.bfPartner = P->bfPartner;
+    a.bfNbrCell = P->bfNbrCell;
+    a.owner = P->owner;
+    a.flux = c.flux;
+    a.vf = c.vf;
+    a.vals = P->vals;
+    a.VS = c.VS;
+    a.c0 = c.c0;
+    a.CB = c.CB;
+    a.patchNbrField = c.pnf;
+    a.recv = P->recvPatch;
+    a.thetaPatch = P->thetaPatch;
+    a.corr = c.corr;
+    a.scheme = c.scheme;
+    a.bounded = c.bounded;
+    launchPatchKernel(a, c.st);
+    P->lastLaunches++;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// public per-step entry points
+// ---------------------------------------------------------------------------
+static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
+                       const double* flux, const double* pnf, double* corr, double* fv,
+                       int memKind, void* stream) {
+    if (!P || !vf || !flux || !corr) {
+        setError("correction: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (nComp < 1 || (scheme != WENOEXT_SCHEME_UPWINDFIT && scheme != WENOEXT_SCHEME_UPWINDFIT01)) {
+        setError("correction: bad scheme or nComp");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (P->nProcs > 1 && !P->comm && P->localPeers.empty()) {
+        setError("correction: parallel plan without a communicator (wenoext_attach_nccl)");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (scheme == WENOEXT_SCHEME_UPWINDFIT && bounded && P->hasProcessor && !pnf && !P->hasNbrCell) {
+        setError("correction: bounded limiter on processor patches needs patchNbrField or desc.patchNbrCell");
+        return WENOEXT_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(P->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    wenoext_call& c = P->call;
+    c = wenoext_call();
+    c.scheme = scheme;
+    c.bounded = bounded ? 1 : 0;
+    c.nComp = nComp;
+    c.st = st;
+    const size_t nV = (size_t)P->nCells * nComp, nF = (size_t)P->nFaces;
+    const size_t nB = (size_t)P->nBnd * nComp, nO = nF * nComp, nFV = (size_t)P->nInt * nComp;
+    if (memKind == WENOEXT_MEM_HOST) {
+        if (int rc = ensureBuf(&P->s_vf, &P->s_vfCap, nV)) return rc;
+        if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
+        if (int rc = ensureBuf(&P->s_corr, &P->s_corrCap, nO)) return rc;
+        CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(P->s_flux, flux, nF * 8, cudaMemcpyHostToDevice, st));
+        c.vf = P->s_vf;
+        c.flux = P->s_flux;
+        c.corr = P->s_corr;
+        if (pnf && nB) {
+            if (int rc = ensureBuf(&P->s_pnf, &P->s_pnfCap, nB)) return rc;
+            CUDA_TRY(cudaMemcpyAsync(P->s_pnf, pnf, nB * 8, cudaMemcpyHostToDevice, st));
+            c.pnf = P->s_pnf;
+        }
+        if (fv) {
+            if (int rc = ensureBuf(&P->s_fv, &P->s_fvCap, nFV)) return rc;
+            c.fv = P->s_fv;
+        }
+    } else {
+        c.vf = vf;
+        c.flux = flux;
+        c.pnf = pnf;
+        c.corr = corr;
+        c.fv = fv;
+    }
+    if (int rc = ensureBuf(&P->vals, &P->valsCap, ((size_t)P->nCells + P->nHaloTotal) * 4)) return rc;
+    if (P->nSendTotal)
+        if (int rc = ensureBuf(&P->sendBuf, &P->sendCap, (size_t)P->nSendTotal * 4)) return rc;
+    if (P->hasCoupled && P->patchCap < nB) {
+        if (P->recvPatch) cudaFree(P->recvPatch);
+        if (P->thetaPatch) cudaFree(P->thetaPatch);
+        P->recvPatch = P->thetaPatch = nullptr;
+        CUDA_TRY(cudaMalloc((void**)&P->recvPatch, nB * 8));
+        CUDA_TRY(cudaMalloc((void**)&P->thetaPatch, nB * 8));
+        CUDA_TRY(cudaMemset(P->recvPatch, 0, nB * 8));
+        CUDA_TRY(cudaMemset(P->thetaPatch, 0, nB * 8));
+        P->patchCap = nB;
+    }
+    P->lastLaunches = 0;
+    // boundaryField starts as pTraits::zero (WENOUpwindFit.C:230-246)
+    if (nB) CUDA_TRY(cudaMemsetAsync(c.corr + (size_t)P->nInt * nComp, 0, nB * 8, st));
+    return 0;
+}
+
+static void setBatch(wenoext_plan* P, int c0) {
+    wenoext_call& c = P->call;
+    c.c0 = c0;
+    c.CB = std::min(3, c.nComp - c0);
+    c.VS = c.CB == 3 ? 4 : c.CB;
+}
+
+static int finishCall(wenoext_plan* P, double* corr, double* fv, int memKind) {
+    if (memKind != WENOEXT_MEM_HOST) return 0;
+    const wenoext_call& c = P->call;
+    CUDA_TRY(cudaMemcpyAsync(corr, c.corr, (size_t)P->nFaces * c.nComp * 8, cudaMemcpyDeviceToHost, c.st));
+    if (fv) CUDA_TRY(cudaMemcpyAsync(fv, c.fv, (size_t)P->nInt * c.nComp * 8, cudaMemcpyDeviceToHost, c.st));
+    CUDA_TRY(cudaStreamSynchronize(c.st));
+    return 0;
+}
+
+extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int nComp,
+                                   const double* vf, const double* faceFlux,
+                                   const double* patchNbrField, double* corr, double* faceValue,
+                                   int memKind, void* stream) {
+    if (P && P->nProcs > 1 && !P->comm) {
+        setError("correction: in-process peers need the split-phase calls (wenoext_correction_begin/...)");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (int rc = prepareCall(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, faceValue,
+                             memKind, stream))
+        return rc;
+    for (int c0 = 0; c0 < nComp; c0 += 3) {
+        setBatch(P, c0);
+        if (int rc = phase0(P)) return rc;
+        if (int rc = phase1(P)) return rc;
+        if (int rc = phase2(P)) return rc;
+    }
+    return finishCall(P, corr, faceValue, memKind);
+}
+
+extern "C" int wenoext_correction(wenoext_plan* P, int scheme, int bounded, int nComp,
+                                  const double* vf, const double* faceFlux,
+                                  const double* patchNbrField, double* corr, int memKind,
+                                  void* stream) {
+    return wenoext_interpolate(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, nullptr,
+                               memKind, stream);
+}
+
+// In-process ranks (tests / single-process multi-GPU): plans[r]->myProc == r.
+extern "C" int wenoext_attach_local(wenoext_plan** plans, int nRanks) {
+    if (!plans || nRanks < 1) return WENOEXT_ERR_INVALID;
+    for (int r = 0; r < nRanks; ++r)
+        if (!plans[r] || plans[r]->myProc != r || plans[r]->nProcs != nRanks) {
+            setError("attach_local: plans must be ordered by rank and share nProcs");
+            return WENOEXT_ERR_INVALID;
+        }
+    for (int r = 0; r < nRanks; ++r) plans[r]->localPeers.assign(plans, plans + nRanks);
+    return 0;
+}
+
+// Split-phase form of wenoext_correction for in-process ranks (device pointers,
+// nComp <= 3): call _begin on every rank, then _exchange on every rank, then _end.
+extern "C" int wenoext_correction_begin(wenoext_plan* P, int scheme, int bounded, int nComp,
+                                        const double* vf, const double* faceFlux,
+                                        const double* patchNbrField, double* corr, void* stream) {
+    if (nComp > 3) {
+        setError("split-phase correction supports nComp <= 3");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (int rc = prepareCall(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, nullptr,
+                             WENOEXT_MEM_DEVICE, stream))
+        return rc;
+    setBatch(P, 0);
+    return phase0(P);
+}
+extern "C" int wenoext_correction_exchange(wenoext_plan* P) {
+    if (!P) return WENOEXT_ERR_INVALID;
+    CUDA_TRY(cudaSetDevice(P->device));
+    return phase1(P);
+}
+extern "C" int wenoext_correction_end(wenoext_plan* P) {
+    if (!P) return WENOEXT_ERR_INVALID;
+    CUDA_TRY(cudaSetDevice(P->device));
+    return phase2(P);
+}

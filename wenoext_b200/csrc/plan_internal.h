@@ -1,0 +1,99 @@
+// Internal definition of the opaque wenoext_plan (one plan <-> one GPU <-> one
+// host thread at a time; SURVEY.md 8b "Threading").
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/wenoext_b200.h"
+
+namespace wenoext {
+void setError(const std::string& s);
+extern thread_local std::string g_lastError;
+
+// NCCL entry points resolved with dlopen (no link-time dependency, so the
+// library loads on machines without NCCL or without a GPU).
+struct NcclId {
+    char internal[128];
+};
+struct NcclApi {
+    void* handle = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclId /*ncclUniqueId by value*/, int) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi* ncclApi();  // nullptr (and last error set) if libnccl cannot be loaded
+}  // namespace wenoext
+
+struct wenoext_call {
+    int scheme = 0, bounded = 0, nComp = 0, c0 = 0, CB = 0, VS = 0;
+    const double *vf = nullptr, *flux = nullptr, *pnf = nullptr;  // device pointers
+    double *corr = nullptr, *fv = nullptr;
+    cudaStream_t st = nullptr;
+};
+
+struct wenoext_plan {
+    int device = 0;
+    int nSM = 0;
+    int smemLimit = 0;
+    int32_t polOrder = 0, K = 0, nCells = 0, nFaces = 0, nInt = 0, nBnd = 0;
+    int32_t nProcs = 1, myProc = 0;
+    // records
+    unsigned char* records = nullptr;
+    int64_t* recOff = nullptr;
+    int64_t recordBytesTotal = 0, maxRecordBytes = 0;
+    int32_t maxTotN = 0, maxSt = 0, maxFc = 0;
+    int32_t* cellListInterior = nullptr;
+    int32_t* cellListBoundary = nullptr;
+    int32_t nInterior = 0, nBoundaryCells = 0;
+    // faces / patches
+    int32_t* owner = nullptr;
+    int32_t* bfPatchType = nullptr;
+    int32_t* bfPartner = nullptr;
+    int32_t* bfNbrCell = nullptr;
+    bool hasCoupled = false, hasProcessor = false, hasNbrCell = false;
+    std::vector<wenoext_patch> patches;
+    // halo exchange #1
+    std::vector<int64_t> haloOff, sendOff;  // [nProcs+1], in cells
+    std::vector<int32_t> sendProcList, receiveProcList;
+    int32_t* sendIds = nullptr;
+    int64_t nSendTotal = 0, nHaloTotal = 0;
+    // work buffers
+    double* vals = nullptr;
+    size_t valsCap = 0;
+    double* sendBuf = nullptr;
+    size_t sendCap = 0;
+    double* recvPatch = nullptr;
+    double* thetaPatch = nullptr;
+    size_t patchCap = 0;
+    // staging for host-pointer calls
+    double *s_vf = nullptr, *s_flux = nullptr, *s_pnf = nullptr, *s_corr = nullptr,
+           *s_fv = nullptr;
+    size_t s_vfCap = 0, s_fluxCap = 0, s_pnfCap = 0, s_corrCap = 0, s_fvCap = 0;
+    // WENODict factors
+    double p = 4.0, dm = 1000.0, eps = 1e-40;
+    int bugCompat = 1;
+    // in-process peers (single-process multi-rank runs, e.g. tests on one GPU)
+    std::vector<wenoext_plan*> localPeers;
+    wenoext_call call;
+    // NCCL
+    void* comm = nullptr;
+    cudaStream_t commStream = nullptr;
+    cudaEvent_t evA = nullptr, evB = nullptr, evC = nullptr;
+    // statistics
+    int lastLaunches = 0;
+    bool timing = false;
+    cudaEvent_t evT0 = nullptr, evT1 = nullptr, evT2 = nullptr, evT3 = nullptr;
+    bool timedTwo = false;
+    double lastKernelMs = -1.0;
+    wenoext_plan_info info{};
+    // launch geometry overrides (tuning): 0 = auto
+    int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0;
+};

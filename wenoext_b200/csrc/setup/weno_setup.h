@@ -1,0 +1,74 @@
+// Host stand-in for the reference's once-only WENOBase preprocessing
+// (libWENOEXT/WENOBase/WENOBase.C:674-938). OpenFOAM is not available here, so
+// the meshes come from polymesh.h; every step below cites what it restates.
+// The result (HostPlan) keeps the shapes of WENOBase's accessors
+// (WENOBase.H:319-397) flattened to CSR, and is the input contract of the
+// per-step CUDA path (include/wenoext_b200.h: wenoext_plan_desc).
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "polymesh.h"
+
+namespace wenoext {
+
+// WENOBase::Cell (WENOBase.H:62-67)
+enum : int32_t { CELL_LOCAL = -1, CELL_DELETED = -4, CELL_EMPTY = -10 };
+
+struct SetupParams {
+    int32_t polOrder = 2;
+    // WENODict keys and defaults (WENOBase.C:728-735)
+    double extendRatio = 2.5;
+    bool bestConditioned = false;
+    double maxCondition = 1e-5;
+    bool checkCondition = true;
+    int32_t nThreads = 0;  // 0: hardware concurrency
+};
+
+struct HostPlan {
+    int32_t polOrder = 0, nDvt = 0;
+    int32_t dim[3] = {0, 0, 0};  // dimList()[cell], identical for all cells
+    int32_t nCells = 0, nFaces = 0, nInternalFaces = 0;
+    // mesh addressing of the rank-local mesh
+    std::vector<int32_t> owner, neighbour, cellFaceStart, cellFaces;
+    std::vector<Patch> patches;
+    // stencilsID()[cell][stencil][j] / cellToProcMap()[cell][stencil][j], CSR
+    std::vector<int64_t> cellStencilStart;   // [nCells+1] -> stencil index
+    std::vector<int64_t> stencilEntryStart;  // [nStencils+1] -> entry index
+    std::vector<int32_t> stencilsID;
+    std::vector<int32_t> cellToProcMap;
+    // LSmatrix()[cell][stencil]: index into the de-duplicated pool (matrixDB), -1 if deleted
+    std::vector<int32_t> stencilMatrix;  // [nStencils]
+    std::vector<int64_t> matrixStart;    // [nUnique+1] offsets into matrixData
+    std::vector<int32_t> matrixCols;     // [nUnique]; rows = nDvt, row-major, unpadded
+    std::vector<double> matrixData;
+    std::vector<double> B;            // [nCells][nDvt][nDvt]
+    std::vector<double> intBasTrans;  // [nFaces][2][(polOrder+1)^3], List3D index
+    std::vector<double> refFacAr;     // [nFaces]
+    // halo lists, indexed by processor id, -1 = no traffic (WENOBase.H:122-138)
+    int32_t nProcs = 1, myProc = 0;
+    std::vector<int32_t> sendProcList, receiveProcList, receiveHaloSize;
+    std::vector<std::vector<int32_t>> sendHaloCellIDList;
+    // what this rank asks of each other rank (their processor-local cell ids, in
+    // halo-id order); the owner's sendHaloCellIDList is filled from it
+    // (distributeStencils, WENOBase.C:334-407)
+    std::vector<std::vector<int32_t>> requestHaloCellID;
+    // for each boundary face of a coupled patch: flat value index of the cell across
+    // (cyclic: local id; processor: nCells + haloOffset(proc) + haloId), else -1
+    std::vector<int32_t> patchNbrCell;
+    // geometry kept for tests / synthetic fields (not read by the hot path)
+    std::vector<double> cellCentres;  // [nCells][3]
+    std::vector<double> faceAreaVec;  // [nFaces][3]  Sf
+    // statistics like matrixDB::info (matrixDB.C:232-273)
+    int64_t nMatricesTotal = 0;
+};
+
+// Generic path: any PolyMesh, any decomposition. `cellProc` may be empty (serial).
+HostPlan buildPlanGeneric(const PolyMesh& globalMesh, const std::vector<int32_t>& cellProc,
+                          int32_t nProcs, int32_t myProc, const SetupParams& prm);
+
+// After every rank has built its plan: hand rank `from`'s request list to the
+// owner `plan` (what Pstream does in distributeStencils).
+void setSendHalo(HostPlan& plan, int32_t from, const int32_t* ids, int64_t n);
+
+}  // namespace wenoext
