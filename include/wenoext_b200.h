@@ -184,10 +184,12 @@ int wenoext_correction_end(wenoext_plan* plan);
 
 /* Number of this library's kernel launches issued by the last correction call. */
 int wenoext_last_launch_count(const wenoext_plan* plan);
-/* CUDA-event time (ms) of the fused cell kernel(s) in the last call made with
- * timing enabled; <0 if timing is off. */
+/* With timing on, every launch of the fused cell kernel is bracketed by a CUDA
+ * event pair on the launching stream. wenoext_kernel_time waits for them and
+ * returns the summed device time (ms) and the number of timed launches since
+ * timing was enabled or last reset. */
 int wenoext_enable_kernel_timing(wenoext_plan* plan, int on);
-double wenoext_last_kernel_ms(const wenoext_plan* plan);
+int wenoext_kernel_time(wenoext_plan* plan, double* msSum, int* nLaunches, int reset);
 
 /* ---------------------------------------------------------------------------
  * Host setup stand-in (WENOBase::WENOBase, WENOBase.C:674-938) on generated box

@@ -58,8 +58,9 @@ static int64_t haloOffset(const wenoext_plan_desc* d, int proc) {
 /* WENOCoeff::getWENOPol + calcCoeff + calcWeight (WENOCoeff.C:299-354, :104-165,
  * :168-221). haloData: receiveHaloData_[proc][id] flattened by proc id.
  * coeffsWeighted: [nCells][nDvt][nComp], zero for Cell::empty cells. */
-int FN(getWENOPol)(const wenoext_plan_desc* d, int nComp, double p_, double dm_, double epsilon_,
-                   const double* vf, const double* haloData, double* coeffsWeighted) {
+int FN(getWENOPol_range)(const wenoext_plan_desc* d, int nComp, double p_, double dm_,
+                         double epsilon_, const double* vf, const double* haloData,
+                         double* coeffsWeighted, int cell0, int cell1) {
     const int K = d->nDvt;
     const unsigned int pExp = (unsigned int)p_;
     int64_t* hoff = (int64_t*)malloc(sizeof(int64_t) * (d->nProcs + 1));
@@ -79,9 +80,10 @@ int FN(getWENOPol)(const wenoext_plan_desc* d, int nComp, double p_, double dm_,
     real* sumB = (real*)malloc(sizeof(real) * K * nComp);
     real* acc = (real*)malloc(sizeof(real) * K * nComp);
     real* gammaSum = (real*)malloc(sizeof(real) * nComp);
-    memset(coeffsWeighted, 0, sizeof(double) * (size_t)d->nCells * K * nComp);
+    memset(coeffsWeighted + (size_t)cell0 * K * nComp, 0,
+           sizeof(double) * (size_t)(cell1 - cell0) * K * nComp);
 
-    for (int cellI = 0; cellI < d->nCells; ++cellI) {
+    for (int cellI = cell0; cellI < cell1; ++cellI) {
         const int64_t s0 = d->cellStencilStart[cellI], s1 = d->cellStencilStart[cellI + 1];
         /* WENOCoeff.C:333 */
         if (d->stencilsID[d->stencilEntryStart[s0]] == WENOEXT_CELL_EMPTY) continue;
@@ -153,6 +155,12 @@ int FN(getWENOPol)(const wenoext_plan_desc* d, int nComp, double p_, double dm_,
     return 0;
 }
 
+int FN(getWENOPol)(const wenoext_plan_desc* d, int nComp, double p_, double dm_, double epsilon_,
+                   const double* vf, const double* haloData, double* coeffsWeighted) {
+    return FN(getWENOPol_range)(d, nComp, p_, dm_, epsilon_, vf, haloData, coeffsWeighted, 0,
+                                d->nCells);
+}
+
 /* WENOUpwindFit::sumFlux (WENOUpwindFit.C:293-323); cube = intBasTrans()[f][side] */
 static void sumFlux(const wenoext_plan_desc* d, int nComp, const double* coeffcI,
                     const double* cube, real* flux) {
@@ -182,15 +190,14 @@ static int isCoupled(const wenoext_patch* p) {
  * (WENOUpwindFit.C:256-282 and :425-470). corr [nFaces][nComp] is fully
  * written (zero where the reference leaves pTraits::zero). btsfUD
  * [nFaces-nInternalFaces][nComp] is what swapData would send. */
-int FN(phaseA)(const wenoext_plan_desc* d, int nComp, const double* faceFlux,
-               const double* coeffsWeighted, double* corr, double* btsfUD) {
+/* internal-face loop of correction() (WENOUpwindFit.C:256-282) over a face range
+ * (the threaded CPU baseline splits it; corr must be pre-zeroed) */
+int FN(internalFaces_range)(const wenoext_plan_desc* d, int nComp, const double* faceFlux,
+                            const double* coeffsWeighted, double* corr, int face0, int face1) {
     const int K = d->nDvt;
-    const int nInt = d->nInternalFaces;
     real flux[16];
     if (nComp > 16) return 1;
-    memset(corr, 0, sizeof(double) * (size_t)d->nFaces * nComp);
-    memset(btsfUD, 0, sizeof(double) * (size_t)(d->nFaces - nInt) * nComp);
-    for (int faceI = 0; faceI < nInt; ++faceI) {
+    for (int faceI = face0; faceI < face1; ++faceI) {
         if (faceFlux[faceI] > 0) {
             const int P = d->owner[faceI];
             sumFlux(d, nComp, coeffsWeighted + (size_t)P * K * nComp, cubeOf(d, faceI, 0), flux);
@@ -203,6 +210,18 @@ int FN(phaseA)(const wenoext_plan_desc* d, int nComp, const double* faceFlux,
                 corr[(size_t)faceI * nComp + c] = (double)(flux[c] / (real)d->refFacAr[faceI]);
         }
     }
+    return 0;
+}
+
+int FN(phaseA)(const wenoext_plan_desc* d, int nComp, const double* faceFlux,
+               const double* coeffsWeighted, double* corr, double* btsfUD) {
+    const int K = d->nDvt;
+    const int nInt = d->nInternalFaces;
+    real flux[16];
+    if (nComp > 16) return 1;
+    memset(corr, 0, sizeof(double) * (size_t)d->nFaces * nComp);
+    memset(btsfUD, 0, sizeof(double) * (size_t)(d->nFaces - nInt) * nComp);
+    FN(internalFaces_range)(d, nComp, faceFlux, coeffsWeighted, corr, 0, nInt);
     for (int patchI = 0; patchI < d->nPatches; ++patchI) {
         const wenoext_patch* pt = &d->patches[patchI];
         if (!isCoupled(pt)) continue; /* :433 */
@@ -223,10 +242,10 @@ int FN(phaseA)(const wenoext_plan_desc* d, int nComp, const double* faceFlux,
 }
 
 /* WENOUpwindFit::calcLimiter (WENOUpwindFit.C:38-209) */
-static void limiterFit(const wenoext_plan_desc* d, int nComp, const double* vf,
-                       const double* faceFlux, const double* patchNbrField, double* corr) {
-    const int nInt = d->nInternalFaces;
-    for (int faceI = 0; faceI < nInt; ++faceI) {
+/* internal-face part of WENOUpwindFit::calcLimiter (:81-108, :172-179) over a range */
+int FN(limiterFitInternal_range)(const wenoext_plan_desc* d, int nComp, const double* vf,
+                                 const double* faceFlux, double* corr, int face0, int face1) {
+    for (int faceI = face0; faceI < face1; ++faceI) {
         const int P = d->owner[faceI], N = d->neighbour[faceI];
         const int up = faceFlux[faceI] > 0 ? P : N, dn = faceFlux[faceI] > 0 ? N : P;
         for (int c = 0; c < nComp; ++c) {
@@ -240,6 +259,13 @@ static void limiterFit(const wenoext_plan_desc* d, int nComp, const double* vf,
             corr[(size_t)faceI * nComp + c] = (double)(theta * t);
         }
     }
+    return 0;
+}
+
+static void limiterFit(const wenoext_plan_desc* d, int nComp, const double* vf,
+                       const double* faceFlux, const double* patchNbrField, double* corr) {
+    const int nInt = d->nInternalFaces;
+    FN(limiterFitInternal_range)(d, nComp, vf, faceFlux, corr, 0, nInt);
     for (int patchI = 0; patchI < d->nPatches; ++patchI) {
         const wenoext_patch* pt = &d->patches[patchI];
         /* theta is computed on every coupled patch (:118-165) but only

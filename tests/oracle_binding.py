@@ -29,6 +29,13 @@ class Oracle:
         self._A = getattr(self.L, pre + "_phaseA")
         self._B = getattr(self.L, pre + "_phaseB")
         self._pol.argtypes = [vp, C.c_int, C.c_double, C.c_double, C.c_double, vp, vp, vp]
+        self._polr = getattr(self.L, pre + "_getWENOPol_range")
+        self._polr.argtypes = [vp, C.c_int, C.c_double, C.c_double, C.c_double, vp, vp, vp,
+                               C.c_int, C.c_int]
+        self._facesr = getattr(self.L, pre + "_internalFaces_range")
+        self._facesr.argtypes = [vp, C.c_int, vp, vp, vp, C.c_int, C.c_int]
+        self._limr = getattr(self.L, pre + "_limiterFitInternal_range")
+        self._limr.argtypes = [vp, C.c_int, vp, vp, vp, C.c_int, C.c_int]
         self._A.argtypes = [vp, C.c_int, vp, vp, vp, vp]
         self._B.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
         self.BL = None
@@ -87,6 +94,51 @@ class Oracle:
         corr, ud = self.phaseA(case, faceFlux, cw)
         self.phaseB(case, scheme, bounded, vf, faceFlux, cw, corr, None, ud, bugCompat)
         return corr[:, 0] if vf.ndim == 1 else corr
+
+
+def correction_threaded(orc, case, bounded, vf, faceFlux, nThreads, p=4.0, dm=1000.0, eps=1e-40):
+    """WENOUpwindFit correction() of a SERIAL case with the cell loop
+    (WENOCoeff.C:326-351), the internal-face loop (WENOUpwindFit.C:256-282) and the
+    internal-face limiter (:81-108,:172-179) split over `nThreads` host threads
+    (ctypes releases the GIL). Stand-in for `mpirun -np <cores>` of the reference on
+    a box without MPI; used by bench.py's CPU legs. Coupled patches are not handled
+    (serial box cases have none)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    vf = _f64(vf)
+    flux = _f64(faceFlux)
+    nComp = 1 if vf.ndim == 1 else vf.shape[1]
+    d = C.addressof(case.desc)
+    cw = np.empty((case.nCells, case.nDvt, nComp))
+    corr = np.zeros((case.nFaces, nComp))
+    blaze = orc.variant == "blaze"
+    h = orc._blaze_handle(case) if blaze else None
+
+    def cells(r):
+        a, b = r
+        if blaze:
+            return orc.BL.weno_oracle_blaze_getWENOPol_range(h, nComp, p, dm, eps, _dp(vf), None,
+                                                             _dp(cw), a, b)
+        return orc._polr(d, nComp, p, dm, eps, _dp(vf), None, _dp(cw), a, b)
+
+    def faces(r):
+        a, b = r
+        rc = orc._facesr(d, nComp, _dp(flux), _dp(cw), _dp(corr), a, b)
+        if bounded and not rc:
+            rc = orc._limr(d, nComp, _dp(vf), _dp(flux), _dp(corr), a, b)
+        return rc
+
+    def split(n):
+        e = np.linspace(0, n, nThreads + 1).astype(int)
+        return [(int(e[i]), int(e[i + 1])) for i in range(nThreads)]
+
+    if nThreads <= 1:
+        assert cells((0, case.nCells)) == 0 and faces((0, case.nInternalFaces)) == 0
+    else:
+        with ThreadPoolExecutor(nThreads) as ex:
+            assert all(rc == 0 for rc in ex.map(cells, split(case.nCells)))
+            assert all(rc == 0 for rc in ex.map(faces, split(case.nInternalFaces)))
+    return corr[:, 0] if vf.ndim == 1 else corr
 
 
 def correction_multirank(orc, cases, scheme, bounded, vfs, fluxes, p=4.0, dm=1000.0, eps=1e-40,

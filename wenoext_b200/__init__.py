@@ -29,7 +29,9 @@ from ._capi import (MEM_DEVICE, MEM_HOST, PATCH_CYCLIC, PATCH_EMPTY, PATCH_GENER
                     lib)
 
 __all__ = ["BoxCase", "WENOBase", "Plan", "WENOUpwindFit", "WENOUpwindFit01", "WenoextError",
-           "exchange_halo_lists", "PATCH_GENERIC", "PATCH_PROCESSOR", "PATCH_CYCLIC", "PATCH_EMPTY"]
+           "exchange_halo_lists", "exchange_halo_lists_distributed", "attach_local",
+           "correction_local", "nccl_unique_id", "SCHEME_UPWINDFIT", "SCHEME_UPWINDFIT01",
+           "PATCH_GENERIC", "PATCH_PROCESSOR", "PATCH_CYCLIC", "PATCH_EMPTY"]
 
 
 def _np_view(ptr, shape, dtype):
@@ -165,8 +167,12 @@ class Plan:
     def enable_kernel_timing(self, on=True):
         check(lib().wenoext_enable_kernel_timing(self._h, int(on)))
 
-    def last_kernel_ms(self):
-        return lib().wenoext_last_kernel_ms(self._h)
+    def kernel_time(self, reset=True):
+        """(summed device ms, launches) of the fused cell kernel since timing was
+        enabled / last reset (CUDA events on the launching stream)."""
+        ms, n = C.c_double(), C.c_int()
+        check(lib().wenoext_kernel_time(self._h, C.byref(ms), C.byref(n), int(reset)))
+        return ms.value, n.value
 
     def last_launch_count(self):
         return lib().wenoext_last_launch_count(self._h)
@@ -230,6 +236,50 @@ class Plan:
             self.destroy()
         except Exception:
             pass
+
+
+def nccl_unique_id():
+    """ncclGetUniqueId through the C ABI (rank 0 creates it, the host side ships it)."""
+    buf = C.create_string_buffer(128)
+    check(lib().wenoext_nccl_unique_id(buf))
+    return buf.raw
+
+
+def attach_local(plans):
+    """wenoext_attach_local: all ranks of a decomposed case as plans in ONE
+    process (exchanges become device-to-device copies)."""
+    arr = (C.c_void_p * len(plans))(*[p._h for p in plans])
+    check(lib().wenoext_attach_local(arr, len(plans)))
+
+
+def correction_local(plans, scheme, bounded, vfs, fluxes, patchNbrFields=None, outs=None):
+    """Split-phase correction() of in-process ranks (torch CUDA tensors): phase k
+    runs on every rank before phase k+1, like the reference's MPI ranks do between
+    collectData / swapData (WENOCoeff.C:224-296, WENOUpwindFit.C:326-385)."""
+    import torch
+    L = lib()
+    R = len(plans)
+    keep = []
+    if outs is None:
+        outs = []
+        for r in range(R):
+            nComp = 1 if vfs[r].ndim == 1 else int(vfs[r].shape[1])
+            shape = (plans[r].nFaces,) if vfs[r].ndim == 1 else (plans[r].nFaces, nComp)
+            outs.append(torch.empty(shape, dtype=torch.float64, device=vfs[r].device))
+    for r in range(R):
+        vf, fl = vfs[r].contiguous(), fluxes[r].contiguous()
+        pn = None if patchNbrFields is None else patchNbrFields[r].contiguous()
+        keep += [vf, fl, pn]
+        nComp = 1 if vf.ndim == 1 else int(vf.shape[1])
+        st = torch.cuda.current_stream(vf.device).cuda_stream
+        check(L.wenoext_correction_begin(plans[r]._h, scheme, int(bounded), nComp, vf.data_ptr(),
+                                         fl.data_ptr(), None if pn is None else pn.data_ptr(),
+                                         outs[r].data_ptr(), st))
+    for r in range(R):
+        check(L.wenoext_correction_exchange(plans[r]._h))
+    for r in range(R):
+        check(L.wenoext_correction_end(plans[r]._h))
+    return outs
 
 
 class WENOBase:

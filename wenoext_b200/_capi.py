@@ -82,7 +82,7 @@ SYMBOLS = {
     "wenoext_correction_end": (C.c_int, [vp]),
     "wenoext_last_launch_count": (C.c_int, [vp]),
     "wenoext_enable_kernel_timing": (C.c_int, [vp, C.c_int]),
-    "wenoext_last_kernel_ms": (C.c_double, [vp]),
+    "wenoext_kernel_time": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_int]),
     "wenoext_setup_box": (C.c_int, [C.POINTER(BoxSpec), C.POINTER(SetupParams), C.c_int32, C.POINTER(vp)]),
     "wenoext_setup_destroy": (C.c_int, [vp]),
     "wenoext_setup_desc": (C.c_int, [vp, C.POINTER(PlanDesc)]),

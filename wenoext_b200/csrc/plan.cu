@@ -428,10 +428,6 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     cudaEventCreateWithFlags(&P->evA, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&P->evB, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&P->evC, cudaEventDisableTiming);
-    cudaEventCreate(&P->evT0);
-    cudaEventCreate(&P->evT1);
-    cudaEventCreate(&P->evT2);
-    cudaEventCreate(&P->evT3);
     wenoext_plan_info& I = P->info;
     I.nCells = nC;
     I.nFaces = d->nFaces;
@@ -461,9 +457,10 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
         if (NcclApi* n = ncclApi()) n->CommDestroy(P->comm);
     }
     if (P->commStream) cudaStreamDestroy(P->commStream);
-    cudaEvent_t evs[] = {P->evA, P->evB, P->evC, P->evT0, P->evT1, P->evT2, P->evT3};
+    cudaEvent_t evs[] = {P->evA, P->evB, P->evC};
     for (cudaEvent_t e : evs)
         if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : P->timeEvents) cudaEventDestroy(e);
     delete P;
     return 0;
 }
@@ -587,16 +584,26 @@ extern "C" int wenoext_last_launch_count(const wenoext_plan* P) { return P ? P->
 extern "C" int wenoext_enable_kernel_timing(wenoext_plan* P, int on) {
     if (!P) return WENOEXT_ERR_INVALID;
     P->timing = on != 0;
-    P->lastKernelMs = -1.0;
+    P->timeUsed = 0;
     return 0;
 }
 
-extern "C" double wenoext_last_kernel_ms(const wenoext_plan* P) {
-    if (!P || !P->timing) return -1.0;
-    float a = 0, b = 0;
-    if (cudaEventElapsedTime(&a, P->evT0, P->evT1) != cudaSuccess) return -1.0;
-    if (P->timedTwo && cudaEventElapsedTime(&b, P->evT2, P->evT3) != cudaSuccess) return -1.0;
-    return (double)a + (double)b;
+extern "C" int wenoext_kernel_time(wenoext_plan* P, double* msSum, int* nLaunches, int reset) {
+    if (!P || !msSum) {
+        setError("kernel_time: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    *msSum = 0.0;
+    if (nLaunches) *nLaunches = (int)(P->timeUsed / 2);
+    CUDA_TRY(cudaSetDevice(P->device));
+    for (size_t i = 0; i + 1 < P->timeUsed; i += 2) {
+        float ms = 0;
+        CUDA_TRY(cudaEventSynchronize(P->timeEvents[i + 1]));
+        CUDA_TRY(cudaEventElapsedTime(&ms, P->timeEvents[i], P->timeEvents[i + 1]));
+        *msSum += (double)ms;
+    }
+    if (reset) P->timeUsed = 0;
+    return 0;
 }
 
 // ---------------------------------------------------------------------------
@@ -618,8 +625,7 @@ static int ensureBuf(double** p, size_t* cap, size_t n) {
     return 0;
 }
 
-static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, cudaEvent_t t0,
-                       cudaEvent_t t1) {
+static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     if (nWork <= 0) return 0;
     const wenoext_call& c = P->call;
     CellKernelArgs a{};
@@ -672,9 +678,23 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, cudaEven
                                             a.maxFc, warps);
     const int nTiles = (nWork + 31) / 32;
     int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);
-    if (P->timing && t0) cudaEventRecord(t0, c.st);
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    if (P->timing) {
+        // one event pair per timed launch, summed by wenoext_kernel_time()
+        if (P->timeUsed + 2 > P->timeEvents.size()) {
+            cudaEvent_t e0, e1;
+            CUDA_TRY(cudaEventCreate(&e0));
+            CUDA_TRY(cudaEventCreate(&e1));
+            P->timeEvents.push_back(e0);
+            P->timeEvents.push_back(e1);
+        }
+        t0 = P->timeEvents[P->timeUsed];
+        t1 = P->timeEvents[P->timeUsed + 1];
+        P->timeUsed += 2;
+        cudaEventRecord(t0, c.st);
+    }
     launchCellKernel(a, c.CB, grid, smem, c.st);
-    if (P->timing && t1) cudaEventRecord(t1, c.st);
+    if (t1) cudaEventRecord(t1, c.st);
     P->lastLaunches++;
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -685,7 +705,6 @@ static int phase0(wenoext_plan* P) {
     const bool parallel = P->nProcs > 1;
     launchPackValues(c.vf, P->nCells, c.nComp, c.c0, c.CB, c.VS, P->vals, c.st);
     P->lastLaunches++;
-    P->timedTwo = false;
     if (!parallel) return 0;
     if (P->nSendTotal > 0) {
         launchPackHalo(P->vals, c.VS, P->sendIds, P->nSendTotal, P->sendBuf, c.st);
@@ -710,14 +729,14 @@ static int phase0(wenoext_plan* P) {
         CUDA_TRY(cudaEventRecord(P->evB, P->commStream));
     }
     // interior cells overlap the exchange (the reference waits first, WENOCoeff.C:295)
-    return launchCells(P, P->cellListInterior, P->nInterior, P->evT0, P->evT1);
+    return launchCells(P, P->cellListInterior, P->nInterior);
 }
 
 static int phase1(wenoext_plan* P) {
     const wenoext_call& c = P->call;
     const bool parallel = P->nProcs > 1;
     if (!parallel) {
-        if (int rc = launchCells(P, nullptr, P->nCells, P->evT0, P->evT1)) return rc;
+        if (int rc = launchCells(P, nullptr, P->nCells)) return rc;
     } else {
         if (P->comm) {
             CUDA_TRY(cudaStreamWaitEvent(c.st, P->evB, 0));
@@ -733,11 +752,7 @@ static int phase1(wenoext_plan* P) {
                                          (size_t)nr * c.VS * 8, cudaMemcpyDeviceToDevice, c.st));
             }
         }
-        P->timedTwo = P->nInterior > 0 && P->nBoundaryCells > 0;
-        if (int rc = launchCells(P, P->cellListBoundary, P->nBoundaryCells,
-                                 P->nInterior > 0 ? P->evT2 : P->evT0,
-                                 P->nInterior > 0 ? P->evT3 : P->evT1))
-            return rc;
+        if (int rc = launchCells(P, P->cellListBoundary, P->nBoundaryCells)) return rc;
     }
     if (P->hasProcessor) {
         CUDA_TRY(cudaEventRecord(P->evC, c.st));

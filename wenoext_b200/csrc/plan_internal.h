@@ -90,9 +90,8 @@ struct wenoext_plan {
     // statistics
     int lastLaunches = 0;
     bool timing = false;
-    cudaEvent_t evT0 = nullptr, evT1 = nullptr, evT2 = nullptr, evT3 = nullptr;
-    bool timedTwo = false;
-    double lastKernelMs = -1.0;
+    std::vector<cudaEvent_t> timeEvents;  // (start, stop) pairs of timed cell-kernel launches
+    size_t timeUsed = 0;
     wenoext_plan_info info{};
     // launch geometry overrides (tuning): 0 = auto
     int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0;
