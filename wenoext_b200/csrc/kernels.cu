@@ -11,9 +11,13 @@
 //
 // Structure: persistent CTAs (one per SM). One producer warp streams whole cell
 // records (device_plan.h) into a shared-memory ring with 1-D TMA bulk copies
-// (cp.async.bulk ... mbarrier::complete_tx, SASS UBLKCP); consumer warps take
-// one cell each. The kernel is HBM-bound: tensor cores are deliberately unused
-// (independent 9x21 GEMVs, no operand reuse).
+// (cp.async.bulk ... mbarrier::complete_tx, SASS UBLKCP): the small meta part
+// and the matrix part complete on separate mbarriers, so the gather of stencil
+// values overlaps the arrival of the matrices. A group of G warps takes one cell:
+// every lane owns one row (stencil, coefficient) of the stacked matrices, reads
+// it conflict-free from the interleaved record and keeps CB component
+// accumulators in registers. The kernel is HBM-bound: tensor cores are
+// deliberately unused (independent 9x21 GEMVs, no operand reuse).
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -23,23 +27,23 @@ namespace wenoext {
 
 namespace {
 
-constexpr int TILE = 32;  // consecutive cells handed to one CTA at a time
+constexpr int TILE = 32;          // consecutive cells handed to one CTA at a time
+constexpr int MAX_THREADS = 544;  // 16 consumer warps + producer
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
 }
-__device__ __forceinline__ void mbarInit(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count));
+__device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void mbarArriveExpectTx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)),
-                 "r"(bytes)
+__device__ __forceinline__ void mbarArriveExpectTx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                  : "memory");
 }
-__device__ __forceinline__ void mbarArrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smemAddr(bar)) : "memory");
+__device__ __forceinline__ void mbarArrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -48,7 +52,7 @@ __device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
         "@p bra DONE_%=;\n"
         "bra WAIT_%=;\n"
         "DONE_%=:\n"
-        "}\n" ::"r"(smemAddr(bar)),
+        "}\n" ::"r"(bar),
         "r"(parity)
         : "memory");
 }
@@ -58,13 +62,42 @@ __device__ __forceinline__ uint64_t evictFirstPolicy() {
     return pol;
 }
 // 1-D TMA bulk copy global -> shared, completion on an mbarrier
-__device__ __forceinline__ void tmaLoad1D(void* dst, const void* src, uint32_t bytes,
-                                          uint64_t* bar, uint64_t policy) {
+__device__ __forceinline__ void tmaLoad1D(uint32_t dst, const void* src, uint32_t bytes,
+                                          uint32_t bar, uint64_t policy) {
     asm volatile(
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
-        "[%0], [%1], %2, [%3], %4;" ::"r"(smemAddr(dst)),
-        "l"(src), "r"(bytes), "r"(smemAddr(bar)), "l"(policy)
+        "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar), "l"(policy)
         : "memory");
+}
+// explicit shared-space accesses (32-bit addresses; guarantees LDS/STS)
+__device__ __forceinline__ double lds64(uint32_t a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double2 lds128(uint32_t a) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ int32_t lds32(uint32_t a) {
+    int32_t v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts64(uint32_t a, double v) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t a, double x, double y) {
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(x), "d"(y) : "memory");
+}
+// barrier of one cell group (G warps); G == 1 is a warp barrier
+__device__ __forceinline__ void groupSync(int G, int grp) {
+    if (G == 1)
+        __syncwarp();
+    else
+        asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(G * 32) : "memory");
 }
 
 __device__ __forceinline__ double intPowD(double base, uint32_t e) {
@@ -73,64 +106,99 @@ __device__ __forceinline__ double intPowD(double base, uint32_t e) {
     return t;
 }
 
-struct WarpScratch {
-    double* bsm;    // [max(maxTotN, maxSt*K)][CB]  b values, later IS products
-    double* coef;   // [maxSt*K][CB]
-    double* gam;    // [maxSt][CB]
-    double* W;      // [K][CB] weighted coefficients
-    double* poly;   // [maxFc][CB]
-    double* theta;  // [4]
-    int32_t* stN;   // [maxSt]
-    int32_t* stA;   // [maxSt] offset (doubles) of A_s in the record
-    int32_t* stB;   // [maxSt] offset (entries) of b_s
-};
-
 __host__ __device__ inline size_t alignUp(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-__host__ __device__ inline size_t warpScratchBytes(int K, int CB, int maxTotN, int maxSt,
-                                                   int maxFc) {
-    size_t nb = (size_t)(maxTotN > maxSt * K ? maxTotN : maxSt * K);
-    size_t d = nb * CB + (size_t)maxSt * K * CB + (size_t)maxSt * CB + (size_t)K * CB +
-               (size_t)maxFc * CB + 4;
-    size_t i = 3 * (size_t)maxSt;
-    return alignUp(d * 8 + i * 4, 16);
-}
+// Per-group scratch: component vectors are stored as a (c0,c1) double2 plane plus
+// a c2 plane so that one LDS.128 + one LDS.64 fetch three components.
+template <int CB>
+struct Vec {
+    uint32_t p01, p2;  // shared addresses of the planes
+    __device__ __forceinline__ void load(int i, double (&v)[CB]) const {
+        if constexpr (CB == 1) {
+            v[0] = lds64(p01 + i * 8);
+        } else {
+            double2 t = lds128(p01 + i * 16);
+            v[0] = t.x;
+            v[1] = t.y;
+            if constexpr (CB == 3) v[2] = lds64(p2 + i * 8);
+        }
+    }
+    __device__ __forceinline__ void store(int i, const double (&v)[CB]) const {
+        if constexpr (CB == 1) {
+            sts64(p01 + i * 8, v[0]);
+        } else {
+            sts128(p01 + i * 16, v[0], v[1]);
+            if constexpr (CB == 3) sts64(p2 + i * 8, v[2]);
+        }
+    }
+    __device__ __forceinline__ uint32_t addr(int i, int c) const {
+        if constexpr (CB == 1) return p01 + i * 8;
+        return c < 2 ? p01 + i * 16 + c * 8 : p2 + i * 8;
+    }
+};
 
 template <int CB>
 __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB]) {
     if constexpr (CB == 1) {
         v[0] = __ldg(p);
-    } else if constexpr (CB == 2) {
-        double2 t = __ldg(reinterpret_cast<const double2*>(p));
-        v[0] = t.x;
-        v[1] = t.y;
     } else {
         double2 t = __ldg(reinterpret_cast<const double2*>(p));
         v[0] = t.x;
         v[1] = t.y;
-        v[2] = __ldg(p + 2);
+        if constexpr (CB == 3) v[2] = __ldg(p + 2);
     }
 }
-
 template <int CB>
-__global__ void __launch_bounds__(1024, 1) weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
+__device__ __forceinline__ double pick(const double (&v)[CB], int c) {
+    double r = v[0];
+    if constexpr (CB > 1) r = c == 1 ? v[1] : r;
+    if constexpr (CB > 2) r = c == 2 ? v[2] : r;
+    return r;
+}
+
+struct GroupScratch {
+    uint32_t b01, b2, c01, c2, gam, W, poly, theta;
+};
+__host__ __device__ inline size_t scratchLayout(int K, int CB, int maxTotN, int maxRows, int maxSt,
+                                                int maxFc, GroupScratch* g, uint32_t base) {
+    const int nb = maxTotN > maxRows ? maxTotN : maxRows;
+    size_t o = 0;
+    const size_t w01 = CB == 1 ? 8 : 16;
+    if (g) g->b01 = base + (uint32_t)o;
+    o += alignUp((size_t)nb * w01, 16);
+    if (g) g->b2 = base + (uint32_t)o;
+    if (CB == 3) o += alignUp((size_t)nb * 8, 16);
+    if (g) g->c01 = base + (uint32_t)o;
+    o += alignUp((size_t)maxRows * w01, 16);
+    if (g) g->c2 = base + (uint32_t)o;
+    if (CB == 3) o += alignUp((size_t)maxRows * 8, 16);
+    if (g) g->gam = base + (uint32_t)o;
+    o += alignUp((size_t)maxSt * CB * 8, 16);
+    if (g) g->W = base + (uint32_t)o;
+    o += alignUp((size_t)K * CB * 8, 16);
+    if (g) g->poly = base + (uint32_t)o;
+    o += alignUp((size_t)maxFc * CB * 8, 16);
+    if (g) g->theta = base + (uint32_t)o;
+    o += 32;
+    return o;
+}
+
+template <int KT, int CB>
+__global__ void __launch_bounds__(MAX_THREADS, 1)
+    weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const int K = a.K;
-    const int NW = a.nConsumerWarps;
+    const int K = KT ? KT : a.K;
+    const int G = a.G, L = G * 32, NG = a.nGroups;
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const int nSlots = a.nSlots;
 
-    unsigned char* ring = smem;
-    uint64_t* fullBar = reinterpret_cast<uint64_t*>(smem + (size_t)a.nSlots * a.slotBytes);
-    uint64_t* emptyBar = fullBar + a.nSlots;
-    unsigned char* scratchBase = reinterpret_cast<unsigned char*>(emptyBar + a.nSlots);
-    scratchBase = reinterpret_cast<unsigned char*>(alignUp((size_t)scratchBase, 16));
+    const uint32_t ring = smemAddr(smem);
+    const uint32_t bars = ring + (uint32_t)nSlots * a.slotBytes;  // per slot: fullMeta, fullA, empty
+    const uint32_t scratch0 = (bars + (uint32_t)nSlots * 24 + 15u) & ~15u;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < a.nSlots; ++s) {
-            mbarInit(&fullBar[s], 1);
-            mbarInit(&emptyBar[s], 1);
-        }
+        for (int s = 0; s < 3 * nSlots; ++s) mbarInit(bars + s * 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -143,181 +211,213 @@ __global__ void __launch_bounds__(1024, 1) weno_cell_kernel(const __grid_constan
         const int lastTile = blockIdx.x + (nMy - 1) * gridDim.x;
         nItems = nMy * TILE - (lastTile == nTiles - 1 ? nTiles * TILE - a.nWork : 0);
     }
-    auto itemToWork = [&](int n) {
-        return ((int)blockIdx.x + (n / TILE) * (int)gridDim.x) * TILE + (n % TILE);
+    auto itemToCell = [&](int n) {
+        const int w = ((int)blockIdx.x + (n / TILE) * (int)gridDim.x) * TILE + (n % TILE);
+        return a.cellList ? __ldg(a.cellList + w) : w;
     };
 
-    if (warp == NW) {
-        // ===== producer: one lane issues the bulk copies =====
-        if (lane == 0) {
-            const uint64_t pol = evictFirstPolicy();
-            for (int n = 0; n < nItems; ++n) {
-                const int slot = n % a.nSlots;
-                const int round = n / a.nSlots;
-                if (round > 0) mbarWait(&emptyBar[slot], (round - 1) & 1);
-                const int w = itemToWork(n);
-                const int cell = a.cellList ? a.cellList[w] : w;
-                const int64_t off = a.recOff[cell];
-                const uint32_t bytes = (uint32_t)(a.recOff[cell + 1] - off);
-                mbarArriveExpectTx(&fullBar[slot], bytes);
-                tmaLoad1D(ring + (size_t)slot * a.slotBytes, a.records + off, bytes,
-                          &fullBar[slot], pol);
+    if (warp == NG * G) {
+        // ===== producer warp: all lanes prefetch the record descriptors of the next
+        // 32 items, lane 0 waits for free slots and issues the bulk copies =====
+        const uint64_t pol = evictFirstPolicy();
+        auto fetch = [&](int n) {
+            int4 r = make_int4(0, 0, 0, 0);
+            if (n < nItems) r = __ldg(reinterpret_cast<const int4*>(a.recInfo + itemToCell(n)));
+            return r;
+        };
+        int4 cur = fetch(lane);
+        int slot = 0, round = 0;
+        for (int n0 = 0; n0 < nItems; n0 += 32) {
+            const int4 nxt = fetch(n0 + 32 + lane);
+            const int cnt = min(32, nItems - n0);
+            for (int i = 0; i < cnt; ++i) {
+                const uint32_t offLo = (uint32_t)__shfl_sync(0xffffffffu, cur.x, i);
+                const uint32_t offHi = (uint32_t)__shfl_sync(0xffffffffu, cur.y, i);
+                const int tot = __shfl_sync(0xffffffffu, cur.z, i);
+                const int meta = __shfl_sync(0xffffffffu, cur.w, i);
+                if (lane == 0) {
+                    const uint64_t off = ((uint64_t)offHi << 32) | offLo;
+                    if (round > 0) mbarWait(bars + (slot * 3 + 2) * 8, (round - 1) & 1);
+                    const uint32_t dst = ring + (uint32_t)slot * a.slotBytes;
+                    const uint32_t bMeta = bars + (slot * 3) * 8, bA = bMeta + 8;
+                    mbarArriveExpectTx(bMeta, (uint32_t)meta);
+                    tmaLoad1D(dst, a.records + off, (uint32_t)meta, bMeta, pol);
+                    const int aB = tot - meta;
+                    if (aB > 0) {
+                        mbarArriveExpectTx(bA, (uint32_t)aB);
+                        tmaLoad1D(dst + meta, a.records + off + meta, (uint32_t)aB, bA, pol);
+                    } else {
+                        mbarArrive(bA);
+                    }
+                }
+                if (++slot == nSlots) {
+                    slot = 0;
+                    ++round;
+                }
             }
+            cur = nxt;
         }
         return;
     }
-    if (warp > NW) return;
+    if (warp > NG * G) return;
 
-    // ===== consumers: one warp per cell =====
-    WarpScratch ws;
+    // ===== consumers: a group of G warps per cell, one lane per matrix row =====
+    const int grp = warp / G;
+    const int gl = (warp - grp * G) * 32 + lane;
+    GroupScratch gs;
     {
-        const size_t per = warpScratchBytes(K, CB, a.maxTotN, a.maxSt, a.maxFc);
-        unsigned char* p = scratchBase + (size_t)warp * per;
-        const size_t nb = (size_t)(a.maxTotN > a.maxSt * K ? a.maxTotN : a.maxSt * K);
-        ws.bsm = reinterpret_cast<double*>(p);
-        ws.coef = ws.bsm + nb * CB;
-        ws.gam = ws.coef + (size_t)a.maxSt * K * CB;
-        ws.W = ws.gam + (size_t)a.maxSt * CB;
-        ws.poly = ws.W + (size_t)K * CB;
-        ws.theta = ws.poly + (size_t)a.maxFc * CB;
-        ws.stN = reinterpret_cast<int32_t*>(ws.theta + 4);
-        ws.stA = ws.stN + a.maxSt;
-        ws.stB = ws.stA + a.maxSt;
+        const size_t per = scratchLayout(K, CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc, nullptr, 0);
+        scratchLayout(K, CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc, &gs,
+                      scratch0 + (uint32_t)(grp * per));
     }
+    const Vec<CB> bv{gs.b01, gs.b2};  // b values, later the IS products t
+    const Vec<CB> cv{gs.c01, gs.c2};  // coefficients per (stencil, k)
     const int nBndBase = a.nInternalFaces;
+    const bool fit01 = a.scheme == 1;
+    const bool fitBounded = a.scheme == 0 && a.bounded;
 
-    for (int n = warp; n < nItems; n += NW) {
-        const int slot = n % a.nSlots;
-        const int round = n / a.nSlots;
-        const int w = itemToWork(n);
-        const int cell = a.cellList ? a.cellList[w] : w;
-        // centre value (broadcast load) while the record is in flight
+    int slot = grp % nSlots, round = grp / nSlots;
+    for (int n = grp; n < nItems; n += NG) {
+        const int cell = itemToCell(n);
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen);
 
-        mbarWait(&fullBar[slot], round & 1);
-        const unsigned char* rec = ring + (size_t)slot * a.slotBytes;
-        const RecHeader hd = *reinterpret_cast<const RecHeader*>(rec);
-        const int nSt = hd.nSt, nFc = hd.nFc, totN = hd.totN;
-        const double* Amat = reinterpret_cast<const double*>(rec + sizeof(RecHeader));
-        // A size is only known after the prefix sum below; the int block is found via totN
-        const double* Bm = Amat + (size_t)K * totN;
-        const double* faceD = Bm + K * K;
-        const double* quirk = faceD + (size_t)nFc * (K + 1);
-        const int32_t* Ns = reinterpret_cast<const int32_t*>(quirk + K);
-        const int32_t* idx = Ns + nSt;
-        const int32_t* faceI = idx + totN;
+        const uint32_t rec = ring + (uint32_t)slot * a.slotBytes;
+        mbarWait(bars + (slot * 3) * 8, round & 1);
+        const int nSt = lds32(rec), nFc = lds32(rec + 4), totN = lds32(rec + 8);
+        const RecLayout lay = recLayout(K, L, nSt, totN, nFc);
+        const int nRows = nSt * K;
+        const int nFaceItems = nFc * CB;
 
-        // per-stencil offsets (nSt <= 32 guaranteed by the plan)
-        {
-            int N = lane < nSt ? Ns[lane] : 0;
-            int incl = N;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int t = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= d) incl += t;
-            }
-            if (lane < nSt) {
-                ws.stN[lane] = N;
-                ws.stB[lane] = incl - N;
-                ws.stA[lane] = (incl - N) * K;
-            }
+        // face data of this lane's first (face, component) item: issue the global
+        // loads now, they are consumed at the very end
+        int pfFace = 0, pfOther = -1, pfKind = 0;
+        double pfFlux = 0.0, pfPsiN = 0.0;
+        if (gl < nFaceItems) {
+            const int f = gl / CB, c = gl - f * CB;
+            const uint32_t fa = rec + lay.oFaceI + f * 12;
+            pfFace = lds32(fa);
+            pfOther = lds32(fa + 4);
+            pfKind = lds32(fa + 8);
+            pfFlux = __ldg(a.flux + pfFace);
+            if (fitBounded && (pfKind >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
+                pfPsiN = __ldg(a.vals + (size_t)pfOther * a.VS + c);
         }
+
         // gather: b[e][c] = psi(id_e)[c] - psi(cell)[c]      (WENOCoeff.C:138-156)
-        for (int e = lane; e < totN; e += 32) {
+        for (int e = gl; e < totN; e += L) {
+            const int id = lds32(rec + lay.oIdx + e * 4);
             double v[CB];
-            loadVals<CB>(a.vals + (size_t)idx[e] * a.VS, v);
+            loadVals<CB>(a.vals + (size_t)id * a.VS, v);
 #pragma unroll
-            for (int c = 0; c < CB; ++c) ws.bsm[e * CB + c] = v[c] - cen[c];
+            for (int c = 0; c < CB; ++c) v[c] -= cen[c];
+            bv.store(e, v);
         }
-        __syncwarp();
+        groupSync(G, grp);
+        mbarWait(bars + (slot * 3 + 1) * 8, round & 1);
+
         // phase 1: coeffs[s][k][c] = sum_j A_s[k][j] * b_s[j][c]   (WENOCoeff.C:159)
-        const int nPairs = nSt * K;
-        for (int p = lane; p < nPairs; p += 32) {
-            const int s = p / K, k = p - s * K;
-            const int N = ws.stN[s];
-            const double* Ar = Amat + ws.stA[s] + (size_t)k * N;
-            const double* bp = ws.bsm + (size_t)ws.stB[s] * CB;
-            double acc[CB];
+        for (int r0 = 0; r0 < nRows; r0 += L) {
+            const int p = r0 + gl;
+            if (p < nRows) {
+                const int s = p / K;
+                const int N = lds32(rec + lay.oN + s * 4);
+                const int bo = lds32(rec + lay.oStOff + s * 4);
+                const int rbase = lds32(rec + lay.oRnd + (r0 / L) * 8 + 4);
+                const int R = min(L, nRows - r0);
+                uint32_t Ap = rec + lay.metaBytes + (uint32_t)(rbase + gl) * 8;
+                const uint32_t stride = (uint32_t)R * 8;
+                double acc[CB];
 #pragma unroll
-            for (int c = 0; c < CB; ++c) acc[c] = 0.0;
-            for (int j = 0; j < N; ++j) {
-                const double av = Ar[j];
+                for (int c = 0; c < CB; ++c) acc[c] = 0.0;
+#pragma unroll 7
+                for (int j = 0; j < N; ++j) {
+                    const double av = lds64(Ap);
+                    Ap += stride;
+                    double b[CB];
+                    bv.load(bo + j, b);
 #pragma unroll
-                for (int c = 0; c < CB; ++c) acc[c] = fma(av, bp[j * CB + c], acc[c]);
+                    for (int c = 0; c < CB; ++c) acc[c] = fma(av, b[c], acc[c]);
+                }
+                cv.store(p, acc);
             }
-#pragma unroll
-            for (int c = 0; c < CB; ++c) ws.coef[p * CB + c] = acc[c];
         }
-        __syncwarp();
+        groupSync(G, grp);
         // phase 2a: t[s][k][c] = c_k * (B c)_k                  (WENOCoeff.C:190-196)
-        for (int p = lane; p < nPairs; p += 32) {
-            const int s = p / K, k = p - s * K;
-            const double* cs = ws.coef + (size_t)s * K * CB;
-            double u[CB];
+        for (int r0 = 0; r0 < nRows; r0 += L) {
+            const int p = r0 + gl;
+            if (p < nRows) {
+                const int s = p / K, k = p - s * K;
+                const uint32_t Bp = rec + lay.oB + (uint32_t)(k * K) * 8;
+                double u[CB];
 #pragma unroll
-            for (int c = 0; c < CB; ++c) u[c] = 0.0;
-            for (int q = 0; q < K; ++q) {
-                const double bv = Bm[k * K + q];
+                for (int c = 0; c < CB; ++c) u[c] = 0.0;
+#pragma unroll(KT ? KT : 4)
+                for (int q = 0; q < K; ++q) {
+                    const double bq = lds64(Bp + q * 8);
+                    double cq[CB];
+                    cv.load(s * K + q, cq);
 #pragma unroll
-                for (int c = 0; c < CB; ++c) u[c] = fma(bv, cs[q * CB + c], u[c]);
+                    for (int c = 0; c < CB; ++c) u[c] = fma(bq, cq[c], u[c]);
+                }
+                double own[CB];
+                cv.load(p, own);
+#pragma unroll
+                for (int c = 0; c < CB; ++c) u[c] *= own[c];
+                bv.store(p, u);
             }
-#pragma unroll
-            for (int c = 0; c < CB; ++c) ws.bsm[p * CB + c] = ws.coef[p * CB + c] * u[c];
         }
-        __syncwarp();
+        groupSync(G, grp);
         // phase 2b: IS and gamma per (stencil, component)      (WENOCoeff.C:196-205)
-        for (int i = lane; i < nSt * CB; i += 32) {
+        for (int i = gl; i < nSt * CB; i += L) {
             const int s = i / CB, c = i - s * CB;
             double IS = 0.0;
-            for (int k = 0; k < K; ++k) IS += ws.bsm[(s * K + k) * CB + c];
-            ws.gam[i] = (s == 0 ? a.dm : 1.0) / intPowD(a.eps + IS, a.pExp);
+            for (int k = 0; k < K; ++k) IS += lds64(bv.addr(s * K + k, c));
+            sts64(gs.gam + i * 8, (s == 0 ? a.dm : 1.0) / intPowD(a.eps + IS, a.pExp));
         }
-        __syncwarp();
+        groupSync(G, grp);
         // phase 2c: weighted combination                        (WENOCoeff.C:207-220)
-        for (int i = lane; i < K * CB; i += 32) {
+        for (int i = gl; i < K * CB; i += L) {
             const int k = i / CB, c = i - k * CB;
-            double acc = 0.0, gs = 0.0;
+            double acc = 0.0, gsum = 0.0;
             for (int s = 0; s < nSt; ++s) {
-                const double g = ws.gam[s * CB + c];
-                gs += g;
-                acc = fma(g, ws.coef[(s * K + k) * CB + c], acc);
+                const double g = lds64(gs.gam + (s * CB + c) * 8);
+                gsum += g;
+                acc = fma(g, lds64(cv.addr(s * K + k, c)), acc);
             }
-            ws.W[i] = nSt > 0 ? acc / gs : 0.0;  // Cell::empty -> zero (WENOCoeff.C:333)
+            sts64(gs.W + i * 8, nSt > 0 ? acc / gsum : 0.0);  // Cell::empty -> zero (WENOCoeff.C:333)
         }
-        __syncwarp();
-        // phase 3: faces
-        const bool fit01 = a.scheme == 1;
+        groupSync(G, grp);
+        // phase 3: faces. Items (face, component) of the cell, one per lane.
         if (fit01) {
             // own polynomial at every internal face (WENOUpwindFit01.C:80-136)
-            for (int i = lane; i < nFc * CB; i += 32) {
+            for (int i = gl; i < nFaceItems; i += L) {
                 const int f = i / CB, c = i - f * CB;
-                const int kind = faceI[f * 3 + 2];
-                double val = 0.0;
+                const uint32_t fa = rec + lay.oFaceI + f * 12;
+                const int kind = lds32(fa + 8);
+                double val = pick<CB>(cen, c);
                 if ((kind >> FACE_TYPE_SHIFT) == FACE_INTERNAL) {
-                    const double* fd = faceD + (size_t)f * (K + 1);
-                    const double fl = __ldg(a.flux + faceI[f * 3]);
+                    const uint32_t fd = rec + lay.oFaceD + (uint32_t)(f * (K + 1)) * 8;
+                    const double fl = i == gl ? pfFlux : __ldg(a.flux + lds32(fa));
                     const bool nei = kind & FACE_SIDE_NEI;
-                    const double* basis = (nei && !(fl < 0) && a.bugCompat) ? quirk : fd;
+                    const uint32_t basis =
+                        (nei && !(fl < 0) && a.bugCompat) ? rec + lay.oQuirk : fd;
                     double s = 0.0;
-                    for (int k = 0; k < K; ++k) s = fma(ws.W[k * CB + c], basis[k], s);
-                    val = cen[c] + s / fd[K];
-                } else {
-                    val = cen[c];
+                    for (int k = 0; k < K; ++k)
+                        s = fma(lds64(gs.W + (k * CB + c) * 8), lds64(basis + k * 8), s);
+                    val += s / lds64(fd + K * 8);
                 }
-                ws.poly[i] = val;
+                sts64(gs.poly + i * 8, val);
             }
-            __syncwarp();
-            if (lane < CB) {
-                const int c = lane;
-                double psi = 0.0;
-#pragma unroll
-                for (int cc = 0; cc < CB; ++cc)
-                    if (cc == c) psi = cen[cc];
+            groupSync(G, grp);
+            if (gl < CB) {
+                const int c = gl;
+                const double psi = pick<CB>(cen, c);
                 double mx = psi, mn = psi;
                 for (int f = 0; f < nFc; ++f) {
-                    if ((faceI[f * 3 + 2] >> FACE_TYPE_SHIFT) != FACE_INTERNAL) continue;
-                    const double t = ws.poly[f * CB + c];
+                    if ((lds32(rec + lay.oFaceI + f * 12 + 8) >> FACE_TYPE_SHIFT) != FACE_INTERNAL)
+                        continue;
+                    const double t = lds64(gs.poly + (f * CB + c) * 8);
                     if (t > mx)
                         mx = t;
                     else if (t < mn)
@@ -325,40 +425,45 @@ __global__ void __launch_bounds__(1024, 1) weno_cell_kernel(const __grid_constan
                 }
                 const double argMax = fabs(mx - psi) < 1e-9 ? 1.0 : fabs((1.0 - psi) / (mx - psi));
                 const double argMin = fabs(mn - psi) < 1e-9 ? 1.0 : fabs((0.0 - psi) / (mn - psi));
-                ws.theta[c] = fmin(fmin(argMax, argMin), 1.0);
+                sts64(gs.theta + c * 8, fmin(fmin(argMax, argMin), 1.0));
             }
-            __syncwarp();
+            groupSync(G, grp);
         }
-        for (int i = lane; i < nFc * CB; i += 32) {
+        for (int i = gl; i < nFaceItems; i += L) {
             const int f = i / CB, c = i - f * CB;
-            const int faceId = faceI[f * 3];
-            const int other = faceI[f * 3 + 1];
-            const int kind = faceI[f * 3 + 2];
+            int faceId = pfFace, other = pfOther, kind = pfKind;
+            double fl = pfFlux;
+            if (i != gl) {
+                const uint32_t fa = rec + lay.oFaceI + f * 12;
+                faceId = lds32(fa);
+                other = lds32(fa + 4);
+                kind = lds32(fa + 8);
+                fl = __ldg(a.flux + faceId);
+            }
             const int type = kind >> FACE_TYPE_SHIFT;
             const bool nei = kind & FACE_SIDE_NEI;
-            const double fl = __ldg(a.flux + faceId);
-            double psi = 0.0;
-#pragma unroll
-            for (int cc = 0; cc < CB; ++cc)
-                if (cc == c) psi = cen[cc];
+            const double psi = pick<CB>(cen, c);
             // who writes: owner unless flux<0 (flux==0 -> owner writes zero), WENOUpwindFit.C:258-281
             const bool up = nei ? (fl < 0) : (fl > 0);
             const bool writer = type == FACE_INTERNAL ? (nei ? (fl < 0) : !(fl < 0)) : (fl > 0);
+            const double th = fit01 ? lds64(gs.theta + c * 8) : 1.0;
             if (fit01 && type == FACE_PROCESSOR && a.thetaPatch)
-                a.thetaPatch[(size_t)(faceId - nBndBase) * a.nComp + a.c0 + c] = ws.theta[c];
+                a.thetaPatch[(size_t)(faceId - nBndBase) * a.nComp + a.c0 + c] = th;
             if (!writer) continue;
             double out = 0.0;
             if (up) {
-                const double* fd = faceD + (size_t)f * (K + 1);
+                const uint32_t fd = rec + lay.oFaceD + (uint32_t)(f * (K + 1)) * 8;
                 double s = 0.0;
-                for (int k = 0; k < K; ++k) s = fma(ws.W[k * CB + c], fd[k], s);
-                out = s / fd[K];
+                for (int k = 0; k < K; ++k)
+                    s = fma(lds64(gs.W + (k * CB + c) * 8), lds64(fd + k * 8), s);
+                out = s / lds64(fd + K * 8);
                 if (type == FACE_INTERNAL) {
                     if (fit01) {
-                        out = ws.theta[c] * out;  // WENOUpwindFit01.C:167-181
+                        out = th * out;  // WENOUpwindFit01.C:167-181
                     } else if (a.bounded) {
                         // WENOUpwindFit.C:81-108, :172-179
-                        const double psiN = __ldg(a.vals + (size_t)other * a.VS + c);
+                        const double psiN =
+                            i == gl ? pfPsiN : __ldg(a.vals + (size_t)other * a.VS + c);
                         const double dpsi = fabs(psi - psiN);
                         if (fabs(out) > dpsi) out = fmin(dpsi / fabs(out), 1.0) * out;
                     }
@@ -368,8 +473,13 @@ __global__ void __launch_bounds__(1024, 1) weno_cell_kernel(const __grid_constan
             if (a.faceValue && type == FACE_INTERNAL)
                 a.faceValue[(size_t)faceId * a.nComp + a.c0 + c] = psi + out;
         }
-        __syncwarp();
-        if (lane == 0) mbarArrive(&emptyBar[slot]);
+        groupSync(G, grp);
+        if (gl == 0) mbarArrive(bars + (slot * 3 + 2) * 8);
+        slot += NG;
+        while (slot >= nSlots) {
+            slot -= nSlots;
+            ++round;
+        }
     }
 }
 
@@ -440,32 +550,51 @@ __global__ void patch_kernel(const PatchKernelArgs a) {
 
 }  // namespace
 
-size_t cellKernelSmemBytes(int K, int CB, int nSlots, int slotBytes, int maxTotN, int maxSt,
-                           int maxFc, int nConsumerWarps) {
-    size_t s = (size_t)nSlots * slotBytes + (size_t)nSlots * 16 + 16;
-    s += (size_t)nConsumerWarps * warpScratchBytes(K, CB, maxTotN, maxSt, maxFc);
+size_t groupScratchBytes(int K, int CB, int maxTotN, int maxRows, int maxSt, int maxFc) {
+    return scratchLayout(K, CB, maxTotN, maxRows, maxSt, maxFc, nullptr, 0);
+}
+
+size_t cellKernelSmemBytes(const CellKernelArgs& a, int CB) {
+    size_t s = (size_t)a.nSlots * a.slotBytes + (size_t)a.nSlots * 24 + 16;
+    s += (size_t)a.nGroups * groupScratchBytes(a.K, CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc);
     return s;
 }
 
-void launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
-                      cudaStream_t st) {
-    const int threads = (a.nConsumerWarps + 1) * 32;
+namespace {
+template <int KT, int CB>
+int launchT(const CellKernelArgs& a, int gridBlocks, size_t smemBytes, cudaStream_t st) {
+    static size_t configured = 0;  // per instantiation
+    if (smemBytes > configured) {
+        if (cudaFuncSetAttribute(weno_cell_kernel<KT, CB>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smemBytes) != cudaSuccess)
+            return 1;
+        configured = smemBytes;
+    }
+    const int threads = (a.nGroups * a.G + 1) * 32;
+    weno_cell_kernel<KT, CB><<<gridBlocks, threads, smemBytes, st>>>(a);
+    return 0;
+}
+template <int KT>
+int launchK(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes, cudaStream_t st) {
     switch (CB) {
-        case 1:
-            cudaFuncSetAttribute(weno_cell_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smemBytes);
-            weno_cell_kernel<1><<<gridBlocks, threads, smemBytes, st>>>(a);
-            break;
-        case 2:
-            cudaFuncSetAttribute(weno_cell_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smemBytes);
-            weno_cell_kernel<2><<<gridBlocks, threads, smemBytes, st>>>(a);
-            break;
-        default:
-            cudaFuncSetAttribute(weno_cell_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smemBytes);
-            weno_cell_kernel<3><<<gridBlocks, threads, smemBytes, st>>>(a);
-            break;
+        case 1: return launchT<KT, 1>(a, gridBlocks, smemBytes, st);
+        case 2: return launchT<KT, 2>(a, gridBlocks, smemBytes, st);
+        default: return launchT<KT, 3>(a, gridBlocks, smemBytes, st);
+    }
+}
+}  // namespace
+
+// K is a template parameter for the common polynomial spaces (3-D order 2: 9,
+// 3-D order 3: 19, 2-D order 2: 5); anything else runs the runtime-K instance.
+int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
+                     cudaStream_t st) {
+    if ((a.nGroups * a.G + 1) * 32 > MAX_THREADS) return 1;
+    switch (a.K) {
+        case 9: return launchK<9>(a, CB, gridBlocks, smemBytes, st);
+        case 19: return launchK<19>(a, CB, gridBlocks, smemBytes, st);
+        case 5: return launchK<5>(a, CB, gridBlocks, smemBytes, st);
+        default: return launchK<0>(a, CB, gridBlocks, smemBytes, st);
     }
 }
 

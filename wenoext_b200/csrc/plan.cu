@@ -41,8 +41,8 @@ int upload(T** dptr, const T* h, size_t n) {
 }
 
 struct ExpandArgs {
-    int32_t nCells, nFaces, nInternalFaces, K, cube;
-    const int64_t* recOff;
+    int32_t nCells, nFaces, nInternalFaces, K, cube, L;
+    const RecInfo* recInfo;
     const int32_t *cellNSt, *cellTotN, *cellNFc;
     const int64_t *cellStencilStart, *stencilEntryStart;
     const int32_t *stencilsID, *cellToProcMap, *stencilMatrix;
@@ -60,32 +60,64 @@ struct ExpandArgs {
 };
 
 // One warp per cell: copies the de-duplicated matrices and the per-cell / per-face
-// setup data into the cell's record (bitwise copies, so parity is unaffected).
+// setup data into the cell's record (bitwise copies, so parity is unaffected). The
+// record memory is zero-filled beforehand (padding of the interleaved rounds).
 __global__ void expand_records_kernel(const ExpandArgs a) {
     const int cell = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const int lane = threadIdx.x & 31;
     if (cell >= a.nCells) return;
-    const int K = a.K;
-    unsigned char* rec = a.records + a.recOff[cell];
+    const int K = a.K, L = a.L;
+    unsigned char* rec = a.records + a.recInfo[cell].off;
     const int nSt = a.cellNSt[cell], totN = a.cellTotN[cell], nFc = a.cellNFc[cell];
-    double* Amat = reinterpret_cast<double*>(rec + sizeof(RecHeader));
-    double* Bm = Amat + (size_t)K * totN;
-    double* faceD = Bm + K * K;
-    double* quirk = faceD + (size_t)nFc * (K + 1);
-    int32_t* Ns = reinterpret_cast<int32_t*>(quirk + K);
-    int32_t* idx = Ns + nSt;
-    int32_t* faceI = idx + totN;
+    const RecLayout lay = recLayout(K, L, nSt, totN, nFc);
+    int32_t* Ns = reinterpret_cast<int32_t*>(rec + lay.oN);
+    int32_t* stOff = reinterpret_cast<int32_t*>(rec + lay.oStOff);
+    int32_t* rnd = reinterpret_cast<int32_t*>(rec + lay.oRnd);
+    int32_t* idx = reinterpret_cast<int32_t*>(rec + lay.oIdx);
+    int32_t* faceI = reinterpret_cast<int32_t*>(rec + lay.oFaceI);
+    double* Bm = reinterpret_cast<double*>(rec + lay.oB);
+    double* faceD = reinterpret_cast<double*>(rec + lay.oFaceD);
+    double* quirk = reinterpret_cast<double*>(rec + lay.oQuirk);
+    double* A2 = reinterpret_cast<double*>(rec + lay.metaBytes);
+    const int nRows = nSt * K;
+    // lane 0: stencil sizes, prefix, and the per-round interleave geometry
+    if (lane == 0 && nSt > 0) {
+        int live = 0, eOff = 0;
+        for (int64_t s = a.cellStencilStart[cell]; s < a.cellStencilStart[cell + 1]; ++s) {
+            const int m = a.stencilMatrix[s];
+            if (m < 0) continue;
+            Ns[live] = a.matrixCols[m];
+            stOff[live] = eOff;
+            eOff += a.matrixCols[m];
+            live++;
+        }
+        int base = 0;
+        for (int r = 0; r * L < nRows; ++r) {
+            const int p0 = r * L, p1 = min(nRows, p0 + L);
+            int jmax = 0;
+            for (int s = p0 / K; s <= (p1 - 1) / K; ++s) jmax = max(jmax, Ns[s]);
+            rnd[2 * r] = jmax;
+            rnd[2 * r + 1] = base;
+            base += jmax * (p1 - p0);
+        }
+    }
+    __syncwarp();
     bool halo = false;
     if (nSt > 0) {
-        int live = 0, eOff = 0;
+        int live = 0;
         for (int64_t s = a.cellStencilStart[cell]; s < a.cellStencilStart[cell + 1]; ++s) {
             const int m = a.stencilMatrix[s];
             if (m < 0) continue;
             const int N = a.matrixCols[m];
             const double* src = a.matrixData + a.matrixStart[m];
-            double* dst = Amat + (size_t)K * eOff;
-            for (int i = lane; i < K * N; i += 32) dst[i] = src[i];
+            for (int i = lane; i < K * N; i += 32) {
+                const int k = i / N, j = i - k * N;
+                const int p = live * K + k, r = p / L;
+                const int R = min(L, nRows - r * L);
+                A2[rnd[2 * r + 1] + j * R + (p - r * L)] = src[i];
+            }
             const int64_t e0 = a.stencilEntryStart[s];
+            const int eOff = stOff[live];
             for (int j = lane; j < N; j += 32) {
                 const int32_t id = a.stencilsID[e0 + 1 + j];
                 const int32_t pm = a.cellToProcMap ? a.cellToProcMap[e0 + 1 + j] : -1;
@@ -96,9 +128,7 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
                 }
                 idx[eOff + j] = flat;
             }
-            if (lane == 0) Ns[live] = N;
             live++;
-            eOff += N;
         }
     }
     for (int i = lane; i < K * K; i += 32) Bm[i] = a.B[(size_t)cell * K * K + i];
@@ -141,13 +171,6 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
         *reinterpret_cast<RecHeader*>(rec) = h;
         a.cellHasHalo[cell] = halo ? 1 : 0;
     }
-}
-
-size_t recordBytes(int K, int nSt, int totN, int nFc) {
-    size_t b = sizeof(RecHeader);
-    b += ((size_t)K * totN + (size_t)K * K + (size_t)nFc * (K + 1) + K) * 8;
-    b += ((size_t)nSt + totN + (size_t)nFc * 3) * 4;
-    return (b + 15) / 16 * 16;
 }
 
 }  // namespace
@@ -212,6 +235,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     if (const char* e = getenv("WENOEXT_WARPS")) P->cfgWarps = atoi(e);
     if (const char* e = getenv("WENOEXT_SLOTS")) P->cfgSlots = atoi(e);
     if (const char* e = getenv("WENOEXT_GRID")) P->cfgGrid = atoi(e);
+    if (const char* e = getenv("WENOEXT_SMEM_KB")) P->cfgSmemKB = atoi(e);
 
     // coefficient enumeration: n-outer, m, l-inner (WENOUpwindFit.C:304-319)
     const int s1 = d->polOrder + 1;
@@ -266,7 +290,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     // per-cell record sizes
     const int nC = d->nCells;
     std::vector<int32_t> cellNSt(nC), cellTotN(nC), cellNFc(nC);
-    std::vector<int64_t> recOff(nC + 1, 0);
+    std::vector<RecInfo> recInfo(nC);
     int64_t algFixed = 0, flopsPerComp = 0, nLive = 0;
     for (int c = 0; c < nC; ++c) {
         int nSt = 0, totN = 0;
@@ -290,16 +314,9 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
             const int f = d->cellFaces[i];
             if (f < P->nInt || bfType[f - P->nInt] >= 0) nFc++;
         }
-        if (nSt > 32) {
-            setError("more than 32 stencils in a cell is not supported");
-            delete P;
-            return WENOEXT_ERR_INVALID;
-        }
         cellNSt[c] = nSt;
         cellTotN[c] = totN;
         cellNFc[c] = nFc;
-        recOff[c + 1] = recOff[c] + (int64_t)recordBytes(K, nSt, totN, nFc);
-        P->maxRecordBytes = std::max(P->maxRecordBytes, recOff[c + 1] - recOff[c]);
         P->maxTotN = std::max(P->maxTotN, totN);
         P->maxSt = std::max(P->maxSt, nSt);
         P->maxFc = std::max(P->maxFc, nFc);
@@ -310,7 +327,42 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     P->maxSt = std::max(P->maxSt, 1);
     P->maxFc = std::max(P->maxFc, 1);
     P->maxTotN = std::max(P->maxTotN, 1);
-    P->recordBytesTotal = recOff[nC];
+    // warps per cell group: one lane per stacked matrix row (stencil, coefficient)
+    // when that fits a group of at most 8 warps; fixed here because the matrix
+    // part of the records is interleaved for it (device_plan.h)
+    P->G = std::min(8, std::max(1, (P->maxSt * K + 31) / 32));
+    if (const char* e = getenv("WENOEXT_G")) P->G = std::min(8, std::max(1, atoi(e)));
+    const int L = P->G * 32;
+    P->maxRows = P->maxSt * K;
+    {
+        int64_t off = 0;
+        std::vector<int32_t> Ns;
+        for (int c = 0; c < nC; ++c) {
+            Ns.clear();
+            if (cellNSt[c] > 0)
+                for (int64_t s = d->cellStencilStart[c]; s < d->cellStencilStart[c + 1]; ++s) {
+                    const int m = d->stencilMatrix[s];
+                    if (m >= 0 && d->stencilsID[d->stencilEntryStart[s]] != WENOEXT_CELL_DELETED)
+                        Ns.push_back(d->matrixCols[m]);
+                }
+            const int nSt = cellNSt[c], nRows = nSt * K;
+            int64_t aDoubles = 0;
+            for (int p0 = 0; p0 < nRows; p0 += L) {
+                const int p1 = std::min(nRows, p0 + L);
+                int jmax = 0;
+                for (int s = p0 / K; s <= (p1 - 1) / K; ++s) jmax = std::max(jmax, Ns[s]);
+                aDoubles += (int64_t)jmax * (p1 - p0);
+            }
+            const RecLayout lay = recLayout(K, L, nSt, cellTotN[c], cellNFc[c]);
+            const int64_t tot = (lay.metaBytes + aDoubles * 8 + 15) / 16 * 16;
+            recInfo[c].off = off;
+            recInfo[c].totBytes = (int32_t)tot;
+            recInfo[c].metaBytes = lay.metaBytes;
+            off += tot;
+            P->maxRecordBytes = std::max(P->maxRecordBytes, tot);
+        }
+        P->recordBytesTotal = off;
+    }
     const int64_t nWritten = (int64_t)P->nInt + nCoupled;
     algFixed += nWritten * (8 * K + 24);
     flopsPerComp += nWritten * 2 * K;
@@ -329,13 +381,14 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         return rc;
     };
     int rc = 0;
-    int64_t* dRecOff = nullptr;
+    RecInfo* dRecInfo = nullptr;
     int32_t *dNSt, *dTotN, *dNFc, *dSID, *dC2P = nullptr, *dSM, *dMC, *dNei = nullptr, *dCFS, *dCF,
                                   *dEnum, *dBfNbr = nullptr;
     int64_t *dCSS, *dSES, *dMS, *dHaloOff;
     double *dMD, *dB, *dIBT, *dRFA;
     const int64_t nEntries = d->stencilEntryStart[d->nStencils];
-    rc = rc ? rc : upload(&dRecOff, recOff.data(), recOff.size());
+    rc = rc ? rc : upload(&dRecInfo, recInfo.data(), recInfo.size());
+    P->recInfo = dRecInfo;
     rc = rc ? rc : up(&dNSt, cellNSt.data(), (size_t)nC);
     rc = rc ? rc : up(&dTotN, cellTotN.data(), (size_t)nC);
     rc = rc ? rc : up(&dNFc, cellNFc.data(), (size_t)nC);
@@ -365,6 +418,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     uint8_t* dHasHalo = nullptr;
     if (!rc) {
         cudaError_t e = cudaMalloc((void**)&P->records, (size_t)P->recordBytesTotal);
+        if (e == cudaSuccess) e = cudaMemset(P->records, 0, (size_t)P->recordBytesTotal);
         if (e == cudaSuccess) e = cudaMalloc((void**)&dHasHalo, (size_t)nC);
         if (e != cudaSuccess) {
             setError(std::string("cudaMalloc(records): ") + cudaGetErrorString(e));
@@ -372,8 +426,8 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         }
     }
     if (!rc) {
-        P->recOff = dRecOff;
-        ea.recOff = dRecOff;
+        ea.recInfo = dRecInfo;
+        ea.L = L;
         ea.cellNSt = dNSt;
         ea.cellTotN = dTotN;
         ea.cellNFc = dNFc;
@@ -448,9 +502,9 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
 extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (!P) return 0;
     cudaSetDevice(P->device);
-    void* ptrs[] = {P->records, P->recOff, P->cellListInterior, P->cellListBoundary, P->owner,
+    void* ptrs[] = {P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
-                    P->recvPatch, P->thetaPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
+                    P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (P->comm) {
@@ -630,7 +684,7 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     const wenoext_call& c = P->call;
     CellKernelArgs a{};
     a.records = P->records;
-    a.recOff = P->recOff;
+    a.recInfo = P->recInfo;
     a.cellList = list;
     a.nWork = nWork;
     a.K = P->K;
@@ -652,20 +706,25 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     a.maxTotN = P->maxTotN;
     a.maxSt = P->maxSt;
     a.maxFc = P->maxFc;
+    a.maxRows = P->maxRows;
+    a.G = P->G;
     a.slotBytes = (int)((P->maxRecordBytes + 127) / 128 * 128);
-    // shared-memory budget: ring slots + per-warp scratch
-    // as many consumer warps (cells in compute) as leave at least warps+1 ring slots
-    int warps = P->cfgWarps > 0 ? P->cfgWarps : 8;
+    // Shared-memory budget: ring slots + per-group scratch. A slot is held while its
+    // cell is being computed, so the ring needs one slot per group plus enough
+    // slots in flight to cover the HBM latency-bandwidth product of one SM
+    // (~64 KB); take as many groups as that allows (at most 16 consumer warps).
+    const size_t budget = (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 256;
+    const size_t scratch = groupScratchBytes(P->K, c.CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc);
+    const int inflight = std::max(2, std::min(8, (int)((65536 + a.slotBytes - 1) / a.slotBytes)));
+    int groups = std::max(1, 16 / P->G);
+    if (P->cfgWarps > 0) groups = std::min(groups, P->cfgWarps);
     int slots = 0;
-    for (; warps >= 1; --warps) {
-        const size_t fixed =
-            cellKernelSmemBytes(P->K, c.CB, 0, a.slotBytes, a.maxTotN, a.maxSt, a.maxFc, warps) + 256;
-        slots = (size_t)P->smemLimit > fixed
-                    ? (int)(((size_t)P->smemLimit - fixed) / ((size_t)a.slotBytes + 16))
-                    : 0;
-        if (slots >= warps + 1 || (warps == 1 && slots >= 1)) break;
+    for (; groups >= 1; --groups) {
+        const size_t fixed = (size_t)groups * scratch + 16;
+        slots = budget > fixed ? (int)((budget - fixed) / ((size_t)a.slotBytes + 24)) : 0;
+        if (slots >= groups + inflight || (groups == 1 && slots >= 1)) break;
     }
-    if (warps < 1) warps = 1;
+    if (groups < 1) groups = 1;
     if (P->cfgSlots > 0) slots = std::min(slots, P->cfgSlots);
     if (slots < 1) {
         setError("cell record does not fit in shared memory (polynomial order too high)");
@@ -673,9 +732,8 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     }
     slots = std::min(slots, 64);
     a.nSlots = slots;
-    a.nConsumerWarps = warps;
-    const size_t smem = cellKernelSmemBytes(P->K, c.CB, slots, a.slotBytes, a.maxTotN, a.maxSt,
-                                            a.maxFc, warps);
+    a.nGroups = groups;
+    const size_t smem = cellKernelSmemBytes(a, c.CB);
     const int nTiles = (nWork + 31) / 32;
     int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);
     cudaEvent_t t0 = nullptr, t1 = nullptr;
@@ -693,7 +751,10 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
         P->timeUsed += 2;
         cudaEventRecord(t0, c.st);
     }
-    launchCellKernel(a, c.CB, grid, smem, c.st);
+    if (launchCellKernel(a, c.CB, grid, smem, c.st)) {
+        setError("cell kernel launch configuration rejected");
+        return WENOEXT_ERR_CUDA;
+    }
     if (t1) cudaEventRecord(t1, c.st);
     P->lastLaunches++;
     CUDA_TRY(cudaGetLastError());
@@ -768,6 +829,12 @@ static int phase1(wenoext_plan* P) {
                                     (size_t)pt.size * c.nComp, 8, pt.nbr, P->comm, c.st));
             }
             NCCL_TRY(n, n->GroupEnd());
+        } else {
+            // in-process peers: snapshot what swapData would send (btsfUD) before
+            // any rank's phase 2 rewrites its patch values in place
+            CUDA_TRY(cudaMemcpyAsync(P->sendPatch, c.corr + (size_t)P->nInt * c.nComp,
+                                     (size_t)P->nBnd * c.nComp * 8, cudaMemcpyDeviceToDevice, c.st));
+            CUDA_TRY(cudaEventRecord(P->evC, c.st));
         }
     }
     return 0;
@@ -789,7 +856,7 @@ static int phase2(wenoext_plan* P) {
             }
             CUDA_TRY(cudaStreamWaitEvent(c.st, Q->evC, 0));
             CUDA_TRY(cudaMemcpyAsync(P->recvPatch + (size_t)(pt.start - P->nInt) * c.nComp,
-                                     Q->call.corr + (size_t)qp->start * c.nComp,
+                                     Q->sendPatch + (size_t)(qp->start - Q->nInt) * c.nComp,
                                      (size_t)pt.size * c.nComp * 8, cudaMemcpyDeviceToDevice, c.st));
         }
     }
@@ -882,7 +949,9 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
     if (P->hasCoupled && P->patchCap < nB) {
         if (P->recvPatch) cudaFree(P->recvPatch);
         if (P->thetaPatch) cudaFree(P->thetaPatch);
-        P->recvPatch = P->thetaPatch = nullptr;
+        if (P->sendPatch) cudaFree(P->sendPatch);
+        P->recvPatch = P->thetaPatch = P->sendPatch = nullptr;
+        CUDA_TRY(cudaMalloc((void**)&P->sendPatch, nB * 8));
         CUDA_TRY(cudaMalloc((void**)&P->recvPatch, nB * 8));
         CUDA_TRY(cudaMalloc((void**)&P->thetaPatch, nB * 8));
         CUDA_TRY(cudaMemset(P->recvPatch, 0, nB * 8));

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../include/wenoext_b200.h"
+#include "device_plan.h"
 
 namespace wenoext {
 void setError(const std::string& s);
@@ -47,7 +48,9 @@ struct wenoext_plan {
     int32_t nProcs = 1, myProc = 0;
     // records
     unsigned char* records = nullptr;
-    int64_t* recOff = nullptr;
+    wenoext::RecInfo* recInfo = nullptr;
+    int G = 1;        // warps per cell group (fixes the record interleave)
+    int32_t maxRows = 0;
     int64_t recordBytesTotal = 0, maxRecordBytes = 0;
     int32_t maxTotN = 0, maxSt = 0, maxFc = 0;
     int32_t* cellListInterior = nullptr;
@@ -72,6 +75,7 @@ struct wenoext_plan {
     size_t sendCap = 0;
     double* recvPatch = nullptr;
     double* thetaPatch = nullptr;
+    double* sendPatch = nullptr;  // in-process peers: snapshot of the patch values to send
     size_t patchCap = 0;
     // staging for host-pointer calls
     double *s_vf = nullptr, *s_flux = nullptr, *s_pnf = nullptr, *s_corr = nullptr,
@@ -94,5 +98,5 @@ struct wenoext_plan {
     size_t timeUsed = 0;
     wenoext_plan_info info{};
     // launch geometry overrides (tuning): 0 = auto
-    int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0;
+    int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0, cfgSmemKB = 0;
 };
