@@ -1,5 +1,5 @@
 """Launch-geometry sweep of the fused cell kernel on one case (developer tool).
-Usage: python tools/tune.py N ORDER NCOMP "G,groups,slots,smemKB" ...   (0 = auto)"""
+Usage: python tools/tune.py N ORDER NCOMP "cells,warps,slots,smemKB" ...   (0 = auto)"""
 import os
 import sys
 import time
@@ -21,7 +21,7 @@ phi = torch.from_numpy(phi_h).cuda()
 ref = None
 for cfg in sys.argv[4:]:
     G, groups, slots, smem = (int(x) for x in cfg.split(","))
-    for k, v in (("WENOEXT_G", G), ("WENOEXT_WARPS", groups), ("WENOEXT_SLOTS", slots),
+    for k, v in (("WENOEXT_CELLS", G), ("WENOEXT_WARPS", groups), ("WENOEXT_SLOTS", slots),
                  ("WENOEXT_SMEM_KB", smem)):
         if v > 0:
             os.environ[k] = str(v)
@@ -41,6 +41,6 @@ for cfg in sys.argv[4:]:
     if ref is None:
         ref = o
     err = np.abs(o - ref).max()
-    print(f"cfg G={G} groups={groups} slots={slots} smemKB={smem}: {ms:.4f} ms  {gbs:.0f} GB/s  "
+    print(f"cfg cells={G} warps={groups} slots={slots} smemKB={smem}: {ms:.4f} ms  {gbs:.0f} GB/s  "
           f"frac {gbs / 6547.8:.3f}  maxdiff_vs_first {err:.2e}", flush=True)
     plan.destroy()

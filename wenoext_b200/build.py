@@ -46,6 +46,8 @@ def build_product(force=False, verbose=False):
     os.makedirs(objdir, exist_ok=True)
     objs = []
     common = ["-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include")]
+    if os.environ.get("WENOEXT_KDEBUG"):  # developer aid: device-side bounds checks
+        common.append("-DWENOEXT_KDEBUG")
     for src in CU_SOURCES + CPP_SOURCES:
         obj = os.path.join(objdir, src.replace("/", "_") + ".o")
         cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo"] + common

@@ -3,34 +3,32 @@
 // cell, so that two TMA bulk copies (meta part, matrix part) bring everything
 // static a cell needs into shared memory.
 //
-// Record layout (byte offsets from the record start; K = nDvt, L = lanes of the
-// warp group that processes one cell, fixed per plan):
+// The fused kernel gives one LANE to every (cell, stencil) pair: the lane owns
+// all K coefficients of its stencil for all components in registers. The record
+// is laid out for that mapping (stencil index fastest), so that the lanes of a
+// cell read consecutive shared-memory words.
+//
+// Record layout (byte offsets from the record start; K = nDvt, nSt = surviving
+// stencils in list order, so stencil 0 is the "first surviving" one that gets dm,
+// WENOCoeff.C:198; Nmax = max_s N_s):
 //   META PART
-//   RecHeader                                   16 B
-//   int32  N[nSt]            columns of each surviving stencil (list order, so
-//                            stencil 0 is the "first surviving" one that gets dm,
-//                            WENOCoeff.C:198)
-//   int32  stOff[nSt]        prefix sum of N (entry offset of the stencil's b block)
-//   int32  rnd[nRounds][2]   per round of L rows: {jmax, offset of its A block in doubles}
-//   int32  idx[sum_s N_s]    flat gather index into the value buffer
-//                            (local id, or nCells + haloOffset(proc) + haloId)
-//   int32  faceI[nFc][3]     face id, flat index of the cell across the face (-1 none), kind
-//   pad to 8 B
-//   double B[K*K]            B()[cell]
-//   double faceD[nFc][K+1]   own-side intBasTrans()[f][side] compacted in sumFlux
-//                            enumeration order (WENOUpwindFit.C:304-319), refFacAr()[f]
-//   double quirk[K]          intBasTrans()[cellI][1] compacted (WENOUpwindFit01.C:125)
+//   RecHeader                                   32 B
+//   int32  N[nSt]              columns of each stencil
+//   int32  idx[Nmax][nSt]      flat gather index of entry j of stencil s into the
+//                              value buffer (local id, or nCells + haloOffset(proc)
+//                              + haloId); the cell itself where j >= N_s
+//   pad to 16 B
+//   int32  faceI[nFc][4]       face id, flat index of the cell across (-1 none), kind, 0
+//   double B[K*K]              B()[cell], row-major
+//   double faceD[nFc][K+1]     own-side intBasTrans()[f][side] compacted in sumFlux
+//                              enumeration order (WENOUpwindFit.C:304-319), refFacAr()[f]
+//   double quirk[K]            intBasTrans()[cellI][1] compacted (WENOUpwindFit01.C:125)
 //   pad to 16 B                                          -> metaBytes
-//   MATRIX PART
-//   double A2[...]           LSmatrix()[cell][s] of the surviving stencils, permuted
-//                            for the kernel's lane-per-row mapping: row p = s*K + k
-//                            belongs to round r = p / L; a round with R rows is stored
-//                            column-interleaved, element (j, p) at j*R + (p - r*L), so
-//                            the R lanes read consecutive doubles (no bank conflicts)
-//                            for every j. Rows shorter than the round's jmax are
-//                            zero-filled (only when stencil sizes differ inside a
-//                            round, i.e. bestConditioned).
-//   pad to 16 B                                          -> recBytes
+//   MATRIX PART  (LSmatrix()[cell][s], bitwise copies, permuted)
+//   double2 pairs[Nmax][K/2][nSt]   (A_s[2q][j], A_s[2q+1][j])
+//   double  single[Nmax][nSt]       A_s[K-1][j]            (K odd only)
+//   zero where j >= N_s (only when stencil sizes differ, i.e. bestConditioned)
+//   pad to 16 B                                          -> totBytes
 // Only internal and coupled-patch faces are listed (others get zero correction).
 #pragma once
 #include <cuda_runtime.h>
@@ -39,10 +37,11 @@
 namespace wenoext {
 
 struct RecHeader {
-    int32_t nSt;   // surviving stencils (0 for Cell::empty)
-    int32_t nFc;   // listed faces
-    int32_t totN;  // sum of N_s
-    int32_t flags; // bit0: some stencil entry is a halo cell
+    int32_t nSt;    // surviving stencils (0 for Cell::empty)
+    int32_t nFc;    // listed faces
+    int32_t Nmax;   // max columns over the stencils
+    int32_t flags;  // bit0: some stencil entry is a halo cell
+    int32_t oIdx, oFace, oB, metaBytes;  // byte offsets of the meta sections
 };
 
 // per cell: where its record lives (one 16-byte load for the TMA producer)
@@ -61,34 +60,25 @@ enum : int32_t {
     FACE_CYCLIC = 2
 };
 
-__host__ __device__ inline int recRounds(int nSt, int K, int L) { return (nSt * K + L - 1) / L; }
-
-// byte offsets of the meta sections
-struct RecLayout {
-    int32_t oN, oStOff, oRnd, oIdx, oFaceI, oB, oFaceD, oQuirk, metaBytes;
-};
-__host__ __device__ inline RecLayout recLayout(int K, int L, int nSt, int totN, int nFc) {
-    RecLayout l;
-    int o = (int)sizeof(RecHeader);
-    l.oN = o;
-    o += 4 * nSt;
-    l.oStOff = o;
-    o += 4 * nSt;
-    l.oRnd = o;
-    o += 8 * recRounds(nSt, K, L);
-    l.oIdx = o;
-    o += 4 * totN;
-    l.oFaceI = o;
-    o += 12 * nFc;
-    o = (o + 7) & ~7;
-    l.oB = o;
-    o += 8 * K * K;
-    l.oFaceD = o;
-    o += 8 * nFc * (K + 1);
-    l.oQuirk = o;
-    o += 8 * K;
-    l.metaBytes = (o + 15) & ~15;
-    return l;
+__host__ __device__ inline RecHeader recLayout(int K, int nSt, int Nmax, int nFc) {
+    RecHeader h;
+    h.nSt = nSt;
+    h.nFc = nFc;
+    h.Nmax = Nmax;
+    h.flags = 0;
+    int o = (int)sizeof(RecHeader) + 4 * nSt;
+    h.oIdx = o;
+    o += 4 * Nmax * nSt;
+    o = (o + 15) & ~15;
+    h.oFace = o;
+    o += 16 * nFc;
+    h.oB = o;
+    o += 8 * (K * K + nFc * (K + 1) + K);
+    h.metaBytes = (o + 15) & ~15;
+    return h;
+}
+__host__ __device__ inline int recMatrixBytes(int K, int nSt, int Nmax) {
+    return (Nmax * nSt * K * 8 + 15) & ~15;
 }
 
 // Arguments of the fused cell kernel (by value, __grid_constant__).
@@ -111,10 +101,14 @@ struct CellKernelArgs {
     uint32_t pExp;
     double dm, eps;
     // launch geometry
-    int32_t G;                 // warps per cell group (L = 32*G, fixed by the plan)
-    int32_t nGroups;           // cell groups per CTA
+    int32_t cellsPerWarp;      // 4, 2 or 1: 32 / cellsPerWarp stencil lanes per cell
+    int32_t nWarps;            // consumer warps per CTA
     int32_t nSlots, slotBytes; // shared-memory ring of records
-    int32_t maxTotN, maxRows, maxSt, maxFc;
+    int32_t maxN;              // max stencil columns in the plan
+    // developer aid (only read when built with -DWENOEXT_KDEBUG): first violated
+    // bounds check is recorded in dbg[0..15]
+    int32_t nVals, nFaces;
+    int32_t* dbg;
 };
 
 struct PatchKernelArgs {
@@ -138,9 +132,8 @@ struct PatchKernelArgs {
 
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st);
-// shared memory of one cell group's scratch / of the whole CTA
-size_t groupScratchBytes(int K, int CB, int maxTotN, int maxRows, int maxSt, int maxFc);
-size_t cellKernelSmemBytes(const CellKernelArgs& a, int CB);
+size_t cellKernelSmemBytes(const CellKernelArgs& a);
+bool cellKernelSupportsK(int K);
 void launchPatchKernel(const PatchKernelArgs& a, cudaStream_t st);
 void launchPackValues(const double* vf, int nCells, int nComp, int c0, int CB, int VS,
                       double* vals, cudaStream_t st);

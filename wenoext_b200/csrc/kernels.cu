@@ -13,11 +13,16 @@
 // records (device_plan.h) into a shared-memory ring with 1-D TMA bulk copies
 // (cp.async.bulk ... mbarrier::complete_tx, SASS UBLKCP): the small meta part
 // and the matrix part complete on separate mbarriers, so the gather of stencil
-// values overlaps the arrival of the matrices. A group of G warps takes one cell:
-// every lane owns one row (stencil, coefficient) of the stacked matrices, reads
-// it conflict-free from the interleaved record and keeps CB component
-// accumulators in registers. The kernel is HBM-bound: tensor cores are
-// deliberately unused (independent 9x21 GEMVs, no operand reuse).
+// values overlaps the arrival of the matrices. Consumer warps take CELLS cells per
+// pass and give one lane to every (cell, stencil): the lane gathers its own
+// stencil's value differences straight into registers (software-pipelined global
+// loads), streams its matrix column by column from shared memory (128-bit loads,
+// stencil index fastest, so the lanes of a cell read consecutive words) and keeps
+// all K x CB coefficients in registers. Smoothness indicators and weights stay in
+// registers; the weighted sum over the stencils of a cell is a warp-shuffle
+// butterfly over the cell's lanes; afterwards every lane evaluates one face.
+// No scratch shared memory and no block-level barriers. The kernel is HBM-bound:
+// tensor cores are deliberately unused (independent 9x21 GEMVs, no operand reuse).
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -28,7 +33,7 @@ namespace wenoext {
 namespace {
 
 constexpr int TILE = 32;          // consecutive cells handed to one CTA at a time
-constexpr int MAX_THREADS = 544;  // 16 consumer warps + producer
+constexpr int MAX_THREADS = 256;  // 7 consumer warps + producer (up to 255 registers)
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -43,6 +48,25 @@ __device__ __forceinline__ void mbarArriveExpectTx(uint32_t bar, uint32_t bytes)
 __device__ __forceinline__ void mbarArrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+#ifdef WENOEXT_KDEBUG
+__device__ int32_t* g_dbg = nullptr;
+__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
+    for (long long it = 0; it < 4000000; ++it) {
+        uint32_t ok;
+        asm volatile(
+            "{\n.reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (ok) return;
+    }
+    if (g_dbg && atomicCAS(g_dbg, 0, 4) == 0) {
+        g_dbg[1] = (int)bar; g_dbg[2] = (int)parity; g_dbg[10] = blockIdx.x; g_dbg[11] = threadIdx.x;
+    }
+}
+#else
 __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"
@@ -56,6 +80,7 @@ __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+#endif
 __device__ __forceinline__ uint64_t evictFirstPolicy() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -86,56 +111,23 @@ __device__ __forceinline__ int32_t lds32(uint32_t a) {
     asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
     return v;
 }
-__device__ __forceinline__ void sts64(uint32_t a, double v) {
-    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
-}
-__device__ __forceinline__ void sts128(uint32_t a, double x, double y) {
-    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(x), "d"(y) : "memory");
-}
-// barrier of one cell group (G warps); G == 1 is a warp barrier
-__device__ __forceinline__ void groupSync(int G, int grp) {
-    if (G == 1)
-        __syncwarp();
-    else
-        asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(G * 32) : "memory");
+__device__ __forceinline__ int4 lds128i(uint32_t a) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(a));
+    return v;
 }
 
+// WENOCoeff.H:149-157: repeated multiplication, exponent truncated to unsigned.
+// The first 8 factors are predicated (no loop) - p = 4 is the default.
 __device__ __forceinline__ double intPowD(double base, uint32_t e) {
     double t = 1.0;
-    for (uint32_t i = 0; i < e; ++i) t *= base;  // WENOCoeff.H:149-157
+#pragma unroll
+    for (uint32_t i = 0; i < 8; ++i) t = i < e ? t * base : t;
+    for (uint32_t i = 8; i < e; ++i) t *= base;
     return t;
 }
-
-__host__ __device__ inline size_t alignUp(size_t x, size_t a) { return (x + a - 1) / a * a; }
-
-// Per-group scratch: component vectors are stored as a (c0,c1) double2 plane plus
-// a c2 plane so that one LDS.128 + one LDS.64 fetch three components.
-template <int CB>
-struct Vec {
-    uint32_t p01, p2;  // shared addresses of the planes
-    __device__ __forceinline__ void load(int i, double (&v)[CB]) const {
-        if constexpr (CB == 1) {
-            v[0] = lds64(p01 + i * 8);
-        } else {
-            double2 t = lds128(p01 + i * 16);
-            v[0] = t.x;
-            v[1] = t.y;
-            if constexpr (CB == 3) v[2] = lds64(p2 + i * 8);
-        }
-    }
-    __device__ __forceinline__ void store(int i, const double (&v)[CB]) const {
-        if constexpr (CB == 1) {
-            sts64(p01 + i * 8, v[0]);
-        } else {
-            sts128(p01 + i * 16, v[0], v[1]);
-            if constexpr (CB == 3) sts64(p2 + i * 8, v[2]);
-        }
-    }
-    __device__ __forceinline__ uint32_t addr(int i, int c) const {
-        if constexpr (CB == 1) return p01 + i * 8;
-        return c < 2 ? p01 + i * 16 + c * 8 : p2 + i * 8;
-    }
-};
 
 template <int CB>
 __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB]) {
@@ -148,55 +140,26 @@ __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&
         if constexpr (CB == 3) v[2] = __ldg(p + 2);
     }
 }
-template <int CB>
-__device__ __forceinline__ double pick(const double (&v)[CB], int c) {
-    double r = v[0];
-    if constexpr (CB > 1) r = c == 1 ? v[1] : r;
-    if constexpr (CB > 2) r = c == 2 ? v[2] : r;
-    return r;
-}
 
-struct GroupScratch {
-    uint32_t b01, b2, c01, c2, gam, W, poly, theta;
-};
-__host__ __device__ inline size_t scratchLayout(int K, int CB, int maxTotN, int maxRows, int maxSt,
-                                                int maxFc, GroupScratch* g, uint32_t base) {
-    const int nb = maxTotN > maxRows ? maxTotN : maxRows;
-    size_t o = 0;
-    const size_t w01 = CB == 1 ? 8 : 16;
-    if (g) g->b01 = base + (uint32_t)o;
-    o += alignUp((size_t)nb * w01, 16);
-    if (g) g->b2 = base + (uint32_t)o;
-    if (CB == 3) o += alignUp((size_t)nb * 8, 16);
-    if (g) g->c01 = base + (uint32_t)o;
-    o += alignUp((size_t)maxRows * w01, 16);
-    if (g) g->c2 = base + (uint32_t)o;
-    if (CB == 3) o += alignUp((size_t)maxRows * 8, 16);
-    if (g) g->gam = base + (uint32_t)o;
-    o += alignUp((size_t)maxSt * CB * 8, 16);
-    if (g) g->W = base + (uint32_t)o;
-    o += alignUp((size_t)K * CB * 8, 16);
-    if (g) g->poly = base + (uint32_t)o;
-    o += alignUp((size_t)maxFc * CB * 8, 16);
-    if (g) g->theta = base + (uint32_t)o;
-    o += 32;
-    return o;
-}
-
-template <int KT, int CB>
+template <int K, int CB, int CELLS, int D>
 __global__ void __launch_bounds__(MAX_THREADS, 1)
     weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const int K = KT ? KT : a.K;
-    const int G = a.G, L = G * 32, NG = a.nGroups;
+    constexpr int SS = 32 / CELLS;  // stencil lanes per cell
+    constexpr int KP = K / 2;       // coefficient pairs per column
+    constexpr bool ODD = (K & 1) != 0;
+    const int NW = a.nWarps;
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int nSlots = a.nSlots;
 
     const uint32_t ring = smemAddr(smem);
     const uint32_t bars = ring + (uint32_t)nSlots * a.slotBytes;  // per slot: fullMeta, fullA, empty
-    const uint32_t scratch0 = (bars + (uint32_t)nSlots * 24 + 15u) & ~15u;
 
+#ifdef WENOEXT_KDEBUG
+    if (threadIdx.x == 0 && blockIdx.x == 0) g_dbg = a.dbg;
+    if (threadIdx.x == 0 && blockIdx.x == 0) { a.dbg[13] = (int)ring; a.dbg[14] = (int)bars; a.dbg[15] = nSlots; }
+#endif
     if (threadIdx.x == 0) {
         for (int s = 0; s < 3 * nSlots; ++s) mbarInit(bars + s * 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -216,7 +179,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         return a.cellList ? __ldg(a.cellList + w) : w;
     };
 
-    if (warp == NG * G) {
+    if (warp == NW) {
         // ===== producer warp: all lanes prefetch the record descriptors of the next
         // 32 items, lane 0 waits for free slots and issues the bulk copies =====
         const uint64_t pol = evictFirstPolicy();
@@ -259,230 +222,362 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         }
         return;
     }
-    if (warp > NG * G) return;
+    if (warp > NW) return;
 
-    // ===== consumers: a group of G warps per cell, one lane per matrix row =====
-    const int grp = warp / G;
-    const int gl = (warp - grp * G) * 32 + lane;
-    GroupScratch gs;
-    {
-        const size_t per = scratchLayout(K, CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc, nullptr, 0);
-        scratchLayout(K, CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc, &gs,
-                      scratch0 + (uint32_t)(grp * per));
-    }
-    const Vec<CB> bv{gs.b01, gs.b2};  // b values, later the IS products t
-    const Vec<CB> cv{gs.c01, gs.c2};  // coefficients per (stencil, k)
-    const int nBndBase = a.nInternalFaces;
+    // ===== consumers: CELLS cells per warp pass, one lane per (cell, stencil) =====
+    const int cslot = lane / SS;
+    const int s = lane - cslot * SS;
     const bool fit01 = a.scheme == 1;
     const bool fitBounded = a.scheme == 0 && a.bounded;
 
-    int slot = grp % nSlots, round = grp / nSlots;
-    for (int n = grp; n < nItems; n += NG) {
-        const int cell = itemToCell(n);
+    for (int base = warp * CELLS; base < nItems; base += NW * CELLS) {
+        const int item = base + cslot;
+        const bool valid = item < nItems;
+        const int slot = item % nSlots;
+        const uint32_t parity = (uint32_t)(item / nSlots) & 1u;
+        const uint32_t rec = ring + (uint32_t)slot * a.slotBytes;
+        const uint32_t bar = bars + (uint32_t)(slot * 3) * 8;
+        const int cell = valid ? itemToCell(item) : 0;
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen);
 
-        const uint32_t rec = ring + (uint32_t)slot * a.slotBytes;
-        mbarWait(bars + (slot * 3) * 8, round & 1);
-        const int nSt = lds32(rec), nFc = lds32(rec + 4), totN = lds32(rec + 8);
-        const RecLayout lay = recLayout(K, L, nSt, totN, nFc);
-        const int nRows = nSt * K;
-        const int nFaceItems = nFc * CB;
-
-        // face data of this lane's first (face, component) item: issue the global
-        // loads now, they are consumed at the very end
-        int pfFace = 0, pfOther = -1, pfKind = 0;
-        double pfFlux = 0.0, pfPsiN = 0.0;
-        if (gl < nFaceItems) {
-            const int f = gl / CB, c = gl - f * CB;
-            const uint32_t fa = rec + lay.oFaceI + f * 12;
-            pfFace = lds32(fa);
-            pfOther = lds32(fa + 4);
-            pfKind = lds32(fa + 8);
-            pfFlux = __ldg(a.flux + pfFace);
-            if (fitBounded && (pfKind >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
-                pfPsiN = __ldg(a.vals + (size_t)pfOther * a.VS + c);
+        if (valid) mbarWait(bar, parity);
+        __syncwarp();
+        int nSt = 0, nFc = 0, Nmax = 0;
+        uint32_t oIdx = 0, oFace = 0, oB = 0, metaBytes = 0;
+        if (valid) {
+            const int4 h0 = lds128i(rec), h1 = lds128i(rec + 16);
+            nSt = h0.x;
+            nFc = h0.y;
+            Nmax = h0.z;
+            oIdx = h1.x;
+            oFace = h1.y;
+            oB = h1.z;
+            metaBytes = h1.w;
         }
-
-        // gather: b[e][c] = psi(id_e)[c] - psi(cell)[c]      (WENOCoeff.C:138-156)
-        for (int e = gl; e < totN; e += L) {
-            const int id = lds32(rec + lay.oIdx + e * 4);
-            double v[CB];
-            loadVals<CB>(a.vals + (size_t)id * a.VS, v);
-#pragma unroll
-            for (int c = 0; c < CB; ++c) v[c] -= cen[c];
-            bv.store(e, v);
+#ifdef WENOEXT_KDEBUG
+        if (valid && (nSt < 0 || nSt > SS || nFc < 0 || nFc > 64 || Nmax < 0 || Nmax > a.maxN ||
+                      oIdx > (uint32_t)a.slotBytes || oFace > (uint32_t)a.slotBytes ||
+                      oB > (uint32_t)a.slotBytes || metaBytes > (uint32_t)a.slotBytes)) {
+            if (atomicCAS(a.dbg, 0, 1) == 0) {
+                a.dbg[1] = item; a.dbg[2] = slot; a.dbg[3] = (int)parity; a.dbg[4] = cell;
+                a.dbg[5] = nSt; a.dbg[6] = nFc; a.dbg[7] = Nmax; a.dbg[8] = (int)oIdx;
+                a.dbg[9] = (int)metaBytes; a.dbg[10] = blockIdx.x; a.dbg[11] = threadIdx.x;
+                a.dbg[12] = nItems;
+            }
+            nSt = nFc = Nmax = 0;
         }
-        groupSync(G, grp);
-        mbarWait(bars + (slot * 3 + 1) * 8, round & 1);
+#endif
+        const bool act = s < nSt;
+        const int N = act ? lds32(rec + (uint32_t)sizeof(RecHeader) + s * 4) : 0;
+        const int Nloop = __reduce_max_sync(0xffffffffu, Nmax);
 
-        // phase 1: coeffs[s][k][c] = sum_j A_s[k][j] * b_s[j][c]   (WENOCoeff.C:159)
-        for (int r0 = 0; r0 < nRows; r0 += L) {
-            const int p = r0 + gl;
-            if (p < nRows) {
-                const int s = p / K;
-                const int N = lds32(rec + lay.oN + s * 4);
-                const int bo = lds32(rec + lay.oStOff + s * 4);
-                const int rbase = lds32(rec + lay.oRnd + (r0 / L) * 8 + 4);
-                const int R = min(L, nRows - r0);
-                uint32_t Ap = rec + lay.metaBytes + (uint32_t)(rbase + gl) * 8;
-                const uint32_t stride = (uint32_t)R * 8;
-                double acc[CB];
+        // first face of this lane: issue its global loads now, consumed at the end
+        int4 pfFace = make_int4(0, -1, 0, 0);
+        double pfFlux = 0.0;
+        double pfPsiN[CB];
 #pragma unroll
-                for (int c = 0; c < CB; ++c) acc[c] = 0.0;
-#pragma unroll 7
-                for (int j = 0; j < N; ++j) {
-                    const double av = lds64(Ap);
-                    Ap += stride;
-                    double b[CB];
-                    bv.load(bo + j, b);
-#pragma unroll
-                    for (int c = 0; c < CB; ++c) acc[c] = fma(av, b[c], acc[c]);
+        for (int c = 0; c < CB; ++c) pfPsiN[c] = 0.0;
+        if (s < nFc) {
+            pfFace = lds128i(rec + oFace + s * 16);
+#ifdef WENOEXT_KDEBUG
+            if (pfFace.x < 0 || pfFace.x >= a.nFaces || pfFace.y < -1 || pfFace.y >= a.nVals) {
+                if (atomicCAS(a.dbg, 0, 3) == 0) {
+                    a.dbg[1] = item; a.dbg[2] = slot; a.dbg[3] = s; a.dbg[4] = cell;
+                    a.dbg[5] = pfFace.x; a.dbg[6] = pfFace.y; a.dbg[7] = pfFace.z; a.dbg[8] = nFc;
                 }
-                cv.store(p, acc);
+                pfFace = make_int4(0, 0, 0, 0);
+            }
+#endif
+            pfFlux = __ldg(a.flux + pfFace.x);
+            if (fitBounded && (pfFace.z >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
+                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN);
+        }
+
+        // gather pipeline: column j of this lane's stencil (WENOCoeff.C:138-156)
+        const uint32_t idxBase = rec + oIdx + s * 4;
+        const uint32_t idxStride = (uint32_t)nSt * 4;
+        auto issue = [&](int j, double (&g)[CB]) {
+            if (j < N) {
+                int id = lds32(idxBase + (uint32_t)j * idxStride);
+#ifdef WENOEXT_KDEBUG
+                if (id < 0 || id >= a.nVals) {
+                    if (atomicCAS(a.dbg, 0, 2) == 0) {
+                        a.dbg[1] = item; a.dbg[2] = slot; a.dbg[3] = j; a.dbg[4] = cell;
+                        a.dbg[5] = nSt; a.dbg[6] = id; a.dbg[7] = N; a.dbg[8] = s;
+                    }
+                    id = 0;
+                }
+#endif
+                loadVals<CB>(a.vals + (size_t)id * a.VS, g);
+            } else {
+#pragma unroll
+                for (int c = 0; c < CB; ++c) g[c] = cen[c];
+            }
+        };
+        double nx[D][CB];
+#pragma unroll
+        for (int d = 0; d < D; ++d) issue(d, nx[d]);
+
+        // phase 1: coeffs[k][c] = sum_j A_s[k][j] * b_s[j][c]        (WENOCoeff.C:159)
+        double acc[K][CB];
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int c = 0; c < CB; ++c) acc[k][c] = 0.0;
+        const uint32_t pairStride = (uint32_t)nSt * 16;
+        const uint32_t colStride = pairStride * KP;
+        const uint32_t sglStride = (uint32_t)nSt * 8;
+        uint32_t Ap = rec + metaBytes + (uint32_t)s * 16;
+        uint32_t Sp = rec + metaBytes + (uint32_t)Nmax * colStride + (uint32_t)s * 8;
+        // One column of this lane's matrix: K/2 128-bit loads (+1 64-bit), K*CB DFMAs
+        auto column = [&](const double (&b)[CB]) {
+            uint32_t ap = Ap;
+#pragma unroll
+            for (int q = 0; q < KP; ++q) {
+                const double2 av = lds128(ap);
+                ap += pairStride;
+#pragma unroll
+                for (int c = 0; c < CB; ++c) {
+                    acc[2 * q][c] = fma(av.x, b[c], acc[2 * q][c]);
+                    acc[2 * q + 1][c] = fma(av.y, b[c], acc[2 * q + 1][c]);
+                }
+            }
+            if constexpr (ODD) {
+                const double a1 = lds64(Sp);
+#pragma unroll
+                for (int c = 0; c < CB; ++c) acc[K - 1][c] = fma(a1, b[c], acc[K - 1][c]);
+            }
+        };
+        // Fast path (uniform meshes): every active lane of the warp has the same number
+        // of columns, a multiple of D -> no per-column predicate. Lanes without a
+        // stencil read the matrix of stencil 0 of the warp's first cell (finite data)
+        // against b == 0.
+        const bool uniform = __all_sync(0xffffffffu, N == Nloop || N == 0) && (Nloop % D) == 0;
+        uint32_t cStr = colStride, sStr = sglStride, pStr = pairStride;
+        {
+            const uint32_t have = __ballot_sync(0xffffffffu, N > 0);
+            const int src = have ? __ffs(have) - 1 : 0;
+            const uint32_t ApS = __shfl_sync(0xffffffffu, Ap, src);
+            const uint32_t SpS = __shfl_sync(0xffffffffu, Sp, src);
+            const uint32_t pS = __shfl_sync(0xffffffffu, pairStride, src);
+            if (uniform && N == 0) {
+                Ap = ApS;
+                Sp = SpS;
+                pStr = pS;
+                cStr = pS * KP;
+                sStr = pS / 2;
             }
         }
-        groupSync(G, grp);
-        // phase 2a: t[s][k][c] = c_k * (B c)_k                  (WENOCoeff.C:190-196)
-        for (int r0 = 0; r0 < nRows; r0 += L) {
-            const int p = r0 + gl;
-            if (p < nRows) {
-                const int s = p / K, k = p - s * K;
-                const uint32_t Bp = rec + lay.oB + (uint32_t)(k * K) * 8;
+        for (int j0 = 0; j0 < Nloop; j0 += D) {
+            double cu[D][CB];
+#pragma unroll
+            for (int d = 0; d < D; ++d)
+#pragma unroll
+                for (int c = 0; c < CB; ++c) cu[d][c] = nx[d][c] - cen[c];
+#pragma unroll
+            for (int d = 0; d < D; ++d) issue(j0 + D + d, nx[d]);
+            if (j0 == 0) {
+                if (valid) mbarWait(bar + 8, parity);
+                __syncwarp();
+            }
+            if (uniform) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    uint32_t ap = Ap;
+#pragma unroll
+                    for (int q = 0; q < KP; ++q) {
+                        const double2 av = lds128(ap);
+                        ap += pStr;
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) {
+                            acc[2 * q][c] = fma(av.x, cu[d][c], acc[2 * q][c]);
+                            acc[2 * q + 1][c] = fma(av.y, cu[d][c], acc[2 * q + 1][c]);
+                        }
+                    }
+                    if constexpr (ODD) {
+                        const double a1 = lds64(Sp);
+#pragma unroll
+                        for (int c = 0; c < CB; ++c)
+                            acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
+                    }
+                    Ap += cStr;
+                    Sp += sStr;
+                }
+            } else {
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    if (j0 + d < N) column(cu[d]);
+                    Ap += colStride;
+                    Sp += sglStride;
+                }
+            }
+        }
+        // phase 2: IS = c^T (B c) per component                  (WENOCoeff.C:190-196)
+        double g[CB];
+        {
+            double IS[CB];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) IS[c] = 0.0;
+            const uint32_t Bb = rec + oB;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
                 double u[CB];
 #pragma unroll
                 for (int c = 0; c < CB; ++c) u[c] = 0.0;
-#pragma unroll(KT ? KT : 4)
+#pragma unroll
                 for (int q = 0; q < K; ++q) {
-                    const double bq = lds64(Bp + q * 8);
-                    double cq[CB];
-                    cv.load(s * K + q, cq);
+                    const double bq = lds64(Bb + (uint32_t)(k * K + q) * 8);
 #pragma unroll
-                    for (int c = 0; c < CB; ++c) u[c] = fma(bq, cq[c], u[c]);
+                    for (int c = 0; c < CB; ++c) u[c] = fma(bq, acc[q][c], u[c]);
                 }
-                double own[CB];
-                cv.load(p, own);
 #pragma unroll
-                for (int c = 0; c < CB; ++c) u[c] *= own[c];
-                bv.store(p, u);
+                for (int c = 0; c < CB; ++c) IS[c] = fma(acc[k][c], u[c], IS[c]);
             }
+            // gamma: dm for the first surviving stencil          (WENOCoeff.C:198-205)
+#pragma unroll
+            for (int c = 0; c < CB; ++c)
+                g[c] = act ? (s == 0 ? a.dm : 1.0) / intPowD(a.eps + IS[c], a.pExp) : 0.0;
         }
-        groupSync(G, grp);
-        // phase 2b: IS and gamma per (stencil, component)      (WENOCoeff.C:196-205)
-        for (int i = gl; i < nSt * CB; i += L) {
-            const int s = i / CB, c = i - s * CB;
-            double IS = 0.0;
-            for (int k = 0; k < K; ++k) IS += lds64(bv.addr(s * K + k, c));
-            sts64(gs.gam + i * 8, (s == 0 ? a.dm : 1.0) / intPowD(a.eps + IS, a.pExp));
+        // weighted sum over the stencils of the cell: butterfly over its SS lanes
+        // (WENOCoeff.C:207-220; the division by gammaSum is applied per face below)
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int c = 0; c < CB; ++c) acc[k][c] *= g[c];
+#pragma unroll
+        for (int m = 1; m < SS; m <<= 1) {
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+#pragma unroll
+                for (int c = 0; c < CB; ++c)
+                    acc[k][c] += __shfl_xor_sync(0xffffffffu, acc[k][c], m);
+#pragma unroll
+            for (int c = 0; c < CB; ++c) g[c] += __shfl_xor_sync(0xffffffffu, g[c], m);
         }
-        groupSync(G, grp);
-        // phase 2c: weighted combination                        (WENOCoeff.C:207-220)
-        for (int i = gl; i < K * CB; i += L) {
-            const int k = i / CB, c = i - k * CB;
-            double acc = 0.0, gsum = 0.0;
-            for (int s = 0; s < nSt; ++s) {
-                const double g = lds64(gs.gam + (s * CB + c) * 8);
-                gsum += g;
-                acc = fma(g, lds64(cv.addr(s * K + k, c)), acc);
+        // now acc = sum_s gamma_s c_s and g = gammaSum on every lane of the cell
+
+        // phase 3: faces, one (or more) per lane
+        const uint32_t fdBase = rec + oB + (uint32_t)(K * K) * 8;
+        const uint32_t quirkA = fdBase + (uint32_t)(nFc * (K + 1)) * 8;
+        // sumFlux with this cell's weighted polynomial (WENOUpwindFit.C:293-323)
+        // (sum_s gamma_s c_s) / gammaSum / refFacAr is evaluated with reciprocals
+        // (one division per component and one per face instead of two per value)
+        double invG[CB];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) invG[c] = nSt > 0 ? 1.0 / g[c] : 0.0;  // Cell::empty -> zero
+        auto polyAt = [&](uint32_t basis, double refFacAr, double (&out)[CB]) {
+            double S[CB];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) S[c] = 0.0;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const double bk = lds64(basis + k * 8);
+#pragma unroll
+                for (int c = 0; c < CB; ++c) S[c] = fma(acc[k][c], bk, S[c]);
             }
-            sts64(gs.W + i * 8, nSt > 0 ? acc / gsum : 0.0);  // Cell::empty -> zero (WENOCoeff.C:333)
-        }
-        groupSync(G, grp);
-        // phase 3: faces. Items (face, component) of the cell, one per lane.
+            const double rinv = 1.0 / refFacAr;
+#pragma unroll
+            for (int c = 0; c < CB; ++c) out[c] = (S[c] * invG[c]) * rinv;
+        };
+        double theta[CB];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) theta[c] = 1.0;
         if (fit01) {
-            // own polynomial at every internal face (WENOUpwindFit01.C:80-136)
-            for (int i = gl; i < nFaceItems; i += L) {
-                const int f = i / CB, c = i - f * CB;
-                const uint32_t fa = rec + lay.oFaceI + f * 12;
-                const int kind = lds32(fa + 8);
-                double val = pick<CB>(cen, c);
-                if ((kind >> FACE_TYPE_SHIFT) == FACE_INTERNAL) {
-                    const uint32_t fd = rec + lay.oFaceD + (uint32_t)(f * (K + 1)) * 8;
-                    const double fl = i == gl ? pfFlux : __ldg(a.flux + lds32(fa));
-                    const bool nei = kind & FACE_SIDE_NEI;
-                    const uint32_t basis =
-                        (nei && !(fl < 0) && a.bugCompat) ? rec + lay.oQuirk : fd;
-                    double s = 0.0;
-                    for (int k = 0; k < K; ++k)
-                        s = fma(lds64(gs.W + (k * CB + c) * 8), lds64(basis + k * 8), s);
-                    val += s / lds64(fd + K * 8);
+            // WENOUpwindFit01.C:66-161: extrema of the own polynomial over the
+            // internal faces of the cell
+            double mx[CB], mn[CB];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) mx[c] = mn[c] = cen[c];
+            for (int f = s; f < nFc; f += SS) {
+                const int4 fi = f == s ? pfFace : lds128i(rec + oFace + f * 16);
+                if ((fi.z >> FACE_TYPE_SHIFT) != FACE_INTERNAL) continue;
+                const double fl = f == s ? pfFlux : __ldg(a.flux + fi.x);
+                const uint32_t fd = fdBase + (uint32_t)(f * (K + 1)) * 8;
+                const bool nei = fi.z & FACE_SIDE_NEI;
+                const uint32_t basis = (nei && !(fl < 0) && a.bugCompat) ? quirkA : fd;
+                double pv[CB];
+                polyAt(basis, lds64(fd + K * 8), pv);
+#pragma unroll
+                for (int c = 0; c < CB; ++c) {
+                    const double t = cen[c] + pv[c];
+                    mx[c] = t > mx[c] ? t : mx[c];
+                    mn[c] = t < mn[c] ? t : mn[c];
                 }
-                sts64(gs.poly + i * 8, val);
             }
-            groupSync(G, grp);
-            if (gl < CB) {
-                const int c = gl;
-                const double psi = pick<CB>(cen, c);
-                double mx = psi, mn = psi;
-                for (int f = 0; f < nFc; ++f) {
-                    if ((lds32(rec + lay.oFaceI + f * 12 + 8) >> FACE_TYPE_SHIFT) != FACE_INTERNAL)
-                        continue;
-                    const double t = lds64(gs.poly + (f * CB + c) * 8);
-                    if (t > mx)
-                        mx = t;
-                    else if (t < mn)
-                        mn = t;
+#pragma unroll
+            for (int m = 1; m < SS; m <<= 1)
+#pragma unroll
+                for (int c = 0; c < CB; ++c) {
+                    const double omx = __shfl_xor_sync(0xffffffffu, mx[c], m);
+                    const double omn = __shfl_xor_sync(0xffffffffu, mn[c], m);
+                    mx[c] = omx > mx[c] ? omx : mx[c];
+                    mn[c] = omn < mn[c] ? omn : mn[c];
                 }
-                const double argMax = fabs(mx - psi) < 1e-9 ? 1.0 : fabs((1.0 - psi) / (mx - psi));
-                const double argMin = fabs(mn - psi) < 1e-9 ? 1.0 : fabs((0.0 - psi) / (mn - psi));
-                sts64(gs.theta + c * 8, fmin(fmin(argMax, argMin), 1.0));
+#pragma unroll
+            for (int c = 0; c < CB; ++c) {
+                const double psi = cen[c];
+                const double argMax =
+                    fabs(mx[c] - psi) < 1e-9 ? 1.0 : fabs((1.0 - psi) / (mx[c] - psi));
+                const double argMin =
+                    fabs(mn[c] - psi) < 1e-9 ? 1.0 : fabs((0.0 - psi) / (mn[c] - psi));
+                theta[c] = fmin(fmin(argMax, argMin), 1.0);
             }
-            groupSync(G, grp);
         }
-        for (int i = gl; i < nFaceItems; i += L) {
-            const int f = i / CB, c = i - f * CB;
-            int faceId = pfFace, other = pfOther, kind = pfKind;
-            double fl = pfFlux;
-            if (i != gl) {
-                const uint32_t fa = rec + lay.oFaceI + f * 12;
-                faceId = lds32(fa);
-                other = lds32(fa + 4);
-                kind = lds32(fa + 8);
-                fl = __ldg(a.flux + faceId);
-            }
-            const int type = kind >> FACE_TYPE_SHIFT;
-            const bool nei = kind & FACE_SIDE_NEI;
-            const double psi = pick<CB>(cen, c);
+        for (int f = s; f < nFc; f += SS) {
+            const int4 fi = f == s ? pfFace : lds128i(rec + oFace + f * 16);
+            const double fl = f == s ? pfFlux : __ldg(a.flux + fi.x);
+            const int faceId = fi.x, type = fi.z >> FACE_TYPE_SHIFT;
+            const bool nei = fi.z & FACE_SIDE_NEI;
             // who writes: owner unless flux<0 (flux==0 -> owner writes zero), WENOUpwindFit.C:258-281
             const bool up = nei ? (fl < 0) : (fl > 0);
             const bool writer = type == FACE_INTERNAL ? (nei ? (fl < 0) : !(fl < 0)) : (fl > 0);
-            const double th = fit01 ? lds64(gs.theta + c * 8) : 1.0;
-            if (fit01 && type == FACE_PROCESSOR && a.thetaPatch)
-                a.thetaPatch[(size_t)(faceId - nBndBase) * a.nComp + a.c0 + c] = th;
+            if (fit01 && type == FACE_PROCESSOR && a.thetaPatch) {
+#pragma unroll
+                for (int c = 0; c < CB; ++c)
+                    a.thetaPatch[(size_t)(faceId - a.nInternalFaces) * a.nComp + a.c0 + c] = theta[c];
+            }
             if (!writer) continue;
-            double out = 0.0;
+            double out[CB];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) out[c] = 0.0;
             if (up) {
-                const uint32_t fd = rec + lay.oFaceD + (uint32_t)(f * (K + 1)) * 8;
-                double s = 0.0;
-                for (int k = 0; k < K; ++k)
-                    s = fma(lds64(gs.W + (k * CB + c) * 8), lds64(fd + k * 8), s);
-                out = s / lds64(fd + K * 8);
+                const uint32_t fd = fdBase + (uint32_t)(f * (K + 1)) * 8;
+                polyAt(fd, lds64(fd + K * 8), out);
                 if (type == FACE_INTERNAL) {
                     if (fit01) {
-                        out = th * out;  // WENOUpwindFit01.C:167-181
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) out[c] = theta[c] * out[c];  // WENOUpwindFit01.C:167-181
                     } else if (a.bounded) {
                         // WENOUpwindFit.C:81-108, :172-179
-                        const double psiN =
-                            i == gl ? pfPsiN : __ldg(a.vals + (size_t)other * a.VS + c);
-                        const double dpsi = fabs(psi - psiN);
-                        if (fabs(out) > dpsi) out = fmin(dpsi / fabs(out), 1.0) * out;
+                        double psiN[CB];
+                        if (f == s) {
+#pragma unroll
+                            for (int c = 0; c < CB; ++c) psiN[c] = pfPsiN[c];
+                        } else {
+                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN);
+                        }
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) {
+                            const double dpsi = fabs(cen[c] - psiN[c]);
+                            if (fabs(out[c]) > dpsi) out[c] = fmin(dpsi / fabs(out[c]), 1.0) * out[c];
+                        }
                     }
                 }
             }
-            a.corr[(size_t)faceId * a.nComp + a.c0 + c] = out;
-            if (a.faceValue && type == FACE_INTERNAL)
-                a.faceValue[(size_t)faceId * a.nComp + a.c0 + c] = psi + out;
+            double* dst = a.corr + (size_t)faceId * a.nComp + a.c0;
+#pragma unroll
+            for (int c = 0; c < CB; ++c) dst[c] = out[c];
+            if (a.faceValue && type == FACE_INTERNAL) {
+                double* fv = a.faceValue + (size_t)faceId * a.nComp + a.c0;
+#pragma unroll
+                for (int c = 0; c < CB; ++c) fv[c] = cen[c] + out[c];
+            }
         }
-        groupSync(G, grp);
-        if (gl == 0) mbarArrive(bars + (slot * 3 + 2) * 8);
-        slot += NG;
-        while (slot >= nSlots) {
-            slot -= nSlots;
-            ++round;
-        }
+        __syncwarp();
+        if (valid && s == 0) mbarArrive(bar + 16);
     }
 }
-
 }  // namespace
 
 namespace {
@@ -550,51 +645,56 @@ __global__ void patch_kernel(const PatchKernelArgs a) {
 
 }  // namespace
 
-size_t groupScratchBytes(int K, int CB, int maxTotN, int maxRows, int maxSt, int maxFc) {
-    return scratchLayout(K, CB, maxTotN, maxRows, maxSt, maxFc, nullptr, 0);
+size_t cellKernelSmemBytes(const CellKernelArgs& a) {
+    return (size_t)a.nSlots * a.slotBytes + (size_t)a.nSlots * 24 + 16;
 }
 
-size_t cellKernelSmemBytes(const CellKernelArgs& a, int CB) {
-    size_t s = (size_t)a.nSlots * a.slotBytes + (size_t)a.nSlots * 24 + 16;
-    s += (size_t)a.nGroups * groupScratchBytes(a.K, CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc);
-    return s;
-}
+bool cellKernelSupportsK(int K) { return K == 5 || K == 9 || K == 14 || K == 19; }
 
 namespace {
-template <int KT, int CB>
+template <int K, int CB, int CELLS, int D>
 int launchT(const CellKernelArgs& a, int gridBlocks, size_t smemBytes, cudaStream_t st) {
     static size_t configured = 0;  // per instantiation
     if (smemBytes > configured) {
-        if (cudaFuncSetAttribute(weno_cell_kernel<KT, CB>,
+        if (cudaFuncSetAttribute(weno_cell_kernel<K, CB, CELLS, D>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smemBytes) != cudaSuccess)
             return 1;
         configured = smemBytes;
     }
-    const int threads = (a.nGroups * a.G + 1) * 32;
-    weno_cell_kernel<KT, CB><<<gridBlocks, threads, smemBytes, st>>>(a);
+    const int threads = (a.nWarps + 1) * 32;
+    weno_cell_kernel<K, CB, CELLS, D><<<gridBlocks, threads, smemBytes, st>>>(a);
     return 0;
 }
-template <int KT>
+template <int K, int D>
 int launchK(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes, cudaStream_t st) {
+    if (a.cellsPerWarp == 4) {
+        switch (CB) {
+            case 1: return launchT<K, 1, 4, D>(a, gridBlocks, smemBytes, st);
+            case 2: return launchT<K, 2, 4, D>(a, gridBlocks, smemBytes, st);
+            default: return launchT<K, 3, 4, D>(a, gridBlocks, smemBytes, st);
+        }
+    }
     switch (CB) {
-        case 1: return launchT<KT, 1>(a, gridBlocks, smemBytes, st);
-        case 2: return launchT<KT, 2>(a, gridBlocks, smemBytes, st);
-        default: return launchT<KT, 3>(a, gridBlocks, smemBytes, st);
+        case 1: return launchT<K, 1, 1, D>(a, gridBlocks, smemBytes, st);
+        case 2: return launchT<K, 2, 1, D>(a, gridBlocks, smemBytes, st);
+        default: return launchT<K, 3, 1, D>(a, gridBlocks, smemBytes, st);
     }
 }
 }  // namespace
 
-// K is a template parameter for the common polynomial spaces (3-D order 2: 9,
-// 3-D order 3: 19, 2-D order 2: 5); anything else runs the runtime-K instance.
+// K (the polynomial space) is a template parameter because every lane keeps the
+// K x CB coefficients of its stencil in registers: 3-D order 2 and 2-D order 3: 9,
+// 3-D order 3: 19, 2-D order 2: 5, 2-D order 4: 14.
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st) {
-    if ((a.nGroups * a.G + 1) * 32 > MAX_THREADS) return 1;
+    if ((a.nWarps + 1) * 32 > MAX_THREADS || (a.cellsPerWarp != 4 && a.cellsPerWarp != 1)) return 1;
     switch (a.K) {
-        case 9: return launchK<9>(a, CB, gridBlocks, smemBytes, st);
-        case 19: return launchK<19>(a, CB, gridBlocks, smemBytes, st);
-        case 5: return launchK<5>(a, CB, gridBlocks, smemBytes, st);
-        default: return launchK<0>(a, CB, gridBlocks, smemBytes, st);
+        case 5: return launchK<5, 7>(a, CB, gridBlocks, smemBytes, st);
+        case 9: return launchK<9, 7>(a, CB, gridBlocks, smemBytes, st);
+        case 14: return launchK<14, 4>(a, CB, gridBlocks, smemBytes, st);
+        case 19: return launchK<19, 4>(a, CB, gridBlocks, smemBytes, st);
+        default: return 1;
     }
 }
 

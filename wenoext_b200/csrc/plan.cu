@@ -41,9 +41,9 @@ int upload(T** dptr, const T* h, size_t n) {
 }
 
 struct ExpandArgs {
-    int32_t nCells, nFaces, nInternalFaces, K, cube, L;
+    int32_t nCells, nFaces, nInternalFaces, K, cube;
     const RecInfo* recInfo;
-    const int32_t *cellNSt, *cellTotN, *cellNFc;
+    const int32_t *cellNSt, *cellNmax, *cellNFc;
     const int64_t *cellStencilStart, *stencilEntryStart;
     const int32_t *stencilsID, *cellToProcMap, *stencilMatrix;
     const int64_t* matrixStart;
@@ -61,46 +61,24 @@ struct ExpandArgs {
 
 // One warp per cell: copies the de-duplicated matrices and the per-cell / per-face
 // setup data into the cell's record (bitwise copies, so parity is unaffected). The
-// record memory is zero-filled beforehand (padding of the interleaved rounds).
+// record memory is zero-filled beforehand (columns beyond a stencil's size).
 __global__ void expand_records_kernel(const ExpandArgs a) {
     const int cell = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const int lane = threadIdx.x & 31;
     if (cell >= a.nCells) return;
-    const int K = a.K, L = a.L;
+    const int K = a.K, KP = K / 2;
     unsigned char* rec = a.records + a.recInfo[cell].off;
-    const int nSt = a.cellNSt[cell], totN = a.cellTotN[cell], nFc = a.cellNFc[cell];
-    const RecLayout lay = recLayout(K, L, nSt, totN, nFc);
-    int32_t* Ns = reinterpret_cast<int32_t*>(rec + lay.oN);
-    int32_t* stOff = reinterpret_cast<int32_t*>(rec + lay.oStOff);
-    int32_t* rnd = reinterpret_cast<int32_t*>(rec + lay.oRnd);
+    const int nSt = a.cellNSt[cell], Nmax = a.cellNmax[cell], nFc = a.cellNFc[cell];
+    const RecHeader lay = recLayout(K, nSt, Nmax, nFc);
+    int32_t* Ns = reinterpret_cast<int32_t*>(rec + sizeof(RecHeader));
     int32_t* idx = reinterpret_cast<int32_t*>(rec + lay.oIdx);
-    int32_t* faceI = reinterpret_cast<int32_t*>(rec + lay.oFaceI);
+    int32_t* faceI = reinterpret_cast<int32_t*>(rec + lay.oFace);
     double* Bm = reinterpret_cast<double*>(rec + lay.oB);
-    double* faceD = reinterpret_cast<double*>(rec + lay.oFaceD);
-    double* quirk = reinterpret_cast<double*>(rec + lay.oQuirk);
-    double* A2 = reinterpret_cast<double*>(rec + lay.metaBytes);
-    const int nRows = nSt * K;
-    // lane 0: stencil sizes, prefix, and the per-round interleave geometry
-    if (lane == 0 && nSt > 0) {
-        int live = 0, eOff = 0;
-        for (int64_t s = a.cellStencilStart[cell]; s < a.cellStencilStart[cell + 1]; ++s) {
-            const int m = a.stencilMatrix[s];
-            if (m < 0) continue;
-            Ns[live] = a.matrixCols[m];
-            stOff[live] = eOff;
-            eOff += a.matrixCols[m];
-            live++;
-        }
-        int base = 0;
-        for (int r = 0; r * L < nRows; ++r) {
-            const int p0 = r * L, p1 = min(nRows, p0 + L);
-            int jmax = 0;
-            for (int s = p0 / K; s <= (p1 - 1) / K; ++s) jmax = max(jmax, Ns[s]);
-            rnd[2 * r] = jmax;
-            rnd[2 * r + 1] = base;
-            base += jmax * (p1 - p0);
-        }
-    }
+    double* faceD = Bm + K * K;
+    double* quirk = faceD + (size_t)nFc * (K + 1);
+    double* pairs = reinterpret_cast<double*>(rec + lay.metaBytes);
+    double* single = pairs + (size_t)Nmax * KP * nSt * 2;
+    for (int i = lane; i < Nmax * nSt; i += 32) idx[i] = cell;  // unused entries: a valid index
     __syncwarp();
     bool halo = false;
     if (nSt > 0) {
@@ -110,14 +88,15 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
             if (m < 0) continue;
             const int N = a.matrixCols[m];
             const double* src = a.matrixData + a.matrixStart[m];
+            if (lane == 0) Ns[live] = N;
             for (int i = lane; i < K * N; i += 32) {
                 const int k = i / N, j = i - k * N;
-                const int p = live * K + k, r = p / L;
-                const int R = min(L, nRows - r * L);
-                A2[rnd[2 * r + 1] + j * R + (p - r * L)] = src[i];
+                if (k < 2 * KP)
+                    pairs[((size_t)(j * KP + (k >> 1)) * nSt + live) * 2 + (k & 1)] = src[i];
+                else
+                    single[(size_t)j * nSt + live] = src[i];
             }
             const int64_t e0 = a.stencilEntryStart[s];
-            const int eOff = stOff[live];
             for (int j = lane; j < N; j += 32) {
                 const int32_t id = a.stencilsID[e0 + 1 + j];
                 const int32_t pm = a.cellToProcMap ? a.cellToProcMap[e0 + 1 + j] : -1;
@@ -126,7 +105,7 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
                     flat = a.nCells + (int32_t)a.haloOff[pm] + id;
                     halo = true;
                 }
-                idx[eOff + j] = flat;
+                idx[j * nSt + live] = flat;
             }
             live++;
         }
@@ -155,18 +134,16 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
             fd[k] = a.intBasTrans[((size_t)f * 2 + side) * a.cube + a.enumIdx[k]];
         if (lane == 0) {
             fd[K] = a.refFacAr[f];
-            faceI[fOut * 3 + 0] = f;
-            faceI[fOut * 3 + 1] = other;
-            faceI[fOut * 3 + 2] = side | (type << FACE_TYPE_SHIFT);
+            faceI[fOut * 4 + 0] = f;
+            faceI[fOut * 4 + 1] = other;
+            faceI[fOut * 4 + 2] = side | (type << FACE_TYPE_SHIFT);
+            faceI[fOut * 4 + 3] = 0;
         }
         fOut++;
     }
     halo = __any_sync(0xffffffffu, halo);
     if (lane == 0) {
-        RecHeader h;
-        h.nSt = nSt;
-        h.nFc = nFc;
-        h.totN = totN;
+        RecHeader h = lay;
         h.flags = halo ? 1 : 0;
         *reinterpret_cast<RecHeader*>(rec) = h;
         a.cellHasHalo[cell] = halo ? 1 : 0;
@@ -233,6 +210,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     P->myProc = d->myProc;
     P->patches.assign(d->patches, d->patches + d->nPatches);
     if (const char* e = getenv("WENOEXT_WARPS")) P->cfgWarps = atoi(e);
+    if (const char* e = getenv("WENOEXT_CELLS")) P->cfgCells = atoi(e);
     if (const char* e = getenv("WENOEXT_SLOTS")) P->cfgSlots = atoi(e);
     if (const char* e = getenv("WENOEXT_GRID")) P->cfgGrid = atoi(e);
     if (const char* e = getenv("WENOEXT_SMEM_KB")) P->cfgSmemKB = atoi(e);
@@ -288,12 +266,17 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     P->nSendTotal = P->sendOff[P->nProcs];
 
     // per-cell record sizes
+    if (!cellKernelSupportsK(K)) {
+        setError("unsupported polynomial space (nDvt must be 5, 9, 14 or 19)");
+        delete P;
+        return WENOEXT_ERR_INVALID;
+    }
     const int nC = d->nCells;
-    std::vector<int32_t> cellNSt(nC), cellTotN(nC), cellNFc(nC);
+    std::vector<int32_t> cellNSt(nC), cellNmax(nC), cellNFc(nC);
     std::vector<RecInfo> recInfo(nC);
-    int64_t algFixed = 0, flopsPerComp = 0, nLive = 0;
+    int64_t algFixed = 0, flopsPerComp = 0, nLive = 0, recOff = 0;
     for (int c = 0; c < nC; ++c) {
-        int nSt = 0, totN = 0;
+        int nSt = 0, totN = 0, Nmax = 0;
         const int64_t s0 = d->cellStencilStart[c], sE = d->cellStencilStart[c + 1];
         const bool empty = d->stencilsID[d->stencilEntryStart[s0]] == WENOEXT_CELL_EMPTY;
         if (!empty)
@@ -308,16 +291,29 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
                 }
                 nSt++;
                 totN += N;
+                Nmax = std::max(Nmax, N);
             }
         int nFc = 0;
         for (int i = d->cellFaceStart[c]; i < d->cellFaceStart[c + 1]; ++i) {
             const int f = d->cellFaces[i];
             if (f < P->nInt || bfType[f - P->nInt] >= 0) nFc++;
         }
+        if (nSt > 32) {
+            setError("more than 32 stencils in a cell is not supported");
+            delete P;
+            return WENOEXT_ERR_INVALID;
+        }
         cellNSt[c] = nSt;
-        cellTotN[c] = totN;
+        cellNmax[c] = Nmax;
         cellNFc[c] = nFc;
-        P->maxTotN = std::max(P->maxTotN, totN);
+        const RecHeader lay = recLayout(K, nSt, Nmax, nFc);
+        const int64_t tot = (int64_t)lay.metaBytes + recMatrixBytes(K, nSt, Nmax);
+        recInfo[c].off = recOff;
+        recInfo[c].totBytes = (int32_t)tot;
+        recInfo[c].metaBytes = lay.metaBytes;
+        recOff += tot;
+        P->maxRecordBytes = std::max(P->maxRecordBytes, tot);
+        P->maxN = std::max(P->maxN, Nmax);
         P->maxSt = std::max(P->maxSt, nSt);
         P->maxFc = std::max(P->maxFc, nFc);
         nLive += nSt;
@@ -325,44 +321,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         flopsPerComp += (int64_t)2 * K * totN + (int64_t)nSt * (2 * K * K + 2 * K) + 2 * nSt * K;
     }
     P->maxSt = std::max(P->maxSt, 1);
-    P->maxFc = std::max(P->maxFc, 1);
-    P->maxTotN = std::max(P->maxTotN, 1);
-    // warps per cell group: one lane per stacked matrix row (stencil, coefficient)
-    // when that fits a group of at most 8 warps; fixed here because the matrix
-    // part of the records is interleaved for it (device_plan.h)
-    P->G = std::min(8, std::max(1, (P->maxSt * K + 31) / 32));
-    if (const char* e = getenv("WENOEXT_G")) P->G = std::min(8, std::max(1, atoi(e)));
-    const int L = P->G * 32;
-    P->maxRows = P->maxSt * K;
-    {
-        int64_t off = 0;
-        std::vector<int32_t> Ns;
-        for (int c = 0; c < nC; ++c) {
-            Ns.clear();
-            if (cellNSt[c] > 0)
-                for (int64_t s = d->cellStencilStart[c]; s < d->cellStencilStart[c + 1]; ++s) {
-                    const int m = d->stencilMatrix[s];
-                    if (m >= 0 && d->stencilsID[d->stencilEntryStart[s]] != WENOEXT_CELL_DELETED)
-                        Ns.push_back(d->matrixCols[m]);
-                }
-            const int nSt = cellNSt[c], nRows = nSt * K;
-            int64_t aDoubles = 0;
-            for (int p0 = 0; p0 < nRows; p0 += L) {
-                const int p1 = std::min(nRows, p0 + L);
-                int jmax = 0;
-                for (int s = p0 / K; s <= (p1 - 1) / K; ++s) jmax = std::max(jmax, Ns[s]);
-                aDoubles += (int64_t)jmax * (p1 - p0);
-            }
-            const RecLayout lay = recLayout(K, L, nSt, cellTotN[c], cellNFc[c]);
-            const int64_t tot = (lay.metaBytes + aDoubles * 8 + 15) / 16 * 16;
-            recInfo[c].off = off;
-            recInfo[c].totBytes = (int32_t)tot;
-            recInfo[c].metaBytes = lay.metaBytes;
-            off += tot;
-            P->maxRecordBytes = std::max(P->maxRecordBytes, tot);
-        }
-        P->recordBytesTotal = off;
-    }
+    P->recordBytesTotal = recOff;
     const int64_t nWritten = (int64_t)P->nInt + nCoupled;
     algFixed += nWritten * (8 * K + 24);
     flopsPerComp += nWritten * 2 * K;
@@ -382,7 +341,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     };
     int rc = 0;
     RecInfo* dRecInfo = nullptr;
-    int32_t *dNSt, *dTotN, *dNFc, *dSID, *dC2P = nullptr, *dSM, *dMC, *dNei = nullptr, *dCFS, *dCF,
+    int32_t *dNSt, *dNmax, *dNFc, *dSID, *dC2P = nullptr, *dSM, *dMC, *dNei = nullptr, *dCFS, *dCF,
                                   *dEnum, *dBfNbr = nullptr;
     int64_t *dCSS, *dSES, *dMS, *dHaloOff;
     double *dMD, *dB, *dIBT, *dRFA;
@@ -390,7 +349,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     rc = rc ? rc : upload(&dRecInfo, recInfo.data(), recInfo.size());
     P->recInfo = dRecInfo;
     rc = rc ? rc : up(&dNSt, cellNSt.data(), (size_t)nC);
-    rc = rc ? rc : up(&dTotN, cellTotN.data(), (size_t)nC);
+    rc = rc ? rc : up(&dNmax, cellNmax.data(), (size_t)nC);
     rc = rc ? rc : up(&dNFc, cellNFc.data(), (size_t)nC);
     rc = rc ? rc : up(&dCSS, d->cellStencilStart, (size_t)nC + 1);
     rc = rc ? rc : up(&dSES, d->stencilEntryStart, (size_t)d->nStencils + 1);
@@ -427,9 +386,8 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     }
     if (!rc) {
         ea.recInfo = dRecInfo;
-        ea.L = L;
         ea.cellNSt = dNSt;
-        ea.cellTotN = dTotN;
+        ea.cellNmax = dNmax;
         ea.cellNFc = dNFc;
         ea.cellStencilStart = dCSS;
         ea.stencilEntryStart = dSES;
@@ -703,37 +661,43 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     a.pExp = (uint32_t)P->p;  // WENOCoeff.H:149: double -> unsigned
     a.dm = P->dm;
     a.eps = P->eps;
-    a.maxTotN = P->maxTotN;
-    a.maxSt = P->maxSt;
-    a.maxFc = P->maxFc;
-    a.maxRows = P->maxRows;
-    a.G = P->G;
-    a.slotBytes = (int)((P->maxRecordBytes + 127) / 128 * 128);
-    // Shared-memory budget: ring slots + per-group scratch. A slot is held while its
-    // cell is being computed, so the ring needs one slot per group plus enough
-    // slots in flight to cover the HBM latency-bandwidth product of one SM
-    // (~64 KB); take as many groups as that allows (at most 16 consumer warps).
-    const size_t budget = (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 256;
-    const size_t scratch = groupScratchBytes(P->K, c.CB, a.maxTotN, a.maxRows, a.maxSt, a.maxFc);
-    const int inflight = std::max(2, std::min(8, (int)((65536 + a.slotBytes - 1) / a.slotBytes)));
-    int groups = std::max(1, 16 / P->G);
-    if (P->cfgWarps > 0) groups = std::min(groups, P->cfgWarps);
-    int slots = 0;
-    for (; groups >= 1; --groups) {
-        const size_t fixed = (size_t)groups * scratch + 16;
-        slots = budget > fixed ? (int)((budget - fixed) / ((size_t)a.slotBytes + 24)) : 0;
-        if (slots >= groups + inflight || (groups == 1 && slots >= 1)) break;
+    a.maxN = P->maxN;
+    a.nVals = (int32_t)(P->nCells + P->nHaloTotal);
+    a.nFaces = P->nFaces;
+#ifdef WENOEXT_KDEBUG
+    if (!P->dbg) {
+        CUDA_TRY(cudaMalloc((void**)&P->dbg, 64));
     }
-    if (groups < 1) groups = 1;
+    CUDA_TRY(cudaMemsetAsync(P->dbg, 0, 64, c.st));
+    a.dbg = P->dbg;
+#endif
+    a.slotBytes = (int)((P->maxRecordBytes + 127) / 128 * 128);
+    // Launch geometry. A consumer warp takes cellsPerWarp consecutive cells per
+    // pass (one lane per (cell, stencil)), so the ring must hold at least one pass;
+    // the rest of the slots are records in flight (an SM needs ~64 KB in flight to
+    // cover the HBM latency-bandwidth product). No scratch shared memory.
+    const size_t budget =
+        (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 64;
+    int slots = (int)(budget / ((size_t)a.slotBytes + 24));
     if (P->cfgSlots > 0) slots = std::min(slots, P->cfgSlots);
-    if (slots < 1) {
-        setError("cell record does not fit in shared memory (polynomial order too high)");
+    slots = std::min(slots, 128);
+    int cpw = (P->maxSt <= 8 && slots >= 8) ? 4 : 1;
+    if (P->cfgCells > 0) cpw = P->cfgCells;
+    if (slots < cpw || (cpw != 4 && cpw != 1) || P->maxSt > 32 / cpw) {
+        setError("cell records do not fit the shared-memory ring (polynomial order too high)");
         return WENOEXT_ERR_INVALID;
     }
-    slots = std::min(slots, 64);
-    a.nSlots = slots;
-    a.nGroups = groups;
-    const size_t smem = cellKernelSmemBytes(a, c.CB);
+    // Slot affinity: the ring size is a multiple of (warps x cells per pass), so a
+    // slot is always consumed by the same warp, round after round. A consumer can
+    // then never wait on round r of a slot before round r-1 has completed (an
+    // mbarrier parity wait cannot tell those apart).
+    const int maxW = std::max(1, std::min(7, P->cfgWarps > 0 ? P->cfgWarps : 7));
+    const int nw = std::min(maxW, slots / cpw);
+    const int m = slots / (cpw * nw);
+    a.cellsPerWarp = cpw;
+    a.nWarps = nw;
+    a.nSlots = cpw * nw * m;
+    const size_t smem = cellKernelSmemBytes(a);
     const int nTiles = (nWork + 31) / 32;
     int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);
     cudaEvent_t t0 = nullptr, t1 = nullptr;
@@ -756,6 +720,16 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
         return WENOEXT_ERR_CUDA;
     }
     if (t1) cudaEventRecord(t1, c.st);
+#ifdef WENOEXT_KDEBUG
+    {
+        int32_t h[16];
+        cudaError_t e = cudaMemcpyAsync(h, P->dbg, 64, cudaMemcpyDeviceToHost, c.st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c.st);
+        fprintf(stderr, "[kdebug] sync=%s code=%d :", cudaGetErrorString(e), h[0]);
+        for (int i = 1; i < 16; ++i) fprintf(stderr, " %d", h[i]);
+        fprintf(stderr, "\n");
+    }
+#endif
     P->lastLaunches++;
     CUDA_TRY(cudaGetLastError());
     return 0;
