@@ -24,11 +24,14 @@
 //                              enumeration order (WENOUpwindFit.C:304-319), refFacAr()[f]
 //   double quirk[K]            intBasTrans()[cellI][1] compacted (WENOUpwindFit01.C:125)
 //   pad to 16 B                                          -> metaBytes
-//   MATRIX PART  (LSmatrix()[cell][s], bitwise copies, permuted)
-//   double2 pairs[Nmax][K/2][nSt]   (A_s[2q][j], A_s[2q+1][j])
-//   double  single[Nmax][nSt]       A_s[K-1][j]            (K odd only)
-//   zero where j >= N_s (only when stencil sizes differ, i.e. bestConditioned)
-//   pad to 16 B                                          -> totBytes
+//   MATRIX PART  (LSmatrix()[cell][s], bitwise copies, permuted), streamed in
+//   CHUNKS of D = chunkCols(K) columns so that shared memory is released as the
+//   columns are consumed. Chunk ch holds columns [ch*D, min(Nmax, ch*D+D)):
+//     double2 pairs[cols][K/2][nSt]   (A_s[2q][j], A_s[2q+1][j])
+//     double  single[cols][nSt]       A_s[K-1][j]            (K odd only)
+//     zero where j >= N_s (only when stencil sizes differ, i.e. bestConditioned)
+//     pad to 16 B
+//                                                        -> totBytes
 // Only internal and coupled-patch faces are listed (others get zero correction).
 #pragma once
 #include <cuda_runtime.h>
@@ -47,9 +50,15 @@ struct RecHeader {
 // per cell: where its record lives (one 16-byte load for the TMA producer)
 struct RecInfo {
     int64_t off;        // byte offset of the record
-    int32_t totBytes;   // whole record
     int32_t metaBytes;  // meta part (multiple of 16)
+    int16_t nSt, Nmax;  // chunk sizes follow from these
 };
+
+// columns per matrix chunk (also the unroll depth of the kernel's column loop)
+__host__ __device__ constexpr int chunkCols(int K) { return K <= 9 ? 7 : 4; }
+__host__ __device__ inline int chunkBytes(int K, int nSt, int cols) {
+    return (cols * nSt * K * 8 + 15) & ~15;
+}
 
 // kind bits of a listed face
 enum : int32_t {
@@ -78,7 +87,8 @@ __host__ __device__ inline RecHeader recLayout(int K, int nSt, int Nmax, int nFc
     return h;
 }
 __host__ __device__ inline int recMatrixBytes(int K, int nSt, int Nmax) {
-    return (Nmax * nSt * K * 8 + 15) & ~15;
+    const int D = chunkCols(K);
+    return (Nmax / D) * chunkBytes(K, nSt, D) + chunkBytes(K, nSt, Nmax % D);
 }
 
 // Arguments of the fused cell kernel (by value, __grid_constant__).
@@ -101,9 +111,11 @@ struct CellKernelArgs {
     uint32_t pExp;
     double dm, eps;
     // launch geometry
-    int32_t cellsPerWarp;      // 4, 2 or 1: 32 / cellsPerWarp stencil lanes per cell
+    int32_t cellsPerWarp;      // 4 or 1: 32 / cellsPerWarp stencil lanes per cell
     int32_t nWarps;            // consumer warps per CTA
-    int32_t nSlots, slotBytes; // shared-memory ring of records
+    int32_t nMetaSlots, metaSlotBytes;    // shared-memory ring of record meta parts
+    int32_t nChunkSlots, chunkSlotBytes;  // shared-memory ring of matrix chunks
+    int32_t nChunks;           // chunk positions per cell: ceil(maxN / chunkCols(K))
     int32_t maxN;              // max stencil columns in the plan
     // developer aid (only read when built with -DWENOEXT_KDEBUG): first violated
     // bounds check is recorded in dbg[0..15]

@@ -141,6 +141,28 @@ __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&
     }
 }
 
+__device__ __forceinline__ uint32_t ldsVolatileU32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void stsVolatileU32(uint32_t a, uint32_t v) {
+    asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+// Ring slot protocol. Slots are not bound to a consumer, so before waiting for
+// round r of a slot a consumer first waits until round r-1 has been RELEASED
+// (release counter): an mbarrier parity wait alone cannot tell "round r done"
+// from "round r-1 not done yet".
+__device__ __forceinline__ void slotWait(uint32_t fullBar, uint32_t relAddr, uint32_t round) {
+    while (ldsVolatileU32(relAddr) < round) {
+    }
+    mbarWait(fullBar, round & 1u);
+}
+__device__ __forceinline__ void slotRelease(uint32_t emptyBar, uint32_t relAddr, uint32_t round) {
+    stsVolatileU32(relAddr, round + 1u);
+    mbarArrive(emptyBar);
+}
+
 template <int K, int CB, int CELLS, int D>
 __global__ void __launch_bounds__(MAX_THREADS, 1)
     weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
@@ -151,19 +173,21 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     const int NW = a.nWarps;
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int nSlots = a.nSlots;
+    const int nMeta = a.nMetaSlots, nChunk = a.nChunkSlots, CH = a.nChunks;
 
-    const uint32_t ring = smemAddr(smem);
-    const uint32_t bars = ring + (uint32_t)nSlots * a.slotBytes;  // per slot: fullMeta, fullA, empty
+    // shared memory: meta ring | chunk ring | mbarriers | release counters
+    const uint32_t metaRing = smemAddr(smem);
+    const uint32_t chunkRing = metaRing + (uint32_t)nMeta * a.metaSlotBytes;
+    const uint32_t barMetaFull = chunkRing + (uint32_t)nChunk * a.chunkSlotBytes;
+    const uint32_t barMetaEmpty = barMetaFull + (uint32_t)nMeta * 8;
+    const uint32_t barChunkFull = barMetaEmpty + (uint32_t)nMeta * 8;
+    const uint32_t barChunkEmpty = barChunkFull + (uint32_t)nChunk * 8;
+    const uint32_t relMeta = barChunkEmpty + (uint32_t)nChunk * 8;
+    const uint32_t relChunk = relMeta + (uint32_t)nMeta * 4;
 
-#ifdef WENOEXT_KDEBUG
-    if (threadIdx.x == 0 && blockIdx.x == 0) g_dbg = a.dbg;
-    if (threadIdx.x == 0 && blockIdx.x == 0) { a.dbg[13] = (int)ring; a.dbg[14] = (int)bars; a.dbg[15] = nSlots; }
-#endif
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < 3 * nSlots; ++s) mbarInit(bars + s * 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
+    for (int i = threadIdx.x; i < 2 * (nMeta + nChunk); i += blockDim.x) mbarInit(barMetaFull + i * 8, 1);
+    for (int i = threadIdx.x; i < nMeta + nChunk; i += blockDim.x) stsVolatileU32(relMeta + i * 4, 0u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
 
     // static work split: tiles of TILE consecutive cells, round-robin over CTAs
@@ -180,42 +204,63 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     };
 
     if (warp == NW) {
-        // ===== producer warp: all lanes prefetch the record descriptors of the next
-        // 32 items, lane 0 waits for free slots and issues the bulk copies =====
+        // ===== producer warp. All lanes prefetch the record descriptors of the next
+        // 32 items. Per pass (CELLS consecutive items) lane l issues one bulk copy:
+        // l < CELLS the meta part of cell l, then chunk ch of cell c in the order the
+        // consumers need them (chunk-major). =====
         const uint64_t pol = evictFirstPolicy();
         auto fetch = [&](int n) {
             int4 r = make_int4(0, 0, 0, 0);
             if (n < nItems) r = __ldg(reinterpret_cast<const int4*>(a.recInfo + itemToCell(n)));
             return r;
         };
+        const int perPass = CELLS * (1 + CH);  // bulk copies per pass
         int4 cur = fetch(lane);
-        int slot = 0, round = 0;
         for (int n0 = 0; n0 < nItems; n0 += 32) {
             const int4 nxt = fetch(n0 + 32 + lane);
-            const int cnt = min(32, nItems - n0);
-            for (int i = 0; i < cnt; ++i) {
-                const uint32_t offLo = (uint32_t)__shfl_sync(0xffffffffu, cur.x, i);
-                const uint32_t offHi = (uint32_t)__shfl_sync(0xffffffffu, cur.y, i);
-                const int tot = __shfl_sync(0xffffffffu, cur.z, i);
-                const int meta = __shfl_sync(0xffffffffu, cur.w, i);
-                if (lane == 0) {
-                    const uint64_t off = ((uint64_t)offHi << 32) | offLo;
-                    if (round > 0) mbarWait(bars + (slot * 3 + 2) * 8, (round - 1) & 1);
-                    const uint32_t dst = ring + (uint32_t)slot * a.slotBytes;
-                    const uint32_t bMeta = bars + (slot * 3) * 8, bA = bMeta + 8;
-                    mbarArriveExpectTx(bMeta, (uint32_t)meta);
-                    tmaLoad1D(dst, a.records + off, (uint32_t)meta, bMeta, pol);
-                    const int aB = tot - meta;
-                    if (aB > 0) {
-                        mbarArriveExpectTx(bA, (uint32_t)aB);
-                        tmaLoad1D(dst + meta, a.records + off + meta, (uint32_t)aB, bA, pol);
-                    } else {
-                        mbarArrive(bA);
+            for (int pp = 0; pp < 32 / CELLS && n0 + pp * CELLS < nItems; ++pp) {
+                for (int r0 = 0; r0 < perPass; r0 += 32) {
+                    const int r = r0 + lane;
+                    const int role = r / CELLS;  // 0: meta, 1 + ch: chunk ch
+                    const int c = r - role * CELLS;
+                    const int srcLane = pp * CELLS + c;
+                    const uint32_t offLo = (uint32_t)__shfl_sync(0xffffffffu, cur.x, srcLane);
+                    const uint32_t offHi = (uint32_t)__shfl_sync(0xffffffffu, cur.y, srcLane);
+                    const int meta = __shfl_sync(0xffffffffu, cur.z, srcLane);
+                    const int packed = __shfl_sync(0xffffffffu, cur.w, srcLane);
+                    const int item = n0 + srcLane;
+                    if (r < perPass && item < nItems) {
+                        const unsigned char* src = a.records + (((uint64_t)offHi << 32) | offLo);
+                        const int nSt = packed & 0xffff, Nmax = (packed >> 16) & 0xffff;
+                        if (role == 0) {
+                            const int slot = item % nMeta;
+                            const uint32_t round = (uint32_t)(item / nMeta);
+                            if (round > 0) mbarWait(barMetaEmpty + slot * 8, (round - 1) & 1u);
+                            const uint32_t fb = barMetaFull + slot * 8;
+                            mbarArriveExpectTx(fb, (uint32_t)meta);
+                            tmaLoad1D(metaRing + (uint32_t)slot * a.metaSlotBytes, src, (uint32_t)meta,
+                                      fb, pol);
+                        } else {
+                            const int ch = role - 1;
+                            const int pass = item / CELLS;
+                            const int q = (pass * CH + ch) * CELLS + c;
+                            const int slot = q % nChunk;
+                            const uint32_t round = (uint32_t)(q / nChunk);
+                            if (round > 0) mbarWait(barChunkEmpty + slot * 8, (round - 1) & 1u);
+                            const uint32_t fb = barChunkFull + slot * 8;
+                            const int cols = min(D, Nmax - ch * D);
+                            if (cols > 0) {
+                                const uint32_t bytes = (uint32_t)chunkBytes(K, nSt, cols);
+                                mbarArriveExpectTx(fb, bytes);
+                                tmaLoad1D(chunkRing + (uint32_t)slot * a.chunkSlotBytes,
+                                          src + meta + (size_t)ch * chunkBytes(K, nSt, D), bytes, fb,
+                                          pol);
+                            } else {
+                                mbarArrive(fb);  // nothing to load (empty cell / short stencils)
+                            }
+                        }
                     }
-                }
-                if (++slot == nSlots) {
-                    slot = 0;
-                    ++round;
+                    __syncwarp();
                 }
             }
             cur = nxt;
@@ -230,21 +275,20 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     const bool fit01 = a.scheme == 1;
     const bool fitBounded = a.scheme == 0 && a.bounded;
 
-    for (int base = warp * CELLS; base < nItems; base += NW * CELLS) {
-        const int item = base + cslot;
+    for (int pass = warp; pass * CELLS < nItems; pass += NW) {
+        const int item = pass * CELLS + cslot;
         const bool valid = item < nItems;
-        const int slot = item % nSlots;
-        const uint32_t parity = (uint32_t)(item / nSlots) & 1u;
-        const uint32_t rec = ring + (uint32_t)slot * a.slotBytes;
-        const uint32_t bar = bars + (uint32_t)(slot * 3) * 8;
+        const int mslot = item % nMeta;
+        const uint32_t mround = (uint32_t)(item / nMeta);
+        const uint32_t rec = metaRing + (uint32_t)mslot * a.metaSlotBytes;
         const int cell = valid ? itemToCell(item) : 0;
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen);
 
-        if (valid) mbarWait(bar, parity);
+        if (valid) slotWait(barMetaFull + mslot * 8, relMeta + mslot * 4, mround);
         __syncwarp();
         int nSt = 0, nFc = 0, Nmax = 0;
-        uint32_t oIdx = 0, oFace = 0, oB = 0, metaBytes = 0;
+        uint32_t oIdx = 0, oFace = 0, oB = 0;
         if (valid) {
             const int4 h0 = lds128i(rec), h1 = lds128i(rec + 16);
             nSt = h0.x;
@@ -253,24 +297,22 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             oIdx = h1.x;
             oFace = h1.y;
             oB = h1.z;
-            metaBytes = h1.w;
         }
 #ifdef WENOEXT_KDEBUG
         if (valid && (nSt < 0 || nSt > SS || nFc < 0 || nFc > 64 || Nmax < 0 || Nmax > a.maxN ||
-                      oIdx > (uint32_t)a.slotBytes || oFace > (uint32_t)a.slotBytes ||
-                      oB > (uint32_t)a.slotBytes || metaBytes > (uint32_t)a.slotBytes)) {
+                      oIdx > (uint32_t)a.metaSlotBytes || oFace > (uint32_t)a.metaSlotBytes ||
+                      oB > (uint32_t)a.metaSlotBytes)) {
             if (atomicCAS(a.dbg, 0, 1) == 0) {
-                a.dbg[1] = item; a.dbg[2] = slot; a.dbg[3] = (int)parity; a.dbg[4] = cell;
+                a.dbg[1] = item; a.dbg[2] = mslot; a.dbg[3] = (int)mround; a.dbg[4] = cell;
                 a.dbg[5] = nSt; a.dbg[6] = nFc; a.dbg[7] = Nmax; a.dbg[8] = (int)oIdx;
-                a.dbg[9] = (int)metaBytes; a.dbg[10] = blockIdx.x; a.dbg[11] = threadIdx.x;
-                a.dbg[12] = nItems;
+                a.dbg[10] = blockIdx.x; a.dbg[11] = threadIdx.x; a.dbg[12] = nItems;
             }
             nSt = nFc = Nmax = 0;
         }
 #endif
         const bool act = s < nSt;
         const int N = act ? lds32(rec + (uint32_t)sizeof(RecHeader) + s * 4) : 0;
-        const int Nloop = __reduce_max_sync(0xffffffffu, Nmax);
+        const int Nw = __reduce_max_sync(0xffffffffu, Nmax);
 
         // first face of this lane: issue its global loads now, consumed at the end
         int4 pfFace = make_int4(0, -1, 0, 0);
@@ -283,7 +325,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #ifdef WENOEXT_KDEBUG
             if (pfFace.x < 0 || pfFace.x >= a.nFaces || pfFace.y < -1 || pfFace.y >= a.nVals) {
                 if (atomicCAS(a.dbg, 0, 3) == 0) {
-                    a.dbg[1] = item; a.dbg[2] = slot; a.dbg[3] = s; a.dbg[4] = cell;
+                    a.dbg[1] = item; a.dbg[2] = mslot; a.dbg[3] = s; a.dbg[4] = cell;
                     a.dbg[5] = pfFace.x; a.dbg[6] = pfFace.y; a.dbg[7] = pfFace.z; a.dbg[8] = nFc;
                 }
                 pfFace = make_int4(0, 0, 0, 0);
@@ -303,7 +345,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #ifdef WENOEXT_KDEBUG
                 if (id < 0 || id >= a.nVals) {
                     if (atomicCAS(a.dbg, 0, 2) == 0) {
-                        a.dbg[1] = item; a.dbg[2] = slot; a.dbg[3] = j; a.dbg[4] = cell;
+                        a.dbg[1] = item; a.dbg[2] = mslot; a.dbg[3] = j; a.dbg[4] = cell;
                         a.dbg[5] = nSt; a.dbg[6] = id; a.dbg[7] = N; a.dbg[8] = s;
                     }
                     id = 0;
@@ -326,50 +368,17 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
             for (int c = 0; c < CB; ++c) acc[k][c] = 0.0;
         const uint32_t pairStride = (uint32_t)nSt * 16;
-        const uint32_t colStride = pairStride * KP;
-        const uint32_t sglStride = (uint32_t)nSt * 8;
-        uint32_t Ap = rec + metaBytes + (uint32_t)s * 16;
-        uint32_t Sp = rec + metaBytes + (uint32_t)Nmax * colStride + (uint32_t)s * 8;
-        // One column of this lane's matrix: K/2 128-bit loads (+1 64-bit), K*CB DFMAs
-        auto column = [&](const double (&b)[CB]) {
-            uint32_t ap = Ap;
-#pragma unroll
-            for (int q = 0; q < KP; ++q) {
-                const double2 av = lds128(ap);
-                ap += pairStride;
-#pragma unroll
-                for (int c = 0; c < CB; ++c) {
-                    acc[2 * q][c] = fma(av.x, b[c], acc[2 * q][c]);
-                    acc[2 * q + 1][c] = fma(av.y, b[c], acc[2 * q + 1][c]);
-                }
-            }
-            if constexpr (ODD) {
-                const double a1 = lds64(Sp);
-#pragma unroll
-                for (int c = 0; c < CB; ++c) acc[K - 1][c] = fma(a1, b[c], acc[K - 1][c]);
-            }
-        };
         // Fast path (uniform meshes): every active lane of the warp has the same number
         // of columns, a multiple of D -> no per-column predicate. Lanes without a
-        // stencil read the matrix of stencil 0 of the warp's first cell (finite data)
-        // against b == 0.
-        const bool uniform = __all_sync(0xffffffffu, N == Nloop || N == 0) && (Nloop % D) == 0;
-        uint32_t cStr = colStride, sStr = sglStride, pStr = pairStride;
-        {
-            const uint32_t have = __ballot_sync(0xffffffffu, N > 0);
-            const int src = have ? __ffs(have) - 1 : 0;
-            const uint32_t ApS = __shfl_sync(0xffffffffu, Ap, src);
-            const uint32_t SpS = __shfl_sync(0xffffffffu, Sp, src);
-            const uint32_t pS = __shfl_sync(0xffffffffu, pairStride, src);
-            if (uniform && N == 0) {
-                Ap = ApS;
-                Sp = SpS;
-                pStr = pS;
-                cStr = pS * KP;
-                sStr = pS / 2;
-            }
-        }
-        for (int j0 = 0; j0 < Nloop; j0 += D) {
+        // stencil read the chunk of the first lane that has one (finite data) against
+        // b == 0.
+        const bool uniform = __all_sync(0xffffffffu, N == Nw || N == 0) && (Nw % D) == 0;
+        const uint32_t have = __ballot_sync(0xffffffffu, N > 0);
+        const int srcLane = have ? __ffs(have) - 1 : 0;
+        const uint32_t pS = __shfl_sync(0xffffffffu, pairStride, srcLane);
+        const uint32_t pStr = (uniform && N == 0) ? pS : pairStride;
+        for (int ch = 0; ch < CH; ++ch) {
+            const int j0 = ch * D;
             double cu[D][CB];
 #pragma unroll
             for (int d = 0; d < D; ++d)
@@ -377,41 +386,71 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 for (int c = 0; c < CB; ++c) cu[d][c] = nx[d][c] - cen[c];
 #pragma unroll
             for (int d = 0; d < D; ++d) issue(j0 + D + d, nx[d]);
-            if (j0 == 0) {
-                if (valid) mbarWait(bar + 8, parity);
-                __syncwarp();
-            }
-            if (uniform) {
+            // this cell's chunk ch
+            const int q = (pass * CH + ch) * CELLS + cslot;
+            const int cs = q % nChunk;
+            const uint32_t cround = (uint32_t)(q / nChunk);
+            if (valid) slotWait(barChunkFull + cs * 8, relChunk + cs * 4, cround);
+            __syncwarp();
+            uint32_t Ap = chunkRing + (uint32_t)cs * a.chunkSlotBytes + (uint32_t)s * 16;
+            if (j0 < Nw) {
+                if (uniform) {
+                    const uint32_t ApS = __shfl_sync(0xffffffffu, Ap, srcLane);
+                    if (N == 0) Ap = ApS;
+                    uint32_t Sp = Ap - (N == 0 ? 0u : (uint32_t)s * 8) + (uint32_t)D * KP * pStr;
 #pragma unroll
-                for (int d = 0; d < D; ++d) {
-                    uint32_t ap = Ap;
+                    for (int d = 0; d < D; ++d) {
+                        uint32_t ap = Ap;
 #pragma unroll
-                    for (int q = 0; q < KP; ++q) {
-                        const double2 av = lds128(ap);
-                        ap += pStr;
+                        for (int q2 = 0; q2 < KP; ++q2) {
+                            const double2 av = lds128(ap);
+                            ap += pStr;
 #pragma unroll
-                        for (int c = 0; c < CB; ++c) {
-                            acc[2 * q][c] = fma(av.x, cu[d][c], acc[2 * q][c]);
-                            acc[2 * q + 1][c] = fma(av.y, cu[d][c], acc[2 * q + 1][c]);
+                            for (int c = 0; c < CB; ++c) {
+                                acc[2 * q2][c] = fma(av.x, cu[d][c], acc[2 * q2][c]);
+                                acc[2 * q2 + 1][c] = fma(av.y, cu[d][c], acc[2 * q2 + 1][c]);
+                            }
                         }
-                    }
-                    if constexpr (ODD) {
-                        const double a1 = lds64(Sp);
+                        if constexpr (ODD) {
+                            const double a1 = lds64(Sp);
 #pragma unroll
-                        for (int c = 0; c < CB; ++c)
-                            acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
+                            for (int c = 0; c < CB; ++c)
+                                acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
+                        }
+                        Ap += pStr * KP;
+                        Sp += pStr / 2;
                     }
-                    Ap += cStr;
-                    Sp += sStr;
-                }
-            } else {
+                } else {
+                    const int cols = min(D, Nmax - j0);  // columns stored in this chunk
+                    uint32_t Sp = Ap - (uint32_t)s * 8 + (uint32_t)(cols > 0 ? cols : 0) * KP * pairStride;
 #pragma unroll
-                for (int d = 0; d < D; ++d) {
-                    if (j0 + d < N) column(cu[d]);
-                    Ap += colStride;
-                    Sp += sglStride;
+                    for (int d = 0; d < D; ++d) {
+                        if (j0 + d < N) {
+                            uint32_t ap = Ap;
+#pragma unroll
+                            for (int q2 = 0; q2 < KP; ++q2) {
+                                const double2 av = lds128(ap);
+                                ap += pairStride;
+#pragma unroll
+                                for (int c = 0; c < CB; ++c) {
+                                    acc[2 * q2][c] = fma(av.x, cu[d][c], acc[2 * q2][c]);
+                                    acc[2 * q2 + 1][c] = fma(av.y, cu[d][c], acc[2 * q2 + 1][c]);
+                                }
+                            }
+                            if constexpr (ODD) {
+                                const double a1 = lds64(Sp);
+#pragma unroll
+                                for (int c = 0; c < CB; ++c)
+                                    acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
+                            }
+                        }
+                        Ap += pairStride * KP;
+                        Sp += pairStride / 2;
+                    }
                 }
             }
+            __syncwarp();
+            if (valid && s == 0) slotRelease(barChunkEmpty + cs * 8, relChunk + cs * 4, cround);
         }
         // phase 2: IS = c^T (B c) per component                  (WENOCoeff.C:190-196)
         double g[CB];
@@ -575,7 +614,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             }
         }
         __syncwarp();
-        if (valid && s == 0) mbarArrive(bar + 16);
+        if (valid && s == 0) slotRelease(barMetaEmpty + mslot * 8, relMeta + mslot * 4, mround);
     }
 }
 }  // namespace
@@ -646,7 +685,7 @@ __global__ void patch_kernel(const PatchKernelArgs a) {
 }  // namespace
 
 size_t cellKernelSmemBytes(const CellKernelArgs& a) {
-    return (size_t)a.nSlots * a.slotBytes + (size_t)a.nSlots * 24 + 16;
+    return (size_t)a.nMetaSlots * (a.metaSlotBytes + 20) + (size_t)a.nChunkSlots * (a.chunkSlotBytes + 20) + 64;
 }
 
 bool cellKernelSupportsK(int K) { return K == 5 || K == 9 || K == 14 || K == 19; }

@@ -76,8 +76,8 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
     double* Bm = reinterpret_cast<double*>(rec + lay.oB);
     double* faceD = Bm + K * K;
     double* quirk = faceD + (size_t)nFc * (K + 1);
-    double* pairs = reinterpret_cast<double*>(rec + lay.metaBytes);
-    double* single = pairs + (size_t)Nmax * KP * nSt * 2;
+    const int D = chunkCols(K);
+    const int fullChunk = chunkBytes(K, nSt, D);
     for (int i = lane; i < Nmax * nSt; i += 32) idx[i] = cell;  // unused entries: a valid index
     __syncwarp();
     bool halo = false;
@@ -91,10 +91,13 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
             if (lane == 0) Ns[live] = N;
             for (int i = lane; i < K * N; i += 32) {
                 const int k = i / N, j = i - k * N;
+                const int ch = j / D, jc = j - ch * D;
+                const int cols = min(D, Nmax - ch * D);
+                double* chunk = reinterpret_cast<double*>(rec + lay.metaBytes + (size_t)ch * fullChunk);
                 if (k < 2 * KP)
-                    pairs[((size_t)(j * KP + (k >> 1)) * nSt + live) * 2 + (k & 1)] = src[i];
+                    chunk[((size_t)(jc * KP + (k >> 1)) * nSt + live) * 2 + (k & 1)] = src[i];
                 else
-                    single[(size_t)j * nSt + live] = src[i];
+                    chunk[(size_t)cols * KP * nSt * 2 + (size_t)jc * nSt + live] = src[i];
             }
             const int64_t e0 = a.stencilEntryStart[s];
             for (int j = lane; j < N; j += 32) {
@@ -211,6 +214,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     P->patches.assign(d->patches, d->patches + d->nPatches);
     if (const char* e = getenv("WENOEXT_WARPS")) P->cfgWarps = atoi(e);
     if (const char* e = getenv("WENOEXT_CELLS")) P->cfgCells = atoi(e);
+    if (const char* e = getenv("WENOEXT_META_PASSES")) P->cfgMetaPasses = atoi(e);
     if (const char* e = getenv("WENOEXT_SLOTS")) P->cfgSlots = atoi(e);
     if (const char* e = getenv("WENOEXT_GRID")) P->cfgGrid = atoi(e);
     if (const char* e = getenv("WENOEXT_SMEM_KB")) P->cfgSmemKB = atoi(e);
@@ -309,8 +313,10 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         const RecHeader lay = recLayout(K, nSt, Nmax, nFc);
         const int64_t tot = (int64_t)lay.metaBytes + recMatrixBytes(K, nSt, Nmax);
         recInfo[c].off = recOff;
-        recInfo[c].totBytes = (int32_t)tot;
         recInfo[c].metaBytes = lay.metaBytes;
+        recInfo[c].nSt = (int16_t)nSt;
+        recInfo[c].Nmax = (int16_t)Nmax;
+        P->maxMetaBytes = std::max(P->maxMetaBytes, (int64_t)lay.metaBytes);
         recOff += tot;
         P->maxRecordBytes = std::max(P->maxRecordBytes, tot);
         P->maxN = std::max(P->maxN, Nmax);
@@ -671,32 +677,54 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     CUDA_TRY(cudaMemsetAsync(P->dbg, 0, 64, c.st));
     a.dbg = P->dbg;
 #endif
-    a.slotBytes = (int)((P->maxRecordBytes + 127) / 128 * 128);
+    const int D = chunkCols(P->K);
+    a.nChunks = (P->maxN + D - 1) / D;
+    a.metaSlotBytes = (int)((P->maxMetaBytes + 127) / 128 * 128);
+    a.chunkSlotBytes = (chunkBytes(P->K, P->maxSt, D) + 127) / 128 * 128;
     // Launch geometry. A consumer warp takes cellsPerWarp consecutive cells per
     // pass (one lane per (cell, stencil)), so the ring must hold at least one pass;
     // the rest of the slots are records in flight (an SM needs ~64 KB in flight to
     // cover the HBM latency-bandwidth product). No scratch shared memory.
+    // Shared memory: a ring of meta slots (a few passes deep) and a ring of matrix
+    // chunk slots (everything else). Chunks are released as their columns are
+    // consumed, so most of the chunk ring is data in flight.
     const size_t budget =
         (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 64;
-    int slots = (int)(budget / ((size_t)a.slotBytes + 24));
-    if (P->cfgSlots > 0) slots = std::min(slots, P->cfgSlots);
-    slots = std::min(slots, 128);
-    int cpw = (P->maxSt <= 8 && slots >= 8) ? 4 : 1;
+    int cpw = P->maxSt <= 8 ? 4 : 1;
     if (P->cfgCells > 0) cpw = P->cfgCells;
-    if (slots < cpw || (cpw != 4 && cpw != 1) || P->maxSt > 32 / cpw) {
-        setError("cell records do not fit the shared-memory ring (polynomial order too high)");
+    if ((cpw != 4 && cpw != 1) || P->maxSt > 32 / cpw) {
+        setError("unsupported stencil shape (more than 32 stencils per cell)");
         return WENOEXT_ERR_INVALID;
     }
-    // Slot affinity: the ring size is a multiple of (warps x cells per pass), so a
-    // slot is always consumed by the same warp, round after round. A consumer can
-    // then never wait on round r of a slot before round r-1 has completed (an
-    // mbarrier parity wait cannot tell those apart).
-    const int maxW = std::max(1, std::min(7, P->cfgWarps > 0 ? P->cfgWarps : 7));
-    const int nw = std::min(maxW, slots / cpw);
-    const int m = slots / (cpw * nw);
+    const int nw = std::max(1, std::min(7, P->cfgWarps > 0 ? P->cfgWarps : 7));
+    // meta ring: nw + 2 passes deep, but at most a quarter of the shared memory
+    int metaPasses = std::min(nw + 2, (int)(budget / 4 / ((size_t)cpw * (a.metaSlotBytes + 20))));
+    metaPasses = std::max(metaPasses, 2);
+    if (P->cfgMetaPasses > 0) metaPasses = P->cfgMetaPasses;
+    const size_t perSlotExtra = 16 + 4;  // two mbarriers + release counter
+    int nMeta = cpw * metaPasses;
+    size_t metaTotal = (size_t)nMeta * (a.metaSlotBytes + perSlotExtra);
+    int nChunk = budget > metaTotal + 64
+                     ? (int)((budget - metaTotal - 64) / ((size_t)a.chunkSlotBytes + perSlotExtra))
+                     : 0;
+    if (P->cfgSlots > 0) nChunk = std::min(nChunk, P->cfgSlots);
+    nChunk = std::min(nChunk, 1024);
+    if (nChunk < cpw) {
+        // very large records (high order): shrink the meta ring to the minimum
+        nMeta = cpw;
+        metaTotal = (size_t)nMeta * (a.metaSlotBytes + perSlotExtra);
+        nChunk = budget > metaTotal + 64
+                     ? (int)((budget - metaTotal - 64) / ((size_t)a.chunkSlotBytes + perSlotExtra))
+                     : 0;
+    }
+    if (nChunk < cpw) {
+        setError("cell records do not fit the shared-memory rings (polynomial order too high)");
+        return WENOEXT_ERR_INVALID;
+    }
     a.cellsPerWarp = cpw;
     a.nWarps = nw;
-    a.nSlots = cpw * nw * m;
+    a.nMetaSlots = nMeta;
+    a.nChunkSlots = nChunk;
     const size_t smem = cellKernelSmemBytes(a);
     const int nTiles = (nWork + 31) / 32;
     int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);
