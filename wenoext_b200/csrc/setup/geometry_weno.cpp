@@ -352,42 +352,52 @@ std::vector<double> getB(const PolyMesh& mesh, int cellI, int polOrder, int nDvt
     return B;
 }
 
+// One face of one cell (geometryWENO.C:772-869): integrals of the basis over the
+// face in the cell's reference space, and the face's reference-space area.
+void surfIntTransFace(const PolyMesh& mesh, int cellI, int f, int polOrder, const List3D& volI,
+                      const Mat3& JInvI, const Vec3& refPointI, double* I, double& faceArea) {
+    const int s = polOrder + 1;
+    const Vec3 refPointTrans = transformPoint(JInvI, mesh.cellCentres[cellI], refPointI);
+    std::vector<std::array<int32_t, 3>> tris;
+    mesh.faceTriangles(f, tris);
+    double area = 0;
+    faceArea = 0;
+    for (const auto& tri : tris) {
+        Vec3 v0 = transformPoint(JInvI, mesh.points[tri[0]], refPointI);
+        Vec3 v1 = transformPoint(JInvI, mesh.points[tri[1]], refPointI);
+        Vec3 v2 = transformPoint(JInvI, mesh.points[tri[2]], refPointI);
+        Vec3 vn = cross(v1 - v0, v2 - v0);
+        area = 0.5 * mag(vn);
+        faceArea += area;
+        for (int n = 0; n <= polOrder; ++n)
+            for (int m = 0; m <= polOrder; ++m)
+                for (int l = 0; l <= polOrder; ++l)
+                    if (n + m + l <= polOrder)
+                        I[(size_t)n * s * s + m * s + l] +=
+                            area * gaussQuad(n, m, l, refPointTrans, v0, v1, v2);
+    }
+    // geometryWENO.C:853-869: subtracts with the LAST triangle's area (the
+    // reference's `area` is overwritten per triangle, not accumulated)
+    for (int n = 0; n <= polOrder; ++n)
+        for (int m = 0; m <= polOrder; ++m)
+            for (int l = 0; l <= polOrder; ++l)
+                if (n + m + l <= polOrder) I[(size_t)n * s * s + m * s + l] -= area * volI(n, m, l);
+}
+
 void surfIntTransCell(const PolyMesh& mesh, int cellI, int polOrder, const List3D& volI,
                       const Mat3& JInvI, const Vec3& refPointI, double* intBasTrans,
                       double* refFacAr) {
     const int s = polOrder + 1;
     const size_t cube = (size_t)s * s * s;
-    const Vec3 refPointTrans = transformPoint(JInvI, mesh.cellCentres[cellI], refPointI);
     const int nf = mesh.cellNFaces(cellI);
     const int32_t* fl = mesh.cellFaceList(cellI);
-    std::vector<std::array<int32_t, 3>> tris;
     for (int i = 0; i < nf; ++i) {
         const int f = fl[i];
         int side = (f < mesh.nInternalFaces && cellI == mesh.neighbour[f]) ? 1 : 0;
-        double* I = intBasTrans + ((size_t)f * 2 + side) * cube;
-        mesh.faceTriangles(f, tris);
         double area = 0;
-        for (const auto& tri : tris) {
-            Vec3 v0 = transformPoint(JInvI, mesh.points[tri[0]], refPointI);
-            Vec3 v1 = transformPoint(JInvI, mesh.points[tri[1]], refPointI);
-            Vec3 v2 = transformPoint(JInvI, mesh.points[tri[2]], refPointI);
-            Vec3 vn = cross(v1 - v0, v2 - v0);
-            area = 0.5 * mag(vn);
-            if (side == 0) refFacAr[f] += area;
-            for (int n = 0; n <= polOrder; ++n)
-                for (int m = 0; m <= polOrder; ++m)
-                    for (int l = 0; l <= polOrder; ++l)
-                        if (n + m + l <= polOrder)
-                            I[(size_t)n * s * s + m * s + l] +=
-                                area * gaussQuad(n, m, l, refPointTrans, v0, v1, v2);
-        }
-        // geometryWENO.C:853-869: subtracts with the LAST triangle's area (the
-        // reference's `area` is overwritten per triangle, not accumulated)
-        for (int n = 0; n <= polOrder; ++n)
-            for (int m = 0; m <= polOrder; ++m)
-                for (int l = 0; l <= polOrder; ++l)
-                    if (n + m + l <= polOrder)
-                        I[(size_t)n * s * s + m * s + l] -= area * volI(n, m, l);
+        surfIntTransFace(mesh, cellI, f, polOrder, volI, JInvI, refPointI,
+                         intBasTrans + ((size_t)f * 2 + side) * cube, area);
+        if (side == 0) refFacAr[f] += area;
     }
 }
 

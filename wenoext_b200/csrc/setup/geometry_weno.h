@@ -64,5 +64,10 @@ void surfIntTransCell(const PolyMesh& mesh, int cellI, int polOrder, const List3
                       const Mat3& JInvI, const Vec3& refPointI, double* intBasTrans,
                       double* refFacAr);
 
+// one face of one cell; I (cube of (polOrder+1)^3) must be zeroed first
+void surfIntTransFace(const PolyMesh& mesh, int cellI, int f, int polOrder,
+                      const List3D& volIntegralsI, const Mat3& JInvI, const Vec3& refPointI,
+                      double* I, double& faceArea);
+
 }  // namespace geom
 }  // namespace wenoext

@@ -209,12 +209,18 @@ PolyMesh makeBoxMesh(const BoxSpec& s) {
     const int nx = s.n[0], ny = s.n[1], nz = s.n[2];
     std::vector<Vec3> pts((size_t)(nx + 1) * (ny + 1) * (nz + 1));
     auto pid = [&](int i, int j, int k) { return i + (nx + 1) * (j + (ny + 1) * k); };
+    const int den[3] = {s.nDen[0] ? s.nDen[0] : nx, s.nDen[1] ? s.nDen[1] : ny,
+                        s.nDen[2] ? s.nDen[2] : nz};
     for (int k = 0; k <= nz; ++k)
         for (int j = 0; j <= ny; ++j)
             for (int i = 0; i <= nx; ++i)
-                pts[pid(i, j, k)] = {s.lo[0] + (s.hi[0] - s.lo[0]) * i / nx,
-                                     s.lo[1] + (s.hi[1] - s.lo[1]) * j / ny,
-                                     s.lo[2] + (s.hi[2] - s.lo[2]) * k / nz};
+                pts[pid(i, j, k)] = {s.lo[0] + (s.hi[0] - s.lo[0]) * i / den[0],
+                                     s.lo[1] + (s.hi[1] - s.lo[1]) * j / den[1],
+                                     s.lo[2] + (s.hi[2] - s.lo[2]) * k / den[2]};
+    // actual upper corner (differs from s.hi for a sub-box)
+    const double hiAct[3] = {s.lo[0] + (s.hi[0] - s.lo[0]) * nx / den[0],
+                             s.lo[1] + (s.hi[1] - s.lo[1]) * ny / den[1],
+                             s.lo[2] + (s.hi[2] - s.lo[2]) * nz / den[2]};
     std::vector<CellShape> cells;
     cells.reserve((size_t)nx * ny * nz * (s.tetSplit ? 6 : 1));
     for (int k = 0; k < nz; ++k)
@@ -259,14 +265,14 @@ PolyMesh makeBoxMesh(const BoxSpec& s) {
         proto[sd].type = s.sideType[sd];
         proto[sd].nbr = (s.sideType[sd] == PATCH_CYCLIC) ? (sd ^ 1) : -1;
     }
-    const double tol[3] = {1e-9 * (s.hi[0] - s.lo[0]), 1e-9 * (s.hi[1] - s.lo[1]),
-                           1e-9 * (s.hi[2] - s.lo[2])};
+    const double tol[3] = {1e-9 * (hiAct[0] - s.lo[0]), 1e-9 * (hiAct[1] - s.lo[1]),
+                           1e-9 * (hiAct[2] - s.lo[2])};
     auto patchOf = [&](const std::vector<int32_t>& fp) -> int {
         for (int ax = 0; ax < 3; ++ax) {
             bool lo = true, hi = true;
             for (int32_t p : fp) {
                 if (std::fabs(pts[p][ax] - s.lo[ax]) > tol[ax]) lo = false;
-                if (std::fabs(pts[p][ax] - s.hi[ax]) > tol[ax]) hi = false;
+                if (std::fabs(pts[p][ax] - hiAct[ax]) > tol[ax]) hi = false;
             }
             if (lo) return 2 * ax;
             if (hi) return 2 * ax + 1;

@@ -87,6 +87,10 @@ struct BoxSpec {
     int32_t sideType[6] = {0, 0, 0, 0, 0, 0};
     // 0: hexes; 6: every hex split into 6 tets (Kuhn); used for irregular stencils
     int32_t tetSplit = 0;
+    // If non-zero: the box is the first n[a] layers of a box with nDen[a] cells
+    // between lo and hi (point i sits at lo + (hi-lo)*i/nDen, bit-identical to the
+    // larger box). Used for the representative box of box_fast.cpp.
+    int32_t nDen[3] = {0, 0, 0};
 };
 
 // blockMesh-like structured hex box, cells numbered i-fastest.

@@ -15,18 +15,7 @@
 namespace wenoext {
 
 namespace {
-
-// Result of steps 1-4 of WENOBase::WENOBase for one cell, in GLOBAL cell ids.
-struct CellSetup {
-    std::vector<int32_t> central;                // sorted central list before the cut
-    std::vector<std::vector<int32_t>> globalID;  // [stencil][j]; {CELL_DELETED} if deleted
-    std::vector<std::vector<double>> Ainv;       // [stencil] nDvt x (size-1), row-major
-    bool empty = false;                          // Cell::empty
-    List3D volI;
-    Mat3 JInv;
-    Vec3 refPoint;
-    double refDet = 0;
-};
+using detail::CellSetup;
 
 inline double ofSign(double s) { return s >= 0 ? 1.0 : -1.0; }  // OpenFOAM sign()
 
@@ -217,8 +206,10 @@ void calcMatrix(const PolyMesh& gm, int g, int stencilI, int nDvt, const int dim
     if (cur.m != stencilSize - 1) st.resize(cur.m + 1);
 }
 
-CellSetup computeCell(const PolyMesh& gm, int g, int nDvt, const int dim[3],
-                      const SetupParams& prm) {
+}  // namespace
+
+CellSetup detail::computeCell(const PolyMesh& gm, int g, int nDvt, const int dim[3],
+                              const SetupParams& prm) {
     CellSetup cs;
     geom::initIntegrals(gm, g, prm.polOrder, cs.volI, cs.JInv, cs.refPoint, cs.refDet);
     int nStencils = 1;
@@ -240,64 +231,58 @@ CellSetup computeCell(const PolyMesh& gm, int g, int nDvt, const int dim[3],
     return cs;
 }
 
-}  // namespace
-
-namespace {
-
 // matrixDB stand-in (libWENOEXT/WENOBase/matrixDB.C:75-199): tolerance-based
 // de-duplication, same key, same search window, same comparison.
-struct MatrixPool {
-    std::multimap<int32_t, int32_t> db;
-    HostPlan* plan;
-    int nDvt;
-    static double maxMag(const std::vector<double>& A) {
-        double m = 0;
-        for (double v : A) m = std::max(m, std::fabs(v));
-        return m;
-    }
-    static int32_t hashMatrix(const std::vector<double>& A) {
-        int32_t key = 0;
-        double mx = maxMag(A);
-        if (mx == 0) return key;
-        double mult = 1.0e6 / mx;
-        for (double v : A) key += (int32_t)(v * mult);
-        return key;
-    }
-    int32_t insertNew(int32_t key, const std::vector<double>& A) {
-        int32_t id = (int32_t)plan->matrixCols.size();
-        plan->matrixCols.push_back((int32_t)(A.size() / nDvt));
-        plan->matrixData.insert(plan->matrixData.end(), A.begin(), A.end());
-        plan->matrixStart.push_back((int64_t)plan->matrixData.size());
-        db.emplace(key, id);
-        return id;
-    }
-    int32_t similar(const std::vector<double>& A) {
-        const int32_t key = hashMatrix(A);
-        if (db.empty()) return insertNew(key, A);
-        const double tol = 1e-9 * maxMag(A);
-        auto itStart = db.lower_bound(key - 5);
-        auto itEnd = db.lower_bound(key + 5);
-        if (itStart == itEnd && itStart != db.begin()) --itStart;
-        for (auto it = itStart; it != itEnd; ++it) {
-            const int32_t id = it->second;
-            const size_t sz = (size_t)(plan->matrixStart[id + 1] - plan->matrixStart[id]);
-            if (sz != A.size()) continue;
-            const double* cmp = &plan->matrixData[plan->matrixStart[id]];
-            bool ok = true;
-            for (size_t i = 0; i < sz; ++i) {
-                if (std::fabs(A[i]) < 1e-15) continue;
-                if (std::fabs(cmp[i] - A[i]) > tol) {
-                    ok = false;
-                    break;
-                }
-            }
-            if (ok) return id;
-        }
-        return insertNew(key, A);
-    }
-};
+namespace {
+double maxMag(const std::vector<double>& A) {
+    double m = 0;
+    for (double v : A) m = std::max(m, std::fabs(v));
+    return m;
+}
+int32_t hashMatrix(const std::vector<double>& A) {
+    int32_t key = 0;
+    double mx = maxMag(A);
+    if (mx == 0) return key;
+    double mult = 1.0e6 / mx;
+    for (double v : A) key += (int32_t)(v * mult);
+    return key;
+}
+}  // namespace
 
-int computeNDvt(const PolyMesh& m, int polOrder, int dim[3]) {
+int32_t detail::MatrixPool::insertNew(int32_t key, const std::vector<double>& A) {
+    int32_t id = (int32_t)plan->matrixCols.size();
+    plan->matrixCols.push_back((int32_t)(A.size() / nDvt));
+    plan->matrixData.insert(plan->matrixData.end(), A.begin(), A.end());
+    plan->matrixStart.push_back((int64_t)plan->matrixData.size());
+    db.emplace(key, id);
+    return id;
+}
+int32_t detail::MatrixPool::similar(const std::vector<double>& A) {
+    const int32_t key = hashMatrix(A);
+    if (db.empty()) return insertNew(key, A);
+    const double tol = 1e-9 * maxMag(A);
+    auto itStart = db.lower_bound(key - 5);
+    auto itEnd = db.lower_bound(key + 5);
+    if (itStart == itEnd && itStart != db.begin()) --itStart;
+    for (auto it = itStart; it != itEnd; ++it) {
+        const int32_t id = it->second;
+        const size_t sz = (size_t)(plan->matrixStart[id + 1] - plan->matrixStart[id]);
+        if (sz != A.size()) continue;
+        const double* cmp = &plan->matrixData[plan->matrixStart[id]];
+        bool ok = true;
+        for (size_t i = 0; i < sz; ++i) {
+            if (std::fabs(A[i]) < 1e-15) continue;
+            if (std::fabs(cmp[i] - A[i]) > tol) {
+                ok = false;
+                break;
+            }
+        }
+        if (ok) return id;
+    }
+    return insertNew(key, A);
+}
+
+int detail::computeNDvt(const PolyMesh& m, int polOrder, int dim[3]) {
     // setDegreeOfFreedom (WENOBase.C:1130-1155)
     int nDvt;
     if (m.nSolutionD() == 3)
@@ -308,6 +293,10 @@ int computeNDvt(const PolyMesh& m, int polOrder, int dim[3]) {
     return nDvt;
 }
 
+namespace {
+using detail::MatrixPool;
+using detail::computeCell;
+using detail::computeNDvt;
 void copyMeshAddressing(const PolyMesh& lm, HostPlan& hp) {
     hp.nCells = lm.nCells;
     hp.nFaces = lm.nFaces();

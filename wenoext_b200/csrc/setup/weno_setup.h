@@ -8,6 +8,9 @@
 #include <cstdint>
 #include <vector>
 
+#include <map>
+
+#include "geometry_weno.h"
 #include "polymesh.h"
 
 namespace wenoext {
@@ -62,6 +65,32 @@ struct HostPlan {
     // statistics like matrixDB::info (matrixDB.C:232-273)
     int64_t nMatricesTotal = 0;
 };
+
+// Pieces of the generic path shared with the structured-box fast path (box_fast.cpp)
+namespace detail {
+// Result of steps 1-4 of WENOBase::WENOBase for one cell, in GLOBAL cell ids.
+struct CellSetup {
+    std::vector<int32_t> central;                // sorted central list before the cut
+    std::vector<std::vector<int32_t>> globalID;  // [stencil][j]; {CELL_DELETED} if deleted
+    std::vector<std::vector<double>> Ainv;       // [stencil] nDvt x (size-1), row-major
+    bool empty = false;                          // Cell::empty
+    List3D volI;
+    Mat3 JInv;
+    Vec3 refPoint;
+    double refDet = 0;
+};
+CellSetup computeCell(const PolyMesh& gm, int g, int nDvt, const int dim[3], const SetupParams& prm);
+int computeNDvt(const PolyMesh& m, int polOrder, int dim[3]);
+// matrixDB stand-in (libWENOEXT/WENOBase/matrixDB.C:75-199): tolerance-based
+// de-duplication, same key, same search window, same comparison.
+struct MatrixPool {
+    std::multimap<int32_t, int32_t> db;
+    HostPlan* plan = nullptr;
+    int nDvt = 0;
+    int32_t insertNew(int32_t key, const std::vector<double>& A);
+    int32_t similar(const std::vector<double>& A);
+};
+}  // namespace detail
 
 // Generic path: any PolyMesh, any decomposition. `cellProc` may be empty (serial).
 HostPlan buildPlanGeneric(const PolyMesh& globalMesh, const std::vector<int32_t>& cellProc,
