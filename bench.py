@@ -85,7 +85,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -299,6 +299,14 @@ def run_ours(a):
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    # DRAM traffic of the dominant kernel: taken from the committed ncu capture of this
+    # workload (profiles/traffic.json), null for workloads that were not captured
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get(workload_name(a, 1), {}).get("traffic_bytes_per_launch")
+    except OSError:
+        pass
     k_ms_launch = t[1].item()  # fused cell kernel(s) per step, max over ranks
     achieved = alg_bytes / (k_ms_launch * 1e-3) / 1e9 if k_ms_launch > 0 else 0.0
     res = {
@@ -314,7 +322,7 @@ def run_ours(a):
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": traffic,
                      "kernel": "weno_cell_kernel", "kernel_ms": k_ms_launch,
                      "alg_bytes_per_launch": alg_bytes,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks

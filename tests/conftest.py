@@ -18,3 +18,4 @@ def _built():
     from wenoext_b200 import build
     build.build_product()
     build.build_oracle()
+    build.build_test_hooks()

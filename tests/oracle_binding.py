@@ -185,3 +185,53 @@ def _send_list(case, to):
     d = case.desc
     a, b = d.sendHaloStart[to], d.sendHaloStart[to + 1]
     return np.array([d.sendHaloCellID[i] for i in range(a, b)], dtype=np.int64)
+
+
+def correction_distributed(orc, case, scheme, bounded, vf, flux, p=4.0, dm=1000.0, eps=1e-40,
+                           bugCompat=1):
+    """One process per rank (torch.distributed, any backend with send/recv): the same
+    two exchange steps as the reference's MPI run - collectData (WENOCoeff.C:224-296)
+    and swapData (WENOUpwindFit.C:326-385) - around the per-rank oracle calls.
+    `case` already had exchange_halo_lists_distributed()."""
+    import torch
+    import torch.distributed as dist
+
+    me, R = case.myProc, case.nProcs
+    vf = _f64(vf).reshape(case.nCells, -1)
+    nComp = vf.shape[1]
+    # exchange #1: cell values of the halo lists
+    reqs, recv_bufs = [], {}
+    for q in range(R):
+        n = case.desc.receiveHaloSize[q]
+        if q != me and n:
+            recv_bufs[q] = torch.empty((n, nComp), dtype=torch.float64)
+            reqs.append(dist.irecv(recv_bufs[q], src=q))
+    for q in range(R):
+        ids = _send_list(case, q)
+        if q != me and len(ids):
+            reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(vf[ids])), dst=q))
+    for r in reqs:
+        r.wait()
+    segs = [recv_bufs[q].numpy() for q in range(R) if q in recv_bufs]
+    halo = np.concatenate(segs) if segs else np.zeros((0, nComp))
+    cw = orc.getWENOPol(case, vf, halo, p, dm, eps)
+    corr, ud = orc.phaseA(case, flux, cw)
+    # exchange #2: processor-patch face values and the patch-neighbour cell values
+    nI = case.nInternalFaces
+    recv, pnf = np.zeros_like(ud), np.zeros_like(ud)
+    reqs, bufs = [], []
+    for (ptype, start, size, nbr) in case.patches:
+        if ptype != 1 or size == 0:
+            continue
+        mine = np.concatenate([ud[start - nI:start - nI + size], vf[case.owner[start:start + size]]])
+        theirs = torch.empty(mine.shape, dtype=torch.float64)
+        bufs.append((start, size, theirs))
+        reqs.append(dist.irecv(theirs, src=nbr))
+        reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(mine)), dst=nbr))
+    for r in reqs:
+        r.wait()
+    for start, size, theirs in bufs:
+        t = theirs.numpy()
+        recv[start - nI:start - nI + size] = t[:size]
+        pnf[start - nI:start - nI + size] = t[size:]
+    return orc.phaseB(case, scheme, bounded, vf, flux, cw, corr, pnf, recv, bugCompat)

@@ -68,7 +68,21 @@ def build_oracle(force=False):
     return os.path.join(odir, "libweno_oracle.so")
 
 
+def build_test_hooks(force=False):
+    """tests/native/libsetup_hooks.so: test-only C hooks into the host setup helpers."""
+    tdir = os.path.join(ROOT, "tests", "native")
+    lib = os.path.join(tdir, "libsetup_hooks.so")
+    srcs = [os.path.join(tdir, "setup_hooks.cpp")] + [
+        os.path.join(CSRC, "setup", f) for f in ("geometry_weno.cpp", "polymesh.cpp")]
+    if not force and not _newer(lib, srcs + _all_deps()):
+        return lib
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-I", CSRC, "-o", lib] + srcs,
+                   check=True)
+    return lib
+
+
 if __name__ == "__main__":
     force = "--force" in sys.argv
     print(build_product(force=force, verbose="-v" in sys.argv))
     print(build_oracle(force=force))
+    print(build_test_hooks(force=force))
