@@ -242,9 +242,8 @@ def run_ours(a):
         step()
     # ---- timed region: device-resident inputs, K steps, CUDA events ----
     plan.enable_kernel_timing(True)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    sampler = ClockSampler(local)  # every rank samples its own GPU; rank 0 reports the slowest
+    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches = 0
     barrier()
@@ -255,7 +254,17 @@ def run_ours(a):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
+    if N > 1:
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        cm = torch.tensor([clocks["sm_mhz"] or 0.0] + [float(nm in clocks["reasons"]) for nm in names],
+                          dtype=torch.float64, device=dev)
+        lo, hi = cm.clone(), cm.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        clocks["sm_mhz"] = lo[0].item() or None  # median under load of the slowest GPU
+        clocks["reasons"] = [nm for i, nm in enumerate(names) if hi[1 + i].item() > 0]
+        clocks["ranks"] = N
     k_ms, k_n = plan.kernel_time()
     plan.enable_kernel_timing(False)
     t = torch.tensor([ms, k_ms / max(a.steps, 1)], dtype=torch.float64, device=dev)

@@ -619,6 +619,12 @@ extern "C" int wenoext_kernel_time(wenoext_plan* P, double* msSum, int* nLaunche
         CUDA_TRY(cudaEventSynchronize(P->timeEvents[i + 1]));
         CUDA_TRY(cudaEventElapsedTime(&ms, P->timeEvents[i], P->timeEvents[i + 1]));
         *msSum += (double)ms;
+        if (getenv("WENOEXT_TIMING_VERBOSE") && i < 12) {  // developer aid
+            float gap = 0;
+            if (i >= 2) cudaEventElapsedTime(&gap, P->timeEvents[i - 1], P->timeEvents[i]);
+            fprintf(stderr, "[wenoext rank %d] cell-kernel launch %zu: %.4f ms (gap before: %.4f ms)\n",
+                    P->myProc, i / 2, ms, gap);
+        }
     }
     if (reset) P->timeUsed = 0;
     return 0;
