@@ -1,37 +1,40 @@
 // Device-side plan: the reference's nested WENOBase containers (a11 in
 // SURVEY.md 8a) flattened into one self-contained, 16-byte aligned RECORD per
-// cell, so that two TMA bulk copies (meta part, matrix part) bring everything
-// static a cell needs into shared memory.
+// cell. A record is a sequence of PARTS, each fetched into shared memory by one
+// 1-D TMA bulk copy exactly when the kernel needs it:
+//   head | tail | chunk 0 | chunk 1 | ...
 //
 // The fused kernel gives one LANE to every (cell, stencil) pair: the lane owns
 // all K coefficients of its stencil for all components in registers. The record
 // is laid out for that mapping (stencil index fastest), so that the lanes of a
 // cell read consecutive shared-memory words.
 //
-// Record layout (byte offsets from the record start; K = nDvt, nSt = surviving
-// stencils in list order, so stencil 0 is the "first surviving" one that gets dm,
-// WENOCoeff.C:198; Nmax = max_s N_s):
-//   META PART
-//   RecHeader                                   32 B
-//   int32  N[nSt]              columns of each stencil
-//   int32  idx[Nmax][nSt]      flat gather index of entry j of stencil s into the
-//                              value buffer (local id, or nCells + haloOffset(proc)
-//                              + haloId); the cell itself where j >= N_s
-//   pad to 16 B
-//   int32  faceI[nFc][4]       face id, flat index of the cell across (-1 none), kind, 0
-//   double B[K*K]              B()[cell], row-major
-//   double faceD[nFc][K+1]     own-side intBasTrans()[f][side] compacted in sumFlux
-//                              enumeration order (WENOUpwindFit.C:304-319), refFacAr()[f]
-//   double quirk[K]            intBasTrans()[cellI][1] compacted (WENOUpwindFit01.C:125)
-//   pad to 16 B                                          -> metaBytes
-//   MATRIX PART  (LSmatrix()[cell][s], bitwise copies, permuted), streamed in
-//   CHUNKS of D = chunkCols(K) columns so that shared memory is released as the
-//   columns are consumed. Chunk ch holds columns [ch*D, min(Nmax, ch*D+D)):
+// Layout (K = nDvt, nSt = surviving stencils in list order, so stencil 0 is the
+// "first surviving" one that gets dm, WENOCoeff.C:198; Nmax = max_s N_s;
+// D = chunkCols(K) matrix columns per chunk):
+//   HEAD (needed from the start of the cell to its end)
+//     RecHeader                                   32 B
+//     int32  N[nSt]              columns of each stencil, pad to 16 B
+//     int32  faceI[nFc][4]       face id, flat index of the cell across (-1 none), kind, 0
+//     int32  idx[min(D,Nmax)][nSt]  gather indices of the columns of chunk 0
+//     pad to 16 B                                          -> headBytes
+//   TAIL (needed after the matrix phase)
+//     double B[K*K]              B()[cell], row-major
+//     double faceD[nFc][K+1]     own-side intBasTrans()[f][side] compacted in sumFlux
+//                                enumeration order (WENOUpwindFit.C:304-319), refFacAr()[f]
+//     double quirk[K]            intBasTrans()[cellI][1] compacted (WENOUpwindFit01.C:125)
+//     pad to 16 B                                          -> tailBytes
+//   CHUNK ch: columns [ch*D, ch*D+cols) of LSmatrix()[cell][s] for all stencils
+//   (bitwise copies, permuted), cols = min(D, Nmax - ch*D), followed by the gather
+//   indices of the NEXT chunk's columns (icols = clamp(Nmax - (ch+1)*D, 0, D)):
 //     double2 pairs[cols][K/2][nSt]   (A_s[2q][j], A_s[2q+1][j])
 //     double  single[cols][nSt]       A_s[K-1][j]            (K odd only)
-//     zero where j >= N_s (only when stencil sizes differ, i.e. bestConditioned)
+//     int32   idx[icols][nSt]
 //     pad to 16 B
-//                                                        -> totBytes
+//   Matrix entries are zero where j >= N_s (only when stencil sizes differ, i.e.
+//   bestConditioned). A gather index is the flat index of entry j of stencil s into
+//   the value buffer (local id, or nCells + haloOffset(proc) + haloId); the cell
+//   itself where j >= N_s (so that the value difference is exactly 0).
 // Only internal and coupled-patch faces are listed (others get zero correction).
 #pragma once
 #include <cuda_runtime.h>
@@ -44,21 +47,29 @@ struct RecHeader {
     int32_t nFc;    // listed faces
     int32_t Nmax;   // max columns over the stencils
     int32_t flags;  // bit0: some stencil entry is a halo cell
-    int32_t oIdx, oFace, oB, metaBytes;  // byte offsets of the meta sections
+    int32_t oFace, oIdx;           // byte offsets inside the head
+    int32_t headBytes, tailBytes;  // part sizes
 };
 
-// per cell: where its record lives (one 16-byte load for the TMA producer)
+// per cell: where its record lives and how big its parts are (one 16-byte load
+// gives the issuing lane everything it needs)
 struct RecInfo {
-    int64_t off;        // byte offset of the record
-    int32_t metaBytes;  // meta part (multiple of 16)
-    int16_t nSt, Nmax;  // chunk sizes follow from these
+    int64_t off;                   // byte offset of the record
+    uint16_t headBytes, tailBytes;
+    int16_t nSt, Nmax;             // chunk sizes follow from these
 };
 
 // columns per matrix chunk (also the unroll depth of the kernel's column loop)
-__host__ __device__ constexpr int chunkCols(int K) { return K <= 9 ? 7 : 4; }
-__host__ __device__ inline int chunkBytes(int K, int nSt, int cols) {
-    return (cols * nSt * K * 8 + 15) & ~15;
+__host__ __device__ constexpr int chunkCols(int K) { return K <= 9 ? 3 : 2; }
+__host__ __device__ inline int clampCols(int n, int D) { return n < 0 ? 0 : (n > D ? D : n); }
+// bytes of chunk ch of a cell with nSt stencils and Nmax columns
+__host__ __device__ inline int chunkBytes(int K, int nSt, int Nmax, int ch) {
+    const int D = chunkCols(K);
+    const int cols = clampCols(Nmax - ch * D, D), icols = clampCols(Nmax - (ch + 1) * D, D);
+    return (cols * nSt * K * 8 + icols * nSt * 4 + 15) & ~15;
 }
+// byte offset of the next chunk's gather indices inside chunk ch
+__host__ __device__ inline int chunkIdxOffset(int K, int nSt, int cols) { return cols * nSt * K * 8; }
 
 // kind bits of a listed face
 enum : int32_t {
@@ -70,25 +81,26 @@ enum : int32_t {
 };
 
 __host__ __device__ inline RecHeader recLayout(int K, int nSt, int Nmax, int nFc) {
+    const int D = chunkCols(K);
     RecHeader h;
     h.nSt = nSt;
     h.nFc = nFc;
     h.Nmax = Nmax;
     h.flags = 0;
-    int o = (int)sizeof(RecHeader) + 4 * nSt;
-    h.oIdx = o;
-    o += 4 * Nmax * nSt;
-    o = (o + 15) & ~15;
+    int o = ((int)sizeof(RecHeader) + 4 * nSt + 15) & ~15;
     h.oFace = o;
     o += 16 * nFc;
-    h.oB = o;
-    o += 8 * (K * K + nFc * (K + 1) + K);
-    h.metaBytes = (o + 15) & ~15;
+    h.oIdx = o;
+    o += 4 * clampCols(Nmax, D) * nSt;
+    h.headBytes = (o + 15) & ~15;
+    h.tailBytes = (8 * (K * K + nFc * (K + 1) + K) + 15) & ~15;
     return h;
 }
-__host__ __device__ inline int recMatrixBytes(int K, int nSt, int Nmax) {
+__host__ __device__ inline int64_t recMatrixBytes(int K, int nSt, int Nmax) {
     const int D = chunkCols(K);
-    return (Nmax / D) * chunkBytes(K, nSt, D) + chunkBytes(K, nSt, Nmax % D);
+    int64_t b = 0;
+    for (int ch = 0; ch * D < Nmax; ++ch) b += chunkBytes(K, nSt, Nmax, ch);
+    return b;
 }
 
 // Arguments of the fused cell kernel (by value, __grid_constant__).
@@ -112,10 +124,11 @@ struct CellKernelArgs {
     double dm, eps;
     // launch geometry
     int32_t cellsPerWarp;      // 4 or 1: 32 / cellsPerWarp stencil lanes per cell
-    int32_t nWarps;            // consumer warps per CTA
-    int32_t nMetaSlots, metaSlotBytes;    // shared-memory ring of record meta parts
-    int32_t nChunkSlots, chunkSlotBytes;  // shared-memory ring of matrix chunks
-    int32_t nChunks;           // chunk positions per cell: ceil(maxN / chunkCols(K))
+    int32_t nWarps;            // warps per CTA (each runs its own TMA pipeline)
+    int32_t ringSteps;         // chunk steps in flight per warp (ring depth, <= nChunks)
+    int32_t headSlotBytes, tailSlotBytes, chunkSlotBytes;  // per-cell shared-memory slots
+    int32_t warpBytes;         // shared memory per warp: 2 heads + tail + ring, x cellsPerWarp
+    int32_t nChunks;           // chunk steps per cell: ceil(maxN / chunkCols(K))
     int32_t maxN;              // max stencil columns in the plan
     // developer aid (only read when built with -DWENOEXT_KDEBUG): first violated
     // bounds check is recorded in dbg[0..15]
@@ -146,6 +159,7 @@ int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t sme
                      cudaStream_t st);
 size_t cellKernelSmemBytes(const CellKernelArgs& a);
 bool cellKernelSupportsK(int K);
+int cellKernelMaxWarps();  // warps per CTA the kernel is compiled for
 void launchPatchKernel(const PatchKernelArgs& a, cudaStream_t st);
 void launchPackValues(const double* vf, int nCells, int nComp, int c0, int CB, int VS,
                       double* vals, cudaStream_t st);

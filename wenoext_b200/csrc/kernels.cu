@@ -33,7 +33,7 @@ namespace wenoext {
 namespace {
 
 constexpr int TILE = 32;          // consecutive cells handed to one CTA at a time
-constexpr int MAX_THREADS = 256;  // 7 consumer warps + producer (up to 255 registers)
+constexpr int MAX_THREADS = 256;  // 8 warps per CTA (up to 255 registers per thread)
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -141,28 +141,11 @@ __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&
     }
 }
 
-__device__ __forceinline__ uint32_t ldsVolatileU32(uint32_t a) {
-    uint32_t v;
-    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
-    return v;
-}
-__device__ __forceinline__ void stsVolatileU32(uint32_t a, uint32_t v) {
-    asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
-}
-// Ring slot protocol. Slots are not bound to a consumer, so before waiting for
-// round r of a slot a consumer first waits until round r-1 has been RELEASED
-// (release counter): an mbarrier parity wait alone cannot tell "round r done"
-// from "round r-1 not done yet".
-__device__ __forceinline__ void slotWait(uint32_t fullBar, uint32_t relAddr, uint32_t round) {
-    while (ldsVolatileU32(relAddr) < round) {
-    }
-    mbarWait(fullBar, round & 1u);
-}
-__device__ __forceinline__ void slotRelease(uint32_t emptyBar, uint32_t relAddr, uint32_t round) {
-    stsVolatileU32(relAddr, round + 1u);
-    mbarArrive(emptyBar);
-}
-
+// One elected-lane-free pipeline per warp: lanes 0..CELLS-1 each issue the bulk
+// copies of "their" cell of the pass (head, tail, chunk steps); all lanes wait on
+// the warp's own mbarriers. A buffer is refilled by the warp itself right after
+// it has consumed it, so program order (plus __syncwarp) is the only "empty"
+// signal needed: no producer warp, no cross-warp synchronisation.
 template <int K, int CB, int CELLS, int D>
 __global__ void __launch_bounds__(MAX_THREADS, 1)
     weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
@@ -171,22 +154,21 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     constexpr int KP = K / 2;       // coefficient pairs per column
     constexpr bool ODD = (K & 1) != 0;
     const int NW = a.nWarps;
-    const int warp = threadIdx.x >> 5;
+    // broadcast through a shuffle: tells the compiler the warp index is warp-uniform
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
-    const int nMeta = a.nMetaSlots, nChunk = a.nChunkSlots, CH = a.nChunks;
+    const int CH = a.nChunks, R = a.ringSteps;
 
-    // shared memory: meta ring | chunk ring | mbarriers | release counters
-    const uint32_t metaRing = smemAddr(smem);
-    const uint32_t chunkRing = metaRing + (uint32_t)nMeta * a.metaSlotBytes;
-    const uint32_t barMetaFull = chunkRing + (uint32_t)nChunk * a.chunkSlotBytes;
-    const uint32_t barMetaEmpty = barMetaFull + (uint32_t)nMeta * 8;
-    const uint32_t barChunkFull = barMetaEmpty + (uint32_t)nMeta * 8;
-    const uint32_t barChunkEmpty = barChunkFull + (uint32_t)nChunk * 8;
-    const uint32_t relMeta = barChunkEmpty + (uint32_t)nChunk * 8;
-    const uint32_t relChunk = relMeta + (uint32_t)nMeta * 4;
-
-    for (int i = threadIdx.x; i < 2 * (nMeta + nChunk); i += blockDim.x) mbarInit(barMetaFull + i * 8, 1);
-    for (int i = threadIdx.x; i < nMeta + nChunk; i += blockDim.x) stsVolatileU32(relMeta + i * 4, 0u);
+    // shared memory of this warp: head[2][CELLS] | tail[CELLS] | ring[R][CELLS]; the
+    // mbarriers of all warps follow the data: head x2, tail, ring x R per warp
+    const uint32_t wbase = smemAddr(smem) + (uint32_t)warp * (uint32_t)a.warpBytes;
+    const uint32_t headBuf = wbase;
+    const uint32_t tailBuf = headBuf + 2u * CELLS * (uint32_t)a.headSlotBytes;
+    const uint32_t ringBuf = tailBuf + (uint32_t)CELLS * (uint32_t)a.tailSlotBytes;
+    const uint32_t bars = smemAddr(smem) + (uint32_t)NW * (uint32_t)a.warpBytes +
+                          (uint32_t)warp * (uint32_t)(3 + R) * 8u;
+    const uint32_t barTail = bars + 16, barRing = bars + 24;
+    if (lane < 3 + R) mbarInit(bars + lane * 8, CELLS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
 
@@ -202,108 +184,119 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const int w = ((int)blockIdx.x + (n / TILE) * (int)gridDim.x) * TILE + (n % TILE);
         return a.cellList ? __ldg(a.cellList + w) : w;
     };
+    const int nPasses = (nItems + CELLS - 1) / CELLS;           // of the CTA
+    const int myPasses = nPasses > warp ? (nPasses - warp - 1) / NW + 1 : 0;  // of this warp
+    if (myPasses == 0) return;
 
-    if (warp == NW) {
-        // ===== producer warp. All lanes prefetch the record descriptors of the next
-        // 32 items. Per pass (CELLS consecutive items) lane l issues one bulk copy:
-        // l < CELLS the meta part of cell l, then chunk ch of cell c in the order the
-        // consumers need them (chunk-major). =====
-        const uint64_t pol = evictFirstPolicy();
-        auto fetch = [&](int n) {
-            int4 r = make_int4(0, 0, 0, 0);
-            if (n < nItems) r = __ldg(reinterpret_cast<const int4*>(a.recInfo + itemToCell(n)));
-            return r;
-        };
-        const int perPass = CELLS * (1 + CH);  // bulk copies per pass
-        int4 cur = fetch(lane);
-        for (int n0 = 0; n0 < nItems; n0 += 32) {
-            const int4 nxt = fetch(n0 + 32 + lane);
-            for (int pp = 0; pp < 32 / CELLS && n0 + pp * CELLS < nItems; ++pp) {
-                for (int r0 = 0; r0 < perPass; r0 += 32) {
-                    const int r = r0 + lane;
-                    const int role = r / CELLS;  // 0: meta, 1 + ch: chunk ch
-                    const int c = r - role * CELLS;
-                    const int srcLane = pp * CELLS + c;
-                    const uint32_t offLo = (uint32_t)__shfl_sync(0xffffffffu, cur.x, srcLane);
-                    const uint32_t offHi = (uint32_t)__shfl_sync(0xffffffffu, cur.y, srcLane);
-                    const int meta = __shfl_sync(0xffffffffu, cur.z, srcLane);
-                    const int packed = __shfl_sync(0xffffffffu, cur.w, srcLane);
-                    const int item = n0 + srcLane;
-                    if (r < perPass && item < nItems) {
-                        const unsigned char* src = a.records + (((uint64_t)offHi << 32) | offLo);
-                        const int nSt = packed & 0xffff, Nmax = (packed >> 16) & 0xffff;
-                        if (role == 0) {
-                            const int slot = item % nMeta;
-                            const uint32_t round = (uint32_t)(item / nMeta);
-                            if (round > 0) mbarWait(barMetaEmpty + slot * 8, (round - 1) & 1u);
-                            const uint32_t fb = barMetaFull + slot * 8;
-                            mbarArriveExpectTx(fb, (uint32_t)meta);
-                            tmaLoad1D(metaRing + (uint32_t)slot * a.metaSlotBytes, src, (uint32_t)meta,
-                                      fb, pol);
-                        } else {
-                            const int ch = role - 1;
-                            const int pass = item / CELLS;
-                            const int q = (pass * CH + ch) * CELLS + c;
-                            const int slot = q % nChunk;
-                            const uint32_t round = (uint32_t)(q / nChunk);
-                            if (round > 0) mbarWait(barChunkEmpty + slot * 8, (round - 1) & 1u);
-                            const uint32_t fb = barChunkFull + slot * 8;
-                            const int cols = min(D, Nmax - ch * D);
-                            if (cols > 0) {
-                                const uint32_t bytes = (uint32_t)chunkBytes(K, nSt, cols);
-                                mbarArriveExpectTx(fb, bytes);
-                                tmaLoad1D(chunkRing + (uint32_t)slot * a.chunkSlotBytes,
-                                          src + meta + (size_t)ch * chunkBytes(K, nSt, D), bytes, fb,
-                                          pol);
-                            } else {
-                                mbarArrive(fb);  // nothing to load (empty cell / short stencils)
-                            }
-                        }
-                    }
-                    __syncwarp();
-                }
-            }
-            cur = nxt;
+    // ---- issue side (lanes 0..CELLS-1; lane c serves cell c of a pass) ----
+    const uint64_t pol = evictFirstPolicy();
+    const bool issuer = lane < CELLS;
+    // RecInfo of cell `lane` of this warp's i-th pass; w < 0: no such cell
+    auto fetchInfo = [&](int i) {
+        int4 v = make_int4(0, 0, 0, -1);
+        const int item = (warp + i * NW) * CELLS + lane;
+        if (issuer && i < myPasses && item < nItems)
+            v = __ldg(reinterpret_cast<const int4*>(a.recInfo + itemToCell(item)));
+        return v;
+    };
+    auto recPtr = [&](const int4& ri) {
+        return a.records + (((uint64_t)(uint32_t)ri.y << 32) | (uint32_t)ri.x);
+    };
+    auto issueHead = [&](const int4& ri, int hb) {
+        if (!issuer) return;
+        const uint32_t bar = bars + hb * 8;
+        if (ri.w >= 0) {
+            const uint32_t bytes = (uint32_t)ri.z & 0xffffu;
+            mbarArriveExpectTx(bar, bytes);
+            tmaLoad1D(headBuf + (uint32_t)(hb * CELLS + lane) * a.headSlotBytes, recPtr(ri), bytes, bar, pol);
+        } else {
+            mbarArrive(bar);
         }
-        return;
-    }
-    if (warp > NW) return;
+    };
+    auto issueTail = [&](const int4& ri) {
+        if (!issuer) return;
+        const uint32_t bytes = ri.w >= 0 ? ((uint32_t)ri.z >> 16) : 0u;
+        if (bytes) {
+            mbarArriveExpectTx(barTail, bytes);
+            tmaLoad1D(tailBuf + (uint32_t)lane * a.tailSlotBytes, recPtr(ri) + ((uint32_t)ri.z & 0xffffu),
+                      bytes, barTail, pol);
+        } else {
+            mbarArrive(barTail);
+        }
+    };
+    // chunk cursor: the next step to issue is chunk cCh of this warp's pass cPass
+    int4 cInfo;
+    const unsigned char* cSrc = nullptr;
+    int cCh = 0, cPass = 0;
+    auto cursorEnter = [&](const int4& ri) {
+        cInfo = ri;
+        cSrc = recPtr(ri) + ((uint32_t)ri.z & 0xffffu) + ((uint32_t)ri.z >> 16);
+        cCh = 0;
+    };
+    auto issueChunk = [&](int slot) {
+        if (issuer) {
+            const uint32_t bar = barRing + slot * 8;
+            uint32_t bytes = 0;
+            if (cInfo.w >= 0) bytes = (uint32_t)chunkBytes(K, cInfo.w & 0xffff, cInfo.w >> 16, cCh);
+            if (bytes) {
+                mbarArriveExpectTx(bar, bytes);
+                tmaLoad1D(ringBuf + (uint32_t)(slot * CELLS + lane) * a.chunkSlotBytes, cSrc, bytes, bar, pol);
+                cSrc += bytes;
+            } else {
+                mbarArrive(bar);
+            }
+        }
+        ++cCh;
+    };
 
-    // ===== consumers: CELLS cells per warp pass, one lane per (cell, stencil) =====
+    int4 infoCur = fetchInfo(0), infoNext = fetchInfo(1), infoNN = fetchInfo(2);
+    issueHead(infoCur, 0);
+    cursorEnter(infoCur);
+    for (int r = 0; r < R; ++r) issueChunk(r);  // R <= CH
+    if (cCh == CH) {
+        cPass = 1;
+        cursorEnter(infoNext);
+    }
+
+    // ---- consumer side: CELLS cells per pass, one lane per (cell, stencil) ----
     const int cslot = lane / SS;
     const int s = lane - cslot * SS;
     const bool fit01 = a.scheme == 1;
     const bool fitBounded = a.scheme == 0 && a.bounded;
+    int rs = 0;           // ring slot of the next step to consume
+    uint32_t rpar = 0;    // its mbarrier phase parity
 
-    for (int pass = warp; pass * CELLS < nItems; pass += NW) {
+    for (int i = 0; i < myPasses; ++i) {
+        const int pass = warp + i * NW;
         const int item = pass * CELLS + cslot;
         const bool valid = item < nItems;
-        const int mslot = item % nMeta;
-        const uint32_t mround = (uint32_t)(item / nMeta);
-        const uint32_t rec = metaRing + (uint32_t)mslot * a.metaSlotBytes;
+        const int hb = i & 1;
+        const uint32_t rec = headBuf + (uint32_t)(hb * CELLS + cslot) * a.headSlotBytes;
+        const uint32_t tail = tailBuf + (uint32_t)cslot * a.tailSlotBytes;
         const int cell = valid ? itemToCell(item) : 0;
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen);
 
-        if (valid) slotWait(barMetaFull + mslot * 8, relMeta + mslot * 4, mround);
-        __syncwarp();
+        // the other head slot and the tail slot were last read by the previous pass
+        issueHead(infoNext, hb ^ 1);
+        issueTail(infoCur);
+
+        mbarWait(bars + hb * 8, (uint32_t)(i >> 1) & 1u);
         int nSt = 0, nFc = 0, Nmax = 0;
-        uint32_t oIdx = 0, oFace = 0, oB = 0;
+        uint32_t oFace = 0, oIdx = 0;
         if (valid) {
             const int4 h0 = lds128i(rec), h1 = lds128i(rec + 16);
             nSt = h0.x;
             nFc = h0.y;
             Nmax = h0.z;
-            oIdx = h1.x;
-            oFace = h1.y;
-            oB = h1.z;
+            oFace = h1.x;
+            oIdx = h1.y;
         }
 #ifdef WENOEXT_KDEBUG
         if (valid && (nSt < 0 || nSt > SS || nFc < 0 || nFc > 64 || Nmax < 0 || Nmax > a.maxN ||
-                      oIdx > (uint32_t)a.metaSlotBytes || oFace > (uint32_t)a.metaSlotBytes ||
-                      oB > (uint32_t)a.metaSlotBytes)) {
+                      oIdx > (uint32_t)a.headSlotBytes || oFace > (uint32_t)a.headSlotBytes)) {
             if (atomicCAS(a.dbg, 0, 1) == 0) {
-                a.dbg[1] = item; a.dbg[2] = mslot; a.dbg[3] = (int)mround; a.dbg[4] = cell;
+                a.dbg[1] = item; a.dbg[2] = hb; a.dbg[3] = i; a.dbg[4] = cell;
                 a.dbg[5] = nSt; a.dbg[6] = nFc; a.dbg[7] = Nmax; a.dbg[8] = (int)oIdx;
                 a.dbg[10] = blockIdx.x; a.dbg[11] = threadIdx.x; a.dbg[12] = nItems;
             }
@@ -325,7 +318,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #ifdef WENOEXT_KDEBUG
             if (pfFace.x < 0 || pfFace.x >= a.nFaces || pfFace.y < -1 || pfFace.y >= a.nVals) {
                 if (atomicCAS(a.dbg, 0, 3) == 0) {
-                    a.dbg[1] = item; a.dbg[2] = mslot; a.dbg[3] = s; a.dbg[4] = cell;
+                    a.dbg[1] = item; a.dbg[2] = hb; a.dbg[3] = s; a.dbg[4] = cell;
                     a.dbg[5] = pfFace.x; a.dbg[6] = pfFace.y; a.dbg[7] = pfFace.z; a.dbg[8] = nFc;
                 }
                 pfFace = make_int4(0, 0, 0, 0);
@@ -336,30 +329,29 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN);
         }
 
-        // gather pipeline: column j of this lane's stencil (WENOCoeff.C:138-156)
-        const uint32_t idxBase = rec + oIdx + s * 4;
-        const uint32_t idxStride = (uint32_t)nSt * 4;
-        auto issue = [&](int j, double (&g)[CB]) {
-            if (j < N) {
-                int id = lds32(idxBase + (uint32_t)j * idxStride);
+        // gather of column j of this lane's stencil (WENOCoeff.C:138-156), branch-free:
+        // lanes without a stencil and columns beyond the cell's stencils load the cell's
+        // own value (difference exactly 0)
+        const uint32_t rowBytes = (uint32_t)nSt * 4;
+        auto gather = [&](uint32_t idxBlock, int j0, double (&g)[D][CB]) {
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                int id = cell;
+                if (act && j0 + d < Nmax) id = lds32(idxBlock + (uint32_t)d * rowBytes + s * 4);
 #ifdef WENOEXT_KDEBUG
                 if (id < 0 || id >= a.nVals) {
                     if (atomicCAS(a.dbg, 0, 2) == 0) {
-                        a.dbg[1] = item; a.dbg[2] = mslot; a.dbg[3] = j; a.dbg[4] = cell;
+                        a.dbg[1] = item; a.dbg[2] = j0 + d; a.dbg[3] = i; a.dbg[4] = cell;
                         a.dbg[5] = nSt; a.dbg[6] = id; a.dbg[7] = N; a.dbg[8] = s;
                     }
                     id = 0;
                 }
 #endif
-                loadVals<CB>(a.vals + (size_t)id * a.VS, g);
-            } else {
-#pragma unroll
-                for (int c = 0; c < CB; ++c) g[c] = cen[c];
+                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d]);
             }
         };
         double nx[D][CB];
-#pragma unroll
-        for (int d = 0; d < D; ++d) issue(d, nx[d]);
+        gather(rec + oIdx, 0, nx);
 
         // phase 1: coeffs[k][c] = sum_j A_s[k][j] * b_s[j][c]        (WENOCoeff.C:159)
         double acc[K][CB];
@@ -368,15 +360,16 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
             for (int c = 0; c < CB; ++c) acc[k][c] = 0.0;
         const uint32_t pairStride = (uint32_t)nSt * 16;
-        // Fast path (uniform meshes): every active lane of the warp has the same number
-        // of columns, a multiple of D -> no per-column predicate. Lanes without a
-        // stencil read the chunk of the first lane that has one (finite data) against
-        // b == 0.
-        const bool uniform = __all_sync(0xffffffffu, N == Nw || N == 0) && (Nw % D) == 0;
+        // Uniform meshes: every active lane of the warp has the same number of columns.
+        // Lanes without a stencil then read the matrix of the first stencil of their own
+        // cell (same shared-memory words as their neighbours, finite data) against b == 0.
+        const bool uniform = __all_sync(0xffffffffu, N == Nw || N == 0);
         const uint32_t have = __ballot_sync(0xffffffffu, N > 0);
-        const int srcLane = have ? __ffs(have) - 1 : 0;
+        const int own0 = cslot * SS;
+        const int srcLane = ((have >> own0) & 1u) ? own0 : (have ? __ffs(have) - 1 : 0);
+        const bool borrow = uniform && N == 0;
         const uint32_t pS = __shfl_sync(0xffffffffu, pairStride, srcLane);
-        const uint32_t pStr = (uniform && N == 0) ? pS : pairStride;
+        const uint32_t pStr = borrow ? pS : pairStride;
         for (int ch = 0; ch < CH; ++ch) {
             const int j0 = ch * D;
             double cu[D][CB];
@@ -384,22 +377,50 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             for (int d = 0; d < D; ++d)
 #pragma unroll
                 for (int c = 0; c < CB; ++c) cu[d][c] = nx[d][c] - cen[c];
+            // this pass's chunk step ch
+            mbarWait(barRing + rs * 8, rpar);
+            const uint32_t chunk = ringBuf + (uint32_t)(rs * CELLS + cslot) * a.chunkSlotBytes;
+            const int cols = max(0, min(D, Nmax - j0));  // columns stored in this cell's chunk
+            // gathers of the next chunk's columns (indices travel with this chunk)
+            if (j0 + D < Nw) gather(chunk + (uint32_t)chunkIdxOffset(K, nSt, cols), j0 + D, nx);
+            uint32_t Ap = chunk + (uint32_t)s * 16;
+            uint32_t Sp = chunk + (uint32_t)cols * KP * pairStride + (uint32_t)s * 8;
+            {
+                const uint32_t ApS = __shfl_sync(0xffffffffu, Ap, srcLane);
+                const uint32_t SpS = __shfl_sync(0xffffffffu, Sp, srcLane);
+                if (borrow) {
+                    Ap = ApS;
+                    Sp = SpS;
+                }
+            }
+            const int colsW = min(D, Nw - j0);  // warp-wide column count of this step
+            if (uniform && colsW == D) {
+                // full step, no predicates
 #pragma unroll
-            for (int d = 0; d < D; ++d) issue(j0 + D + d, nx[d]);
-            // this cell's chunk ch
-            const int q = (pass * CH + ch) * CELLS + cslot;
-            const int cs = q % nChunk;
-            const uint32_t cround = (uint32_t)(q / nChunk);
-            if (valid) slotWait(barChunkFull + cs * 8, relChunk + cs * 4, cround);
-            __syncwarp();
-            uint32_t Ap = chunkRing + (uint32_t)cs * a.chunkSlotBytes + (uint32_t)s * 16;
-            if (j0 < Nw) {
-                if (uniform) {
-                    const uint32_t ApS = __shfl_sync(0xffffffffu, Ap, srcLane);
-                    if (N == 0) Ap = ApS;
-                    uint32_t Sp = Ap - (N == 0 ? 0u : (uint32_t)s * 8) + (uint32_t)D * KP * pStr;
+                for (int d = 0; d < D; ++d) {
+                    uint32_t ap = Ap;
 #pragma unroll
-                    for (int d = 0; d < D; ++d) {
+                    for (int q2 = 0; q2 < KP; ++q2) {
+                        const double2 av = lds128(ap);
+                        ap += pStr;
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) {
+                            acc[2 * q2][c] = fma(av.x, cu[d][c], acc[2 * q2][c]);
+                            acc[2 * q2 + 1][c] = fma(av.y, cu[d][c], acc[2 * q2 + 1][c]);
+                        }
+                    }
+                    if constexpr (ODD) {
+                        const double a1 = lds64(Sp);
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
+                    }
+                    Ap += pStr * KP;
+                    Sp += pStr / 2;
+                }
+            } else if (colsW > 0) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    if (uniform ? (d < colsW) : (j0 + d < N)) {
                         uint32_t ap = Ap;
 #pragma unroll
                         for (int q2 = 0; q2 < KP; ++q2) {
@@ -417,48 +438,33 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                             for (int c = 0; c < CB; ++c)
                                 acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
                         }
-                        Ap += pStr * KP;
-                        Sp += pStr / 2;
                     }
-                } else {
-                    const int cols = min(D, Nmax - j0);  // columns stored in this chunk
-                    uint32_t Sp = Ap - (uint32_t)s * 8 + (uint32_t)(cols > 0 ? cols : 0) * KP * pairStride;
-#pragma unroll
-                    for (int d = 0; d < D; ++d) {
-                        if (j0 + d < N) {
-                            uint32_t ap = Ap;
-#pragma unroll
-                            for (int q2 = 0; q2 < KP; ++q2) {
-                                const double2 av = lds128(ap);
-                                ap += pairStride;
-#pragma unroll
-                                for (int c = 0; c < CB; ++c) {
-                                    acc[2 * q2][c] = fma(av.x, cu[d][c], acc[2 * q2][c]);
-                                    acc[2 * q2 + 1][c] = fma(av.y, cu[d][c], acc[2 * q2 + 1][c]);
-                                }
-                            }
-                            if constexpr (ODD) {
-                                const double a1 = lds64(Sp);
-#pragma unroll
-                                for (int c = 0; c < CB; ++c)
-                                    acc[K - 1][c] = fma(a1, cu[d][c], acc[K - 1][c]);
-                            }
-                        }
-                        Ap += pairStride * KP;
-                        Sp += pairStride / 2;
-                    }
+                    Ap += pStr * KP;
+                    Sp += pStr / 2;
                 }
             }
             __syncwarp();
-            if (valid && s == 0) slotRelease(barChunkEmpty + cs * 8, relChunk + cs * 4, cround);
+            // refill the slot just consumed with the step R ahead in this warp's stream
+            if (cPass < myPasses) {
+                issueChunk(rs);
+                if (cCh == CH) {
+                    ++cPass;
+                    cursorEnter(cPass - i == 1 ? infoNext : infoNN);
+                }
+            }
+            if (++rs == R) {
+                rs = 0;
+                rpar ^= 1u;
+            }
         }
         // phase 2: IS = c^T (B c) per component                  (WENOCoeff.C:190-196)
+        mbarWait(barTail, (uint32_t)i & 1u);
         double g[CB];
         {
             double IS[CB];
 #pragma unroll
             for (int c = 0; c < CB; ++c) IS[c] = 0.0;
-            const uint32_t Bb = rec + oB;
+            const uint32_t Bb = tail;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 double u[CB];
@@ -497,7 +503,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         // now acc = sum_s gamma_s c_s and g = gammaSum on every lane of the cell
 
         // phase 3: faces, one (or more) per lane
-        const uint32_t fdBase = rec + oB + (uint32_t)(K * K) * 8;
+        const uint32_t fdBase = tail + (uint32_t)(K * K) * 8;
         const uint32_t quirkA = fdBase + (uint32_t)(nFc * (K + 1)) * 8;
         // sumFlux with this cell's weighted polynomial (WENOUpwindFit.C:293-323)
         // (sum_s gamma_s c_s) / gammaSum / refFacAr is evaluated with reciprocals
@@ -614,7 +620,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             }
         }
         __syncwarp();
-        if (valid && s == 0) slotRelease(barMetaEmpty + mslot * 8, relMeta + mslot * 4, mround);
+        infoCur = infoNext;
+        infoNext = infoNN;
+        infoNN = fetchInfo(i + 3);
     }
 }
 }  // namespace
@@ -685,10 +693,11 @@ __global__ void patch_kernel(const PatchKernelArgs a) {
 }  // namespace
 
 size_t cellKernelSmemBytes(const CellKernelArgs& a) {
-    return (size_t)a.nMetaSlots * (a.metaSlotBytes + 20) + (size_t)a.nChunkSlots * (a.chunkSlotBytes + 20) + 64;
+    return (size_t)a.nWarps * ((size_t)a.warpBytes + (size_t)(3 + a.ringSteps) * 8);
 }
 
 bool cellKernelSupportsK(int K) { return K == 5 || K == 9 || K == 14 || K == 19; }
+int cellKernelMaxWarps() { return MAX_THREADS / 32; }
 
 namespace {
 template <int K, int CB, int CELLS, int D>
@@ -701,7 +710,7 @@ int launchT(const CellKernelArgs& a, int gridBlocks, size_t smemBytes, cudaStrea
             return 1;
         configured = smemBytes;
     }
-    const int threads = (a.nWarps + 1) * 32;
+    const int threads = a.nWarps * 32;
     weno_cell_kernel<K, CB, CELLS, D><<<gridBlocks, threads, smemBytes, st>>>(a);
     return 0;
 }
@@ -727,12 +736,14 @@ int launchK(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes, c
 // 3-D order 3: 19, 2-D order 2: 5, 2-D order 4: 14.
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st) {
-    if ((a.nWarps + 1) * 32 > MAX_THREADS || (a.cellsPerWarp != 4 && a.cellsPerWarp != 1)) return 1;
+    if (a.nWarps * 32 > MAX_THREADS || a.nWarps < 1 || a.ringSteps < 1 || a.ringSteps > a.nChunks ||
+        a.ringSteps > 29 || (a.cellsPerWarp != 4 && a.cellsPerWarp != 1))
+        return 1;
     switch (a.K) {
-        case 5: return launchK<5, 7>(a, CB, gridBlocks, smemBytes, st);
-        case 9: return launchK<9, 7>(a, CB, gridBlocks, smemBytes, st);
-        case 14: return launchK<14, 4>(a, CB, gridBlocks, smemBytes, st);
-        case 19: return launchK<19, 4>(a, CB, gridBlocks, smemBytes, st);
+        case 5: return launchK<5, chunkCols(5)>(a, CB, gridBlocks, smemBytes, st);
+        case 9: return launchK<9, chunkCols(9)>(a, CB, gridBlocks, smemBytes, st);
+        case 14: return launchK<14, chunkCols(14)>(a, CB, gridBlocks, smemBytes, st);
+        case 19: return launchK<19, chunkCols(19)>(a, CB, gridBlocks, smemBytes, st);
         default: return 1;
     }
 }

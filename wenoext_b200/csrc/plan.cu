@@ -25,6 +25,7 @@ void setError(const std::string& s) { g_lastError = s; }
         cudaError_t _e = (expr);                                                         \
         if (_e != cudaSuccess) {                                                         \
             setError(std::string(#expr) + ": " + cudaGetErrorString(_e));                \
+            cudaGetLastError(); /* reported: do not leave it for the next call */        \
             return WENOEXT_ERR_CUDA;                                                     \
         }                                                                                \
     } while (0)
@@ -71,14 +72,31 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
     const int nSt = a.cellNSt[cell], Nmax = a.cellNmax[cell], nFc = a.cellNFc[cell];
     const RecHeader lay = recLayout(K, nSt, Nmax, nFc);
     int32_t* Ns = reinterpret_cast<int32_t*>(rec + sizeof(RecHeader));
-    int32_t* idx = reinterpret_cast<int32_t*>(rec + lay.oIdx);
     int32_t* faceI = reinterpret_cast<int32_t*>(rec + lay.oFace);
-    double* Bm = reinterpret_cast<double*>(rec + lay.oB);
+    double* Bm = reinterpret_cast<double*>(rec + lay.headBytes);
     double* faceD = Bm + K * K;
     double* quirk = faceD + (size_t)nFc * (K + 1);
     const int D = chunkCols(K);
-    const int fullChunk = chunkBytes(K, nSt, D);
-    for (int i = lane; i < Nmax * nSt; i += 32) idx[i] = cell;  // unused entries: a valid index
+    const int nCh = (Nmax + D - 1) / D;
+    const int fullChunk = chunkBytes(K, nSt, 2 * D + 1, 0);  // D columns + D index rows
+    unsigned char* chunks = rec + lay.headBytes + lay.tailBytes;
+    // all chunks before the last two are full
+    auto chunkAt = [&](int ch) {
+        if (ch <= nCh - 2 || nCh < 2) return chunks + (size_t)ch * fullChunk;
+        return chunks + (size_t)(nCh - 2) * fullChunk + chunkBytes(K, nSt, Nmax, nCh - 2);
+    };
+    // gather-index row of column j: chunk 0's rows are in the head, the others in the
+    // preceding chunk (which always holds D columns)
+    auto idxRow = [&](int j) {
+        const int ch = j / D, jc = j - ch * D;
+        unsigned char* base = ch == 0 ? rec + lay.oIdx
+                                      : chunkAt(ch - 1) + chunkIdxOffset(K, nSt, D);
+        return reinterpret_cast<int32_t*>(base) + (size_t)jc * nSt;
+    };
+    for (int i = lane; i < Nmax * nSt; i += 32) {
+        const int j = i / nSt;
+        idxRow(j)[i - j * nSt] = cell;  // unused entries: a valid index, difference 0
+    }
     __syncwarp();
     bool halo = false;
     if (nSt > 0) {
@@ -93,7 +111,7 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
                 const int k = i / N, j = i - k * N;
                 const int ch = j / D, jc = j - ch * D;
                 const int cols = min(D, Nmax - ch * D);
-                double* chunk = reinterpret_cast<double*>(rec + lay.metaBytes + (size_t)ch * fullChunk);
+                double* chunk = reinterpret_cast<double*>(chunkAt(ch));
                 if (k < 2 * KP)
                     chunk[((size_t)(jc * KP + (k >> 1)) * nSt + live) * 2 + (k & 1)] = src[i];
                 else
@@ -108,7 +126,7 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
                     flat = a.nCells + (int32_t)a.haloOff[pm] + id;
                     halo = true;
                 }
-                idx[j * nSt + live] = flat;
+                idxRow(j)[live] = flat;
             }
             live++;
         }
@@ -214,7 +232,6 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     P->patches.assign(d->patches, d->patches + d->nPatches);
     if (const char* e = getenv("WENOEXT_WARPS")) P->cfgWarps = atoi(e);
     if (const char* e = getenv("WENOEXT_CELLS")) P->cfgCells = atoi(e);
-    if (const char* e = getenv("WENOEXT_META_PASSES")) P->cfgMetaPasses = atoi(e);
     if (const char* e = getenv("WENOEXT_SLOTS")) P->cfgSlots = atoi(e);
     if (const char* e = getenv("WENOEXT_GRID")) P->cfgGrid = atoi(e);
     if (const char* e = getenv("WENOEXT_SMEM_KB")) P->cfgSmemKB = atoi(e);
@@ -311,12 +328,19 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         cellNmax[c] = Nmax;
         cellNFc[c] = nFc;
         const RecHeader lay = recLayout(K, nSt, Nmax, nFc);
-        const int64_t tot = (int64_t)lay.metaBytes + recMatrixBytes(K, nSt, Nmax);
+        const int64_t tot = (int64_t)lay.headBytes + lay.tailBytes + recMatrixBytes(K, nSt, Nmax);
         recInfo[c].off = recOff;
-        recInfo[c].metaBytes = lay.metaBytes;
+        recInfo[c].headBytes = (uint16_t)lay.headBytes;
+        recInfo[c].tailBytes = (uint16_t)lay.tailBytes;
         recInfo[c].nSt = (int16_t)nSt;
         recInfo[c].Nmax = (int16_t)Nmax;
-        P->maxMetaBytes = std::max(P->maxMetaBytes, (int64_t)lay.metaBytes);
+        if (lay.headBytes > 65520 || lay.tailBytes > 65520 || Nmax > 32767) {
+            setError("cell record parts too large (polynomial order too high)");
+            delete P;
+            return WENOEXT_ERR_INVALID;
+        }
+        P->maxHeadBytes = std::max(P->maxHeadBytes, (int64_t)lay.headBytes);
+        P->maxTailBytes = std::max(P->maxTailBytes, (int64_t)lay.tailBytes);
         recOff += tot;
         P->maxRecordBytes = std::max(P->maxRecordBytes, tot);
         P->maxN = std::max(P->maxN, Nmax);
@@ -684,16 +708,16 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     a.dbg = P->dbg;
 #endif
     const int D = chunkCols(P->K);
-    a.nChunks = (P->maxN + D - 1) / D;
-    a.metaSlotBytes = (int)((P->maxMetaBytes + 127) / 128 * 128);
-    a.chunkSlotBytes = (chunkBytes(P->K, P->maxSt, D) + 127) / 128 * 128;
-    // Launch geometry. A consumer warp takes cellsPerWarp consecutive cells per
-    // pass (one lane per (cell, stencil)), so the ring must hold at least one pass;
-    // the rest of the slots are records in flight (an SM needs ~64 KB in flight to
-    // cover the HBM latency-bandwidth product). No scratch shared memory.
-    // Shared memory: a ring of meta slots (a few passes deep) and a ring of matrix
-    // chunk slots (everything else). Chunks are released as their columns are
-    // consumed, so most of the chunk ring is data in flight.
+    a.nChunks = std::max(1, (P->maxN + D - 1) / D);
+    // Launch geometry. Every warp of the CTA runs its own TMA pipeline: two head
+    // slots (this pass and the next), one tail slot and a ring of `ringSteps` chunk
+    // steps, each for cellsPerWarp cells. Slot strides are 32 (mod 128) bytes so that
+    // the cells of one pass, which read the same field at the same time, do not fall
+    // into the same shared-memory banks. No scratch shared memory.
+    auto bankStride = [](int64_t bytes) { return (int)((bytes + 95) / 128 * 128 + 32); };
+    a.headSlotBytes = bankStride(P->maxHeadBytes);
+    a.tailSlotBytes = bankStride(P->maxTailBytes);
+    a.chunkSlotBytes = bankStride(chunkBytes(P->K, P->maxSt, 2 * D + 1, 0));
     const size_t budget =
         (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 64;
     int cpw = P->maxSt <= 8 ? 4 : 1;
@@ -702,35 +726,29 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
         setError("unsupported stencil shape (more than 32 stencils per cell)");
         return WENOEXT_ERR_INVALID;
     }
-    const int nw = std::max(1, std::min(7, P->cfgWarps > 0 ? P->cfgWarps : 7));
-    // meta ring: nw + 2 passes deep, but at most a quarter of the shared memory
-    int metaPasses = std::min(nw + 2, (int)(budget / 4 / ((size_t)cpw * (a.metaSlotBytes + 20))));
-    metaPasses = std::max(metaPasses, 2);
-    if (P->cfgMetaPasses > 0) metaPasses = P->cfgMetaPasses;
-    const size_t perSlotExtra = 16 + 4;  // two mbarriers + release counter
-    int nMeta = cpw * metaPasses;
-    size_t metaTotal = (size_t)nMeta * (a.metaSlotBytes + perSlotExtra);
-    int nChunk = budget > metaTotal + 64
-                     ? (int)((budget - metaTotal - 64) / ((size_t)a.chunkSlotBytes + perSlotExtra))
-                     : 0;
-    if (P->cfgSlots > 0) nChunk = std::min(nChunk, P->cfgSlots);
-    nChunk = std::min(nChunk, 1024);
-    if (nChunk < cpw) {
-        // very large records (high order): shrink the meta ring to the minimum
-        nMeta = cpw;
-        metaTotal = (size_t)nMeta * (a.metaSlotBytes + perSlotExtra);
-        nChunk = budget > metaTotal + 64
-                     ? (int)((budget - metaTotal - 64) / ((size_t)a.chunkSlotBytes + perSlotExtra))
-                     : 0;
+    auto warpBytesFor = [&](int ring) {
+        return (size_t)cpw * (2 * (size_t)a.headSlotBytes + a.tailSlotBytes +
+                              (size_t)ring * a.chunkSlotBytes);
+    };
+    auto perWarp = [&](int ring) { return warpBytesFor(ring) + (size_t)(3 + ring) * 8; };
+    // ring depth 3 (one step being consumed, two in flight) unless that leaves fewer
+    // than 4 warps; the ring cannot be deeper than the number of steps of a cell
+    int ring = std::min(3, a.nChunks);
+    if (P->cfgSlots > 0) ring = std::min(P->cfgSlots, a.nChunks);
+    int nw = (int)std::min<size_t>(cellKernelMaxWarps(), budget / perWarp(ring));
+    while (nw < 4 && ring > 1 && P->cfgSlots <= 0) {
+        --ring;
+        nw = (int)std::min<size_t>(cellKernelMaxWarps(), budget / perWarp(ring));
     }
-    if (nChunk < cpw) {
-        setError("cell records do not fit the shared-memory rings (polynomial order too high)");
+    if (P->cfgWarps > 0) nw = std::min(nw, P->cfgWarps);
+    if (nw < 1) {
+        setError("cell records do not fit the shared memory (polynomial order too high)");
         return WENOEXT_ERR_INVALID;
     }
     a.cellsPerWarp = cpw;
     a.nWarps = nw;
-    a.nMetaSlots = nMeta;
-    a.nChunkSlots = nChunk;
+    a.ringSteps = ring;
+    a.warpBytes = (int32_t)warpBytesFor(ring);
     const size_t smem = cellKernelSmemBytes(a);
     const int nTiles = (nWork + 31) / 32;
     int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);

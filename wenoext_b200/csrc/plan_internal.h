@@ -51,7 +51,7 @@ struct wenoext_plan {
     wenoext::RecInfo* recInfo = nullptr;
     int32_t maxN = 0;
     int32_t* dbg = nullptr;  // WENOEXT_KDEBUG builds only
-    int64_t recordBytesTotal = 0, maxRecordBytes = 0, maxMetaBytes = 0;
+    int64_t recordBytesTotal = 0, maxRecordBytes = 0, maxHeadBytes = 0, maxTailBytes = 0;
     int32_t maxSt = 0, maxFc = 0;
     int32_t* cellListInterior = nullptr;
     int32_t* cellListBoundary = nullptr;
@@ -98,5 +98,5 @@ struct wenoext_plan {
     size_t timeUsed = 0;
     wenoext_plan_info info{};
     // launch geometry overrides (tuning): 0 = auto
-    int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0, cfgSmemKB = 0, cfgCells = 0, cfgMetaPasses = 0;
+    int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0, cfgSmemKB = 0, cfgCells = 0;
 };
