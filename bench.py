@@ -96,6 +96,13 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
+    def mark(self):
+        """start of the timed region: earlier samples are dropped (unless nothing follows)"""
+        t0 = time.time()
+        while self.proc and not self.lines and time.time() - t0 < 5.0:
+            time.sleep(0.01)  # nvidia-smi still starting
+        self.first = len(self.lines)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -103,7 +110,8 @@ class ClockSampler:
         self.t.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        timed = self.lines[getattr(self, "first", 0):]
+        for ln in (timed if timed else self.lines[-3:]):
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -238,15 +246,19 @@ def run_ours(a):
     def step():
         plan.correction(FIT, a.bounded, vf, phi, out=out)
 
+    # every rank samples its own GPU; rank 0 reports the slowest. nvidia-smi needs a while to
+    # start (longer with 8 of them), so it is started before the warm-up and only the samples
+    # taken during the timed region are used.
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(a.warmup):
         step()
     # ---- timed region: device-resident inputs, K steps, CUDA events ----
     plan.enable_kernel_timing(True)
-    sampler = ClockSampler(local)  # every rank samples its own GPU; rank 0 reports the slowest
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches = 0
     barrier()
+    sampler.mark()
     e0.record()
     for _ in range(a.steps):
         step()
@@ -358,8 +370,19 @@ def run_ours(a):
         dist.destroy_process_group()
 
 
+def _quiet_stdout():
+    """Libraries (NCCL's version banner, torchrun) write to fd 1; the contract is ONE JSON
+    line on stdout. Route fd 1 to stderr for the run and keep the real stdout for the result."""
+    real = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
     args = parse()
+    _real_stdout = _quiet_stdout()
+    sys.stdout = _real_stdout
     if args.impl == "reference":
         run_reference(args)
     else:
