@@ -257,8 +257,8 @@ def run_ours(a):
     plan.enable_kernel_timing(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches = 0
-    barrier()
     sampler.mark()
+    barrier()
     e0.record()
     for _ in range(a.steps):
         step()

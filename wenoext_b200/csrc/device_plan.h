@@ -16,7 +16,8 @@
 //     RecHeader                                   32 B
 //     int32  N[nSt]              columns of each stencil, pad to 16 B
 //     int32  faceI[nFc][4]       face id, flat index of the cell across (-1 none), kind, 0
-//     int32  idx[min(D,Nmax)][nSt]  gather indices of the columns of chunk 0
+//     int32  idx[min(GA*D,Nmax)][nSt]  gather indices of the columns of chunks 0..GA-1
+//                                (GA = GATHER_AHEAD)
 //     pad to 16 B                                          -> headBytes
 //   TAIL (needed after the matrix phase)
 //     double B[K*K]              B()[cell], row-major
@@ -26,7 +27,7 @@
 //     pad to 16 B                                          -> tailBytes
 //   CHUNK ch: columns [ch*D, ch*D+cols) of LSmatrix()[cell][s] for all stencils
 //   (bitwise copies, permuted), cols = min(D, Nmax - ch*D), followed by the gather
-//   indices of the NEXT chunk's columns (icols = clamp(Nmax - (ch+1)*D, 0, D)):
+//   indices of the columns of chunk ch+GA (icols = clamp(Nmax - (ch+GA)*D, 0, D)):
 //     double2 pairs[cols][K/2][nSt]   (A_s[2q][j], A_s[2q+1][j])
 //     double  single[cols][nSt]       A_s[K-1][j]            (K odd only)
 //     int32   idx[icols][nSt]
@@ -61,15 +62,30 @@ struct RecInfo {
 
 // columns per matrix chunk (also the unroll depth of the kernel's column loop)
 __host__ __device__ constexpr int chunkCols(int K) { return K <= 9 ? 3 : 2; }
+// the gather indices of chunk ch + GATHER_AHEAD travel with chunk ch (the kernel
+// issues the gathers of a column GATHER_AHEAD chunk steps before it needs the value)
+constexpr int GATHER_AHEAD = 2;
 __host__ __device__ inline int clampCols(int n, int D) { return n < 0 ? 0 : (n > D ? D : n); }
 // bytes of chunk ch of a cell with nSt stencils and Nmax columns
 __host__ __device__ inline int chunkBytes(int K, int nSt, int Nmax, int ch) {
     const int D = chunkCols(K);
-    const int cols = clampCols(Nmax - ch * D, D), icols = clampCols(Nmax - (ch + 1) * D, D);
+    const int cols = clampCols(Nmax - ch * D, D);
+    const int icols = clampCols(Nmax - (ch + GATHER_AHEAD) * D, D);
     return (cols * nSt * K * 8 + icols * nSt * 4 + 15) & ~15;
 }
-// byte offset of the next chunk's gather indices inside chunk ch
+// byte offset of the travelling gather indices inside a chunk holding `cols` columns
 __host__ __device__ inline int chunkIdxOffset(int K, int nSt, int cols) { return cols * nSt * K * 8; }
+// byte offset of chunk ch from the first chunk: all chunks up to cf1 are full
+__host__ __device__ inline int64_t chunkOffset(int K, int nSt, int Nmax, int ch) {
+    const int D = chunkCols(K);
+    int cf1 = Nmax / D - GATHER_AHEAD;  // first chunk that may not be full
+    if (cf1 < 0) cf1 = 0;
+    const int full = (D * nSt * K * 8 + D * nSt * 4 + 15) & ~15;
+    if (ch <= cf1) return (int64_t)ch * full;
+    int64_t o = (int64_t)cf1 * full;
+    for (int c = cf1; c < ch; ++c) o += chunkBytes(K, nSt, Nmax, c);
+    return o;
+}
 
 // kind bits of a listed face
 enum : int32_t {
@@ -91,7 +107,7 @@ __host__ __device__ inline RecHeader recLayout(int K, int nSt, int Nmax, int nFc
     h.oFace = o;
     o += 16 * nFc;
     h.oIdx = o;
-    o += 4 * clampCols(Nmax, D) * nSt;
+    o += 4 * clampCols(Nmax, GATHER_AHEAD * D) * nSt;
     h.headBytes = (o + 15) & ~15;
     h.tailBytes = (8 * (K * K + nFc * (K + 1) + K) + 15) & ~15;
     return h;

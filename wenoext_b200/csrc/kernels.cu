@@ -129,15 +129,23 @@ __device__ __forceinline__ double intPowD(double base, uint32_t e) {
     return t;
 }
 
+__device__ __forceinline__ uint64_t evictLastPolicy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+// Cell values are re-read by every neighbouring stencil while 26 GB of records
+// stream through the L2 once: keep them resident (evict_last) against the stream.
 template <int CB>
-__device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB]) {
+__device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB], uint64_t pol) {
     if constexpr (CB == 1) {
-        v[0] = __ldg(p);
+        asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v[0]) : "l"(p), "l"(pol));
     } else {
-        double2 t = __ldg(reinterpret_cast<const double2*>(p));
-        v[0] = t.x;
-        v[1] = t.y;
-        if constexpr (CB == 3) v[2] = __ldg(p + 2);
+        asm volatile("ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+                     : "=d"(v[0]), "=d"(v[1])
+                     : "l"(p), "l"(pol));
+        if constexpr (CB == 3)
+            asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v[2]) : "l"(p + 2), "l"(pol));
     }
 }
 
@@ -190,6 +198,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 
     // ---- issue side (lanes 0..CELLS-1; lane c serves cell c of a pass) ----
     const uint64_t pol = evictFirstPolicy();
+    const uint64_t polV = evictLastPolicy();
     const bool issuer = lane < CELLS;
     // RecInfo of cell `lane` of this warp's i-th pass; w < 0: no such cell
     auto fetchInfo = [&](int i) {
@@ -275,7 +284,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const uint32_t tail = tailBuf + (uint32_t)cslot * a.tailSlotBytes;
         const int cell = valid ? itemToCell(item) : 0;
         double cen[CB];
-        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen);
+        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV);
 
         // the other head slot and the tail slot were last read by the previous pass
         issueHead(infoNext, hb ^ 1);
@@ -326,7 +335,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #endif
             pfFlux = __ldg(a.flux + pfFace.x);
             if (fitBounded && (pfFace.z >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
-                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN);
+                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN, polV);
         }
 
         // gather of column j of this lane's stencil (WENOCoeff.C:138-156), branch-free:
@@ -347,11 +356,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                     id = 0;
                 }
 #endif
-                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d]);
+                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d], polV);
             }
         };
-        double nx[D][CB];
-        gather(rec + oIdx, 0, nx);
+        // two buffers: the columns of step ch are gathered GATHER_AHEAD = 2 steps earlier
+        static_assert(GATHER_AHEAD == 2, "the chunk loop below alternates two gather buffers");
+        double nxA[D][CB], nxB[D][CB];
+        gather(rec + oIdx, 0, nxA);
+        gather(rec + oIdx + (uint32_t)D * rowBytes, D, nxB);
 
         // phase 1: coeffs[k][c] = sum_j A_s[k][j] * b_s[j][c]        (WENOCoeff.C:159)
         double acc[K][CB];
@@ -370,7 +382,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const bool borrow = uniform && N == 0;
         const uint32_t pS = __shfl_sync(0xffffffffu, pairStride, srcLane);
         const uint32_t pStr = borrow ? pS : pairStride;
-        for (int ch = 0; ch < CH; ++ch) {
+        auto step = [&](const int ch, double (&nx)[D][CB]) {
             const int j0 = ch * D;
             double cu[D][CB];
 #pragma unroll
@@ -381,8 +393,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             mbarWait(barRing + rs * 8, rpar);
             const uint32_t chunk = ringBuf + (uint32_t)(rs * CELLS + cslot) * a.chunkSlotBytes;
             const int cols = max(0, min(D, Nmax - j0));  // columns stored in this cell's chunk
-            // gathers of the next chunk's columns (indices travel with this chunk)
-            if (j0 + D < Nw) gather(chunk + (uint32_t)chunkIdxOffset(K, nSt, cols), j0 + D, nx);
+            // gathers of the columns two steps ahead (their indices travel with this chunk)
+            if (j0 + GATHER_AHEAD * D < Nw)
+                gather(chunk + (uint32_t)chunkIdxOffset(K, nSt, cols), j0 + GATHER_AHEAD * D, nx);
             uint32_t Ap = chunk + (uint32_t)s * 16;
             uint32_t Sp = chunk + (uint32_t)cols * KP * pairStride + (uint32_t)s * 8;
             {
@@ -456,6 +469,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 rs = 0;
                 rpar ^= 1u;
             }
+        };
+        for (int ch = 0; ch < CH; ch += 2) {
+            step(ch, nxA);
+            if (ch + 1 < CH) step(ch + 1, nxB);
         }
         // phase 2: IS = c^T (B c) per component                  (WENOCoeff.C:190-196)
         mbarWait(barTail, (uint32_t)i & 1u);
@@ -600,7 +617,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                             for (int c = 0; c < CB; ++c) psiN[c] = pfPsiN[c];
                         } else {
-                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN);
+                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN, polV);
                         }
 #pragma unroll
                         for (int c = 0; c < CB; ++c) {

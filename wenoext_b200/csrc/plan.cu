@@ -77,20 +77,15 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
     double* faceD = Bm + K * K;
     double* quirk = faceD + (size_t)nFc * (K + 1);
     const int D = chunkCols(K);
-    const int nCh = (Nmax + D - 1) / D;
-    const int fullChunk = chunkBytes(K, nSt, 2 * D + 1, 0);  // D columns + D index rows
     unsigned char* chunks = rec + lay.headBytes + lay.tailBytes;
-    // all chunks before the last two are full
-    auto chunkAt = [&](int ch) {
-        if (ch <= nCh - 2 || nCh < 2) return chunks + (size_t)ch * fullChunk;
-        return chunks + (size_t)(nCh - 2) * fullChunk + chunkBytes(K, nSt, Nmax, nCh - 2);
-    };
-    // gather-index row of column j: chunk 0's rows are in the head, the others in the
-    // preceding chunk (which always holds D columns)
+    auto chunkAt = [&](int ch) { return chunks + chunkOffset(K, nSt, Nmax, ch); };
+    // gather-index row of column j: the rows of chunks 0..GA-1 are in the head, the
+    // others in chunk ch-GA (which always holds D columns)
     auto idxRow = [&](int j) {
         const int ch = j / D, jc = j - ch * D;
-        unsigned char* base = ch == 0 ? rec + lay.oIdx
-                                      : chunkAt(ch - 1) + chunkIdxOffset(K, nSt, D);
+        unsigned char* base = ch < GATHER_AHEAD
+                                  ? rec + lay.oIdx + (size_t)ch * D * nSt * 4
+                                  : chunkAt(ch - GATHER_AHEAD) + chunkIdxOffset(K, nSt, D);
         return reinterpret_cast<int32_t*>(base) + (size_t)jc * nSt;
     };
     for (int i = lane; i < Nmax * nSt; i += 32) {
@@ -717,7 +712,7 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
     auto bankStride = [](int64_t bytes) { return (int)((bytes + 95) / 128 * 128 + 32); };
     a.headSlotBytes = bankStride(P->maxHeadBytes);
     a.tailSlotBytes = bankStride(P->maxTailBytes);
-    a.chunkSlotBytes = bankStride(chunkBytes(P->K, P->maxSt, 2 * D + 1, 0));
+    a.chunkSlotBytes = bankStride(chunkBytes(P->K, P->maxSt, (GATHER_AHEAD + 1) * D, 0));
     const size_t budget =
         (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 64;
     int cpw = P->maxSt <= 8 ? 4 : 1;
@@ -731,13 +726,18 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
                               (size_t)ring * a.chunkSlotBytes);
     };
     auto perWarp = [&](int ring) { return warpBytesFor(ring) + (size_t)(3 + ring) * 8; };
-    // ring depth 3 (one step being consumed, two in flight) unless that leaves fewer
-    // than 4 warps; the ring cannot be deeper than the number of steps of a cell
-    int ring = std::min(3, a.nChunks);
-    if (P->cfgSlots > 0) ring = std::min(P->cfgSlots, a.nChunks);
-    int nw = (int)std::min<size_t>(cellKernelMaxWarps(), budget / perWarp(ring));
-    while (nw < 4 && ring > 1 && P->cfgSlots <= 0) {
-        --ring;
+    // ring depth: 3 (one step being consumed, two in flight) or 2, whichever lets more
+    // warps run; never deeper than the number of steps of a cell
+    int ring = 0, nw = 0;
+    for (int r = std::min(3, a.nChunks); r >= 1; --r) {
+        const int w = (int)std::min<size_t>(cellKernelMaxWarps(), budget / perWarp(r));
+        if (w > nw) {
+            nw = w;
+            ring = r;
+        }
+    }
+    if (P->cfgSlots > 0) {
+        ring = std::min(P->cfgSlots, a.nChunks);
         nw = (int)std::min<size_t>(cellKernelMaxWarps(), budget / perWarp(ring));
     }
     if (P->cfgWarps > 0) nw = std::min(nw, P->cfgWarps);
