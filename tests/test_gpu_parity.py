@@ -230,3 +230,24 @@ def test_no_gpu_no_fallback_message():
     case = case_of("hex8")
     with pytest.raises(wx.WenoextError):
         wx.Plan(case.desc, device=63)
+
+
+@pytest.mark.parametrize("sides", [(0,) * 6, (2, 2, 0, 0, 0, 0)])
+@pytest.mark.parametrize("scheme,bounded,nComp", [(FIT, 1, 3), (FIT01, 1, 1), (FIT, 0, 2)])
+def test_pipelined_host_path_equals_device_path(sides, scheme, bounded, nComp):
+    """Host buffers on a serial plan take the slab-pipelined path (H2D, kernel and D2H
+    overlapped); it must return exactly what the device-buffer path returns."""
+    import torch
+    case = wx.BoxCase((48, 48, 40), 2, sides=sides)
+    plan = wx.Plan(case.desc)
+    vf = _fields(case, nComp, seed=5)
+    flux = H.face_flux(case.Sf, U=(1.0, -1.0, 0.5), zero_frac=0.02)
+    host = np.asarray(plan.correction(scheme, bounded, vf, flux)).reshape(case.nFaces, -1)
+    dvf = torch.from_numpy(np.ascontiguousarray(vf)).cuda()
+    dfl = torch.from_numpy(flux).cuda()
+    out = torch.empty((case.nFaces, nComp), dtype=torch.float64, device="cuda")
+    plan.correction(scheme, bounded, dvf, dfl, out=out)
+    np.testing.assert_array_equal(host, out.cpu().numpy())
+    ref = Oracle("c").correction(case, scheme, bounded, vf, flux)
+    assert H.normwise_err(host, ref) <= TOL
+    plan.destroy()

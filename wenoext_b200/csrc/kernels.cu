@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         nItems = nMy * TILE - (lastTile == nTiles - 1 ? nTiles * TILE - a.nWork : 0);
     }
     auto itemToCell = [&](int n) {
-        const int w = ((int)blockIdx.x + (n / TILE) * (int)gridDim.x) * TILE + (n % TILE);
+        const int w = a.workBase + ((int)blockIdx.x + (n / TILE) * (int)gridDim.x) * TILE + (n % TILE);
         return a.cellList ? __ldg(a.cellList + w) : w;
     };
     const int nPasses = (nItems + CELLS - 1) / CELLS;           // of the CTA

@@ -1,6 +1,7 @@
 // Device plan creation (flatten + upload + on-device record expansion) and the
 // per-call orchestration of correction(). See include/wenoext_b200.h.
 #include <cuda_runtime.h>
+#include <climits>
 #include <dlfcn.h>
 
 #include <algorithm>
@@ -58,6 +59,7 @@ struct ExpandArgs {
     const int32_t* enumIdx;      // [K] cube index of coefficient k
     unsigned char* records;
     uint8_t* cellHasHalo;
+    int32_t* cellExt;  // [nCells][3]: max local value index read, min / max listed face
 };
 
 // One warp per cell: copies the de-duplicated matrices and the per-cell / per-face
@@ -94,6 +96,7 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
     }
     __syncwarp();
     bool halo = false;
+    int maxId = cell, minFace = INT32_MAX, maxFace = -1;  // what the cell reads (extents)
     if (nSt > 0) {
         int live = 0;
         for (int64_t s = a.cellStencilStart[cell]; s < a.cellStencilStart[cell + 1]; ++s) {
@@ -120,6 +123,8 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
                 if (pm >= 0) {
                     flat = a.nCells + (int32_t)a.haloOff[pm] + id;
                     halo = true;
+                } else {
+                    maxId = max(maxId, id);
                 }
                 idxRow(j)[live] = flat;
             }
@@ -145,6 +150,9 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
             if (type < 0) continue;
             other = a.bfNbrCell ? a.bfNbrCell[f - a.nInternalFaces] : -1;
         }
+        if (other >= 0 && other < a.nCells) maxId = max(maxId, other);
+        minFace = min(minFace, f);
+        maxFace = max(maxFace, f);
         double* fd = faceD + (size_t)fOut * (K + 1);
         for (int k = lane; k < K; k += 32)
             fd[k] = a.intBasTrans[((size_t)f * 2 + side) * a.cube + a.enumIdx[k]];
@@ -158,7 +166,11 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
         fOut++;
     }
     halo = __any_sync(0xffffffffu, halo);
+    maxId = __reduce_max_sync(0xffffffffu, maxId);
     if (lane == 0) {
+        a.cellExt[(size_t)cell * 3 + 0] = maxId;
+        a.cellExt[(size_t)cell * 3 + 1] = minFace;
+        a.cellExt[(size_t)cell * 3 + 2] = maxFace;
         RecHeader h = lay;
         h.flags = halo ? 1 : 0;
         *reinterpret_cast<RecHeader*>(rec) = h;
@@ -400,10 +412,12 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     rc = rc ? rc : up(&dEnum, enumIdx.data(), enumIdx.size());
     if (P->nSendTotal > 0) rc = rc ? rc : upload(&P->sendIds, d->sendHaloCellID, (size_t)P->nSendTotal);
     uint8_t* dHasHalo = nullptr;
+    int32_t* dCellExt = nullptr;
     if (!rc) {
         cudaError_t e = cudaMalloc((void**)&P->records, (size_t)P->recordBytesTotal);
         if (e == cudaSuccess) e = cudaMemset(P->records, 0, (size_t)P->recordBytesTotal);
         if (e == cudaSuccess) e = cudaMalloc((void**)&dHasHalo, (size_t)nC);
+        if (e == cudaSuccess) e = cudaMalloc((void**)&dCellExt, (size_t)nC * 3 * sizeof(int32_t));
         if (e != cudaSuccess) {
             setError(std::string("cudaMalloc(records): ") + cudaGetErrorString(e));
             rc = WENOEXT_ERR_CUDA;
@@ -435,6 +449,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         ea.enumIdx = dEnum;
         ea.records = P->records;
         ea.cellHasHalo = dHasHalo;
+        ea.cellExt = dCellExt;
         const int64_t threads = (int64_t)nC * 32;
         expand_records_kernel<<<(unsigned)((threads + 255) / 256), 256>>>(ea);
         cudaError_t e = cudaDeviceSynchronize();
@@ -456,8 +471,43 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
             rc = rc ? rc : upload(&P->cellListBoundary, lb.data(), lb.size());
         }
     }
+    // Slabs for the pipelined host-buffer path (serial plans): what a prefix of the cells
+    // reads (cell values, fluxes) and which faces are final once it has been processed.
+    if (!rc && P->nProcs == 1) {
+        int S = 8;
+        if (const char* e = getenv("WENOEXT_E2E_SLABS")) S = std::max(1, atoi(e));
+        if (nC < S * 8192) S = 1;
+        if (S > 1) {
+            std::vector<int32_t> ext((size_t)nC * 3);
+            cudaMemcpy(ext.data(), dCellExt, ext.size() * sizeof(int32_t), cudaMemcpyDeviceToHost);
+            const int per = ((nC + S - 1) / S + 31) / 32 * 32;
+            P->slabEnd.clear();
+            for (int k = 0; k < S; ++k) P->slabEnd.push_back(std::min(nC, (k + 1) * per));
+            while (P->slabEnd.size() > 1 && P->slabEnd[P->slabEnd.size() - 2] >= nC) P->slabEnd.pop_back();
+            S = (int)P->slabEnd.size();
+            P->needVf.assign(S, 0);
+            P->needFlux.assign(S, 0);
+            P->doneFaces.assign(S, 0);
+            int c = 0, mv = 0, mf = 0;
+            for (int k = 0; k < S; ++k) {
+                for (; c < P->slabEnd[k]; ++c) {
+                    mv = std::max(mv, ext[(size_t)c * 3] + 1);
+                    mf = std::max(mf, ext[(size_t)c * 3 + 2] + 1);
+                }
+                P->needVf[k] = std::min(nC, std::max(mv, P->slabEnd[k]));
+                P->needFlux[k] = mf;
+            }
+            int lo = P->nInt;
+            c = nC;
+            for (int k = S - 1; k >= 0; --k) {
+                for (; c > P->slabEnd[k]; --c) lo = std::min(lo, ext[(size_t)(c - 1) * 3 + 1]);
+                P->doneFaces[k] = std::min(lo, P->nInt);
+            }
+        }
+    }
     for (void* t : temps) cudaFree(t);
     if (dHasHalo) cudaFree(dHasHalo);
+    if (dCellExt) cudaFree(dCellExt);
     if (rc) {
         wenoext_plan_destroy(P);
         return rc;
@@ -494,6 +544,9 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
         if (NcclApi* n = ncclApi()) n->CommDestroy(P->comm);
     }
     if (P->commStream) cudaStreamDestroy(P->commStream);
+    if (P->sIn) cudaStreamDestroy(P->sIn);
+    if (P->sOut) cudaStreamDestroy(P->sOut);
+    for (cudaEvent_t e : P->evSlab) cudaEventDestroy(e);
     cudaEvent_t evs[] = {P->evA, P->evB, P->evC};
     for (cudaEvent_t e : evs)
         if (e) cudaEventDestroy(e);
@@ -668,13 +721,14 @@ static int ensureBuf(double** p, size_t* cap, size_t n) {
     return 0;
 }
 
-static int launchCells(wenoext_plan* P, const int32_t* list, int nWork) {
+static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase = 0) {
     if (nWork <= 0) return 0;
     const wenoext_call& c = P->call;
     CellKernelArgs a{};
     a.records = P->records;
     a.recInfo = P->recInfo;
     a.cellList = list;
+    a.workBase = workBase;
     a.nWork = nWork;
     a.K = P->K;
     a.nComp = c.nComp;
@@ -915,6 +969,10 @@ static int phase2(wenoext_plan* P) {
 // ---------------------------------------------------------------------------
 // public per-step entry points
 // ---------------------------------------------------------------------------
+static bool usePipeline(const wenoext_plan* P, int nComp) {
+    return P->nProcs == 1 && P->slabEnd.size() > 1 && nComp <= 3;
+}
+
 static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
                        const double* flux, const double* pnf, double* corr, double* fv,
                        int memKind, void* stream) {
@@ -948,14 +1006,18 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
         if (int rc = ensureBuf(&P->s_vf, &P->s_vfCap, nV)) return rc;
         if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
         if (int rc = ensureBuf(&P->s_corr, &P->s_corrCap, nO)) return rc;
-        CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(P->s_flux, flux, nF * 8, cudaMemcpyHostToDevice, st));
+        // (the pipelined path copies slab by slab, see pipelinedHostCall)
+        const bool pipelined = usePipeline(P, nComp);
+        if (!pipelined) {
+            CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaMemcpyAsync(P->s_flux, flux, nF * 8, cudaMemcpyHostToDevice, st));
+        }
         c.vf = P->s_vf;
         c.flux = P->s_flux;
         c.corr = P->s_corr;
         if (pnf && nB) {
             if (int rc = ensureBuf(&P->s_pnf, &P->s_pnfCap, nB)) return rc;
-            CUDA_TRY(cudaMemcpyAsync(P->s_pnf, pnf, nB * 8, cudaMemcpyHostToDevice, st));
+            if (!pipelined) CUDA_TRY(cudaMemcpyAsync(P->s_pnf, pnf, nB * 8, cudaMemcpyHostToDevice, st));
             c.pnf = P->s_pnf;
         }
         if (fv) {
@@ -1006,6 +1068,79 @@ static int finishCall(wenoext_plan* P, double* corr, double* fv, int memKind) {
     return 0;
 }
 
+// Host-buffer call on a serial plan, pipelined over slabs of cells: the H2D copy of
+// what slab k+1 reads, the kernel of slab k and the D2H copy of the faces slab k-1
+// finalised run concurrently on three streams (copy engines in both directions).
+static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* flux, const double* pnf,
+                             double* corr, double* fv) {
+    wenoext_call& c = P->call;
+    const int S = (int)P->slabEnd.size();
+    const int nComp = c.nComp;
+    if (!P->sIn) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&P->sIn, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&P->sOut, cudaStreamNonBlocking));
+    }
+    while ((int)P->evSlab.size() < 2 * S + 2) {
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        P->evSlab.push_back(e);
+    }
+    // the staging buffers may still be in use by the caller's stream
+    cudaEvent_t evStart = P->evSlab[2 * S], evEnd = P->evSlab[2 * S + 1];
+    CUDA_TRY(cudaEventRecord(evStart, c.st));
+    CUDA_TRY(cudaStreamWaitEvent(P->sIn, evStart, 0));
+    CUDA_TRY(cudaStreamWaitEvent(P->sOut, evStart, 0));
+    double* dvf = const_cast<double*>(c.vf);
+    double* dflux = const_cast<double*>(c.flux);
+    if (pnf && P->nBnd)
+        CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.pnf), pnf, (size_t)P->nBnd * nComp * 8,
+                                 cudaMemcpyHostToDevice, P->sIn));
+    int haveVf = 0, haveFlux = 0, sent = 0, cell0 = 0;
+    for (int k = 0; k < S; ++k) {
+        const int nv = P->needVf[k], nf = k == S - 1 ? P->nFaces : std::max(haveFlux, (int)P->needFlux[k]);
+        if (nv > haveVf)
+            CUDA_TRY(cudaMemcpyAsync(dvf + (size_t)haveVf * nComp, vf + (size_t)haveVf * nComp,
+                                     (size_t)(nv - haveVf) * nComp * 8, cudaMemcpyHostToDevice, P->sIn));
+        if (nf > haveFlux)
+            CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
+                                     cudaMemcpyHostToDevice, P->sIn));
+        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sIn));
+        CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * k], 0));
+        if (nv > haveVf) {
+            launchPackValues(c.vf + (size_t)haveVf * nComp, nv - haveVf, nComp, c.c0, c.CB, c.VS,
+                             P->vals + (size_t)haveVf * c.VS, c.st);
+            P->lastLaunches++;
+        }
+        haveVf = std::max(haveVf, nv);
+        haveFlux = nf;
+        if (int rc = launchCells(P, nullptr, P->slabEnd[k] - cell0, cell0)) return rc;
+        cell0 = P->slabEnd[k];
+        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], c.st));
+        const int done = k == S - 1 ? sent : P->doneFaces[k];  // the rest follows the patch kernel
+        if (done > sent) {
+            CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
+            CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                                     (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+            if (fv)
+                CUDA_TRY(cudaMemcpyAsync(fv + (size_t)sent * nComp, c.fv + (size_t)sent * nComp,
+                                         (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost,
+                                         P->sOut));
+            sent = done;
+        }
+    }
+    if (int rc = phase2(P)) return rc;  // cyclic patches
+    CUDA_TRY(cudaEventRecord(evEnd, c.st));
+    CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
+    CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                             (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    if (fv && P->nInt > sent)
+        CUDA_TRY(cudaMemcpyAsync(fv + (size_t)sent * nComp, c.fv + (size_t)sent * nComp,
+                                 (size_t)(P->nInt - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    CUDA_TRY(cudaStreamSynchronize(P->sOut));
+    CUDA_TRY(cudaStreamSynchronize(c.st));
+    return 0;
+}
+
 extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int nComp,
                                    const double* vf, const double* faceFlux,
                                    const double* patchNbrField, double* corr, double* faceValue,
@@ -1017,6 +1152,10 @@ extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int
     if (int rc = prepareCall(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, faceValue,
                              memKind, stream))
         return rc;
+    if (memKind == WENOEXT_MEM_HOST && usePipeline(P, nComp)) {
+        setBatch(P, 0);
+        return pipelinedHostCall(P, vf, faceFlux, patchNbrField, corr, faceValue);
+    }
     for (int c0 = 0; c0 < nComp; c0 += 3) {
         setBatch(P, c0);
         if (int rc = phase0(P)) return rc;

@@ -81,6 +81,12 @@ struct wenoext_plan {
     double *s_vf = nullptr, *s_flux = nullptr, *s_pnf = nullptr, *s_corr = nullptr,
            *s_fv = nullptr;
     size_t s_vfCap = 0, s_fluxCap = 0, s_pnfCap = 0, s_corrCap = 0, s_fvCap = 0;
+    // pipelined host-buffer path (serial plans): slab k = cells [slabEnd[k-1], slabEnd[k])
+    // needs vf[0, needVf[k]) and flux[0, needFlux[k]); afterwards the internal faces
+    // [0, doneFaces[k]) are final
+    std::vector<int32_t> slabEnd, needVf, needFlux, doneFaces;
+    cudaStream_t sIn = nullptr, sOut = nullptr;
+    std::vector<cudaEvent_t> evSlab;  // [2 * slabs]: inputs arrived, slab computed
     // WENODict factors
     double p = 4.0, dm = 1000.0, eps = 1e-40;
     int bugCompat = 1;
