@@ -125,6 +125,7 @@ struct CellKernelArgs {
     const RecInfo* recInfo;    // [nCells]
     const int32_t* cellList;   // nullable: work item -> cell
     int32_t workBase;          // first work item of this launch (slabs of one call)
+    int32_t* tileCounter;      // zeroed before the launch: next tile of 32 work items
     int32_t nWork;
     int32_t K;
     int32_t nComp;             // stride of corr / faceValue / thetaPatch

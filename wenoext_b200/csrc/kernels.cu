@@ -180,32 +180,39 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
 
-    // static work split: tiles of TILE consecutive cells, round-robin over CTAs
+    // Dynamic work split: a warp takes tiles of TILE consecutive work items from a global
+    // counter (one tile ahead, so the atomic's latency is hidden). A CTA that starts late
+    // (e.g. while a NCCL kernel holds its SM) simply takes fewer tiles.
+    constexpr int PPT = TILE / CELLS;  // passes per tile
     const int nTiles = (a.nWork + TILE - 1) / TILE;
-    int nItems = 0;
-    if (nTiles > (int)blockIdx.x) {
-        const int nMy = (nTiles - (int)blockIdx.x - 1) / (int)gridDim.x + 1;
-        const int lastTile = blockIdx.x + (nMy - 1) * gridDim.x;
-        nItems = nMy * TILE - (lastTile == nTiles - 1 ? nTiles * TILE - a.nWork : 0);
-    }
-    auto itemToCell = [&](int n) {
-        const int w = a.workBase + ((int)blockIdx.x + (n / TILE) * (int)gridDim.x) * TILE + (n % TILE);
-        return a.cellList ? __ldg(a.cellList + w) : w;
+    auto grabTile = [&]() {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(a.tileCounter, 1);
+        return __shfl_sync(0xffffffffu, t, 0);
     };
-    const int nPasses = (nItems + CELLS - 1) / CELLS;           // of the CTA
-    const int myPasses = nPasses > warp ? (nPasses - warp - 1) / NW + 1 : 0;  // of this warp
-    if (myPasses == 0) return;
+    int curTile = grabTile();
+    if (curTile >= nTiles) return;
+    int nextTile = grabTile();
+    int tp = 0;  // pass of the current tile being consumed
+    // work item of cell c of the pass k passes after the one being consumed (k <= 3 < PPT);
+    // -1 beyond the end of the work
+    auto workItem = [&](int k, int c) {
+        const int t = tp + k;
+        const int tile = t < PPT ? curTile : nextTile;
+        const int w = tile * TILE + (t & (PPT - 1)) * CELLS + c;
+        return (tile < nTiles && w < a.nWork) ? a.workBase + w : -1;
+    };
+    auto workToCell = [&](int w) { return a.cellList ? __ldg(a.cellList + w) : w; };
 
     // ---- issue side (lanes 0..CELLS-1; lane c serves cell c of a pass) ----
     const uint64_t pol = evictFirstPolicy();
     const uint64_t polV = evictLastPolicy();
     const bool issuer = lane < CELLS;
-    // RecInfo of cell `lane` of this warp's i-th pass; w < 0: no such cell
-    auto fetchInfo = [&](int i) {
+    // RecInfo of cell `lane` of the pass k passes ahead; w < 0: no such cell
+    auto fetchInfo = [&](int k) {
         int4 v = make_int4(0, 0, 0, -1);
-        const int item = (warp + i * NW) * CELLS + lane;
-        if (issuer && i < myPasses && item < nItems)
-            v = __ldg(reinterpret_cast<const int4*>(a.recInfo + itemToCell(item)));
+        const int w = issuer ? workItem(k, lane) : -1;
+        if (w >= 0) v = __ldg(reinterpret_cast<const int4*>(a.recInfo + workToCell(w)));
         return v;
     };
     auto recPtr = [&](const int4& ri) {
@@ -266,6 +273,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         cPass = 1;
         cursorEnter(infoNext);
     }
+    // (cells beyond the end of the work have info.w < 0: their copies degenerate to plain
+    // arrivals, so the pipeline can run past the last pass without anything in flight)
 
     // ---- consumer side: CELLS cells per pass, one lane per (cell, stencil) ----
     const int cslot = lane / SS;
@@ -275,14 +284,13 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     int rs = 0;           // ring slot of the next step to consume
     uint32_t rpar = 0;    // its mbarrier phase parity
 
-    for (int i = 0; i < myPasses; ++i) {
-        const int pass = warp + i * NW;
-        const int item = pass * CELLS + cslot;
-        const bool valid = item < nItems;
+    for (int i = 0;; ++i) {
+        const int item = workItem(0, cslot);
+        const bool valid = item >= 0;
         const int hb = i & 1;
         const uint32_t rec = headBuf + (uint32_t)(hb * CELLS + cslot) * a.headSlotBytes;
         const uint32_t tail = tailBuf + (uint32_t)cslot * a.tailSlotBytes;
-        const int cell = valid ? itemToCell(item) : 0;
+        const int cell = valid ? workToCell(item) : 0;
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV);
 
@@ -307,7 +315,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             if (atomicCAS(a.dbg, 0, 1) == 0) {
                 a.dbg[1] = item; a.dbg[2] = hb; a.dbg[3] = i; a.dbg[4] = cell;
                 a.dbg[5] = nSt; a.dbg[6] = nFc; a.dbg[7] = Nmax; a.dbg[8] = (int)oIdx;
-                a.dbg[10] = blockIdx.x; a.dbg[11] = threadIdx.x; a.dbg[12] = nItems;
+                a.dbg[10] = blockIdx.x; a.dbg[11] = threadIdx.x; a.dbg[12] = curTile;
             }
             nSt = nFc = Nmax = 0;
         }
@@ -458,12 +466,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             }
             __syncwarp();
             // refill the slot just consumed with the step R ahead in this warp's stream
-            if (cPass < myPasses) {
-                issueChunk(rs);
-                if (cCh == CH) {
-                    ++cPass;
-                    cursorEnter(cPass - i == 1 ? infoNext : infoNN);
-                }
+            issueChunk(rs);
+            if (cCh == CH) {
+                ++cPass;
+                cursorEnter(cPass - i == 1 ? infoNext : infoNN);
             }
             if (++rs == R) {
                 rs = 0;
@@ -637,9 +643,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             }
         }
         __syncwarp();
+        if (++tp == PPT) {
+            tp = 0;
+            curTile = nextTile;
+            if (curTile >= nTiles) break;
+            nextTile = grabTile();
+        }
         infoCur = infoNext;
         infoNext = infoNN;
-        infoNN = fetchInfo(i + 3);
+        infoNN = fetchInfo(2);
     }
 }
 }  // namespace

@@ -535,7 +535,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
 extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (!P) return 0;
     cudaSetDevice(P->device);
-    void* ptrs[] = {P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
+    void* ptrs[] = {P->tileCounter, P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
                     P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
     for (void* p : ptrs)
@@ -728,6 +728,9 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
     a.records = P->records;
     a.recInfo = P->recInfo;
     a.cellList = list;
+    if (!P->tileCounter) CUDA_TRY(cudaMalloc((void**)&P->tileCounter, sizeof(int32_t)));
+    CUDA_TRY(cudaMemsetAsync(P->tileCounter, 0, sizeof(int32_t), c.st));
+    a.tileCounter = P->tileCounter;
     a.workBase = workBase;
     a.nWork = nWork;
     a.K = P->K;

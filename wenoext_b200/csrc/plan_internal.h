@@ -51,6 +51,7 @@ struct wenoext_plan {
     wenoext::RecInfo* recInfo = nullptr;
     int32_t maxN = 0;
     int32_t* dbg = nullptr;  // WENOEXT_KDEBUG builds only
+    int32_t* tileCounter = nullptr;  // work counter of the cell kernel, zeroed before every launch
     int64_t recordBytesTotal = 0, maxRecordBytes = 0, maxHeadBytes = 0, maxTailBytes = 0;
     int32_t maxSt = 0, maxFc = 0;
     int32_t* cellListInterior = nullptr;
