@@ -182,11 +182,11 @@ def run_reference(a):
         "unit": "faces/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a, 1), "cells": case.nCells,
-                   "faces": case.nInternalFaces},
+        "config": {"workload": workload_name(a, a.gpus), "sample_cells": case.nCells,
+                   "sample_faces": case.nInternalFaces},
         "cpu_baseline": {"value": val, "unit": "faces/s", "cores": T, "kind": "port",
                          "cpu": cpu_model(),
-                         "sample": f"full {a.n}^3 block per step, {what}, "
+                         "sample": f"one full {a.n}^3 block (the per-GPU share of the workload) per step, {what}, "
                                    f"de-duplicated matrices ({case.desc.nUniqueMatrices} unique)"},
         "e2e": {"value": val, "unit": "faces/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
