@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--order", type=int, default=2)
     ap.add_argument("--ncomp", type=int, default=3)
     ap.add_argument("--bounded", type=int, default=1)
+    ap.add_argument("--tets", type=int, default=0, choices=[0, 6],
+                    help="6: split every hex into 6 tets (irregular stencils, BASELINE config 4 variant)")
+    ap.add_argument("--best-conditioned", action="store_true", help="WENODict bestConditioned true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -54,8 +57,19 @@ def parse():
 def workload_name(a, N):
     px, py, pz = NPROC[N]
     g = (a.n * px, a.n * py, a.n * pz)
-    return (f"hex box {g[0]}x{g[1]}x{g[2]} ({a.n}^3 per GPU), WENOUpwindFit {a.order} {a.bounded}, "
+    mesh = "hex box" if not a.tets else "tet-split box (6 tets per hex" + \
+        (", bestConditioned" if a.best_conditioned else "") + ")"
+    return (f"{mesh} {g[0]}x{g[1]}x{g[2]} ({a.n}^3 per GPU), WENOUpwindFit {a.order} {a.bounded}, "
             f"{'vector U' if a.ncomp == 3 else str(a.ncomp) + ' component(s)'}, fp64")
+
+
+def case_kwargs(a):
+    kw = {}
+    if a.tets:
+        kw["tetSplit"] = a.tets
+    if a.best_conditioned:
+        kw["bestConditioned"] = True
+    return kw
 
 
 def make_fields(case, ncomp, rank=0):
@@ -165,7 +179,7 @@ def run_reference(a):
     import wenoext_b200 as wx
     from tests.oracle_binding import correction_threaded
     t0 = time.time()
-    case = wx.BoxCase((a.n,) * 3, a.order)
+    case = wx.BoxCase((a.n,) * 3, a.order, **case_kwargs(a))
     log(f"[reference] setup {time.time() - t0:.1f}s, {case.nCells} cells")
     vf, phi = make_fields(case, a.ncomp)
     orc, what = oracle_for_cpu()
@@ -217,7 +231,8 @@ def run_ours(a):
         dist.init_process_group("nccl", device_id=dev)
     px, py, pz = NPROC[N]
     t0 = time.time()
-    case = wx.BoxCase((a.n * px, a.n * py, a.n * pz), a.order, nProc=(px, py, pz), myProc=rank)
+    case = wx.BoxCase((a.n * px, a.n * py, a.n * pz), a.order, nProc=(px, py, pz), myProc=rank,
+                      **case_kwargs(a))
     if N > 1:
         wx.exchange_halo_lists_distributed(case)
     t_setup = time.time() - t0
