@@ -1,0 +1,75 @@
+"""One process per GPU over NCCL (the production multi-GPU path): needs >= 2 GPUs,
+skipped otherwise. Each rank reconstructs its block; every rank checks its result
+against the in-process multi-rank emulation of the oracle."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+NPROC = {2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+N = (24, 16, 16)
+
+
+def _worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+
+    import wenoext_b200 as wx
+    from tests import helpers as H
+    from tests.oracle_binding import Oracle, correction_multirank
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        cases = [wx.BoxCase(N, 2, nProc=NPROC[world], myProc=r) for r in range(world)]
+        wx.exchange_halo_lists(cases)  # every process builds all ranks: the oracle needs them
+        mine = cases[rank]
+        plan = wx.Plan(mine.desc, device=rank)
+        uid = [wx.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        plan.attach_nccl(uid[0], rank, world)
+        vfs = [H.vector_field(c.C, seed=4) for c in cases]
+        fls = [H.face_flux(c.Sf, U=(1.0, -1.0, 0.5), zero_frac=0.03) for c in cases]
+        errs = []
+        for scheme, bounded in ((0, 0), (0, 1), (1, 1)):
+            ref = correction_multirank(Oracle("c"), cases, scheme, bounded, vfs, fls)[rank]
+            for _ in range(2):  # twice: buffers and events are reused across calls
+                got = plan.correction(scheme, bounded, vfs[rank], fls[rank])
+            errs.append(H.normwise_err(np.asarray(got).reshape(ref.shape), ref))
+            dvf = torch.from_numpy(vfs[rank]).cuda()
+            dfl = torch.from_numpy(fls[rank]).cuda()
+            out = torch.empty((mine.nFaces, 3), dtype=torch.float64, device="cuda")
+            plan.correction(scheme, bounded, dvf, dfl, out=out)
+            errs.append(H.normwise_err(out.cpu().numpy().reshape(ref.shape), ref))
+        q.put((rank, errs))
+        dist.barrier()
+        plan.destroy()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_ranks_match_oracle(world):
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for r in range(world):
+        assert max(got[r]) <= 1e-12, (r, got[r])
