@@ -32,7 +32,7 @@ namespace wenoext {
 
 namespace {
 
-constexpr int TILE = 32;          // consecutive cells handed to one CTA at a time
+constexpr int TILE = 16;          // consecutive work items a warp takes at a time
 constexpr int MAX_THREADS = 256;  // 8 warps per CTA (up to 255 registers per thread)
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) {
@@ -185,16 +185,20 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     // (e.g. while a NCCL kernel holds its SM) simply takes fewer tiles.
     constexpr int PPT = TILE / CELLS;  // passes per tile
     const int nTiles = (a.nWork + TILE - 1) / TILE;
+    // The atomic's result stays untouched in lane 0 (pendingTile) for half a tile before
+    // it is broadcast, so nobody ever waits for its latency.
     auto grabTile = [&]() {
         int t = 0;
         if (lane == 0) t = atomicAdd(a.tileCounter, 1);
-        return __shfl_sync(0xffffffffu, t, 0);
+        return t;
     };
-    int curTile = grabTile();
+    int curTile = __shfl_sync(0xffffffffu, grabTile(), 0);
     if (curTile >= nTiles) return;
-    int nextTile = grabTile();
+    int pendingTile = grabTile();  // becomes nextTile at pass PPT / 2 of the current tile
+    int nextTile = nTiles;
+    static_assert(PPT >= 4, "the next tile is broadcast at pass PPT / 2, at least 2 passes before its first use");
     int tp = 0;  // pass of the current tile being consumed
-    // work item of cell c of the pass k passes after the one being consumed (k <= 3 < PPT);
+    // work item of cell c of the pass k passes after the one being consumed (k <= 2);
     // -1 beyond the end of the work
     auto workItem = [&](int k, int c) {
         const int t = tp + k;
@@ -244,16 +248,22 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     int4 cInfo;
     const unsigned char* cSrc = nullptr;
     int cCh = 0, cPass = 0;
+    uint32_t cFullBytes = 0;  // size of a chunk with D columns and D index rows
+    int cNFull = 0;           // chunks [0, cNFull) are full
     auto cursorEnter = [&](const int4& ri) {
         cInfo = ri;
         cSrc = recPtr(ri) + ((uint32_t)ri.z & 0xffffu) + ((uint32_t)ri.z >> 16);
         cCh = 0;
+        const int nSt = ri.w & 0xffff, Nmax = ri.w >> 16;
+        cFullBytes = (uint32_t)((D * nSt * K * 8 + D * nSt * 4 + 15) & ~15);
+        cNFull = ri.w >= 0 ? max(0, Nmax / D - GATHER_AHEAD) : 0;
     };
     auto issueChunk = [&](int slot) {
         if (issuer) {
             const uint32_t bar = barRing + slot * 8;
-            uint32_t bytes = 0;
-            if (cInfo.w >= 0) bytes = (uint32_t)chunkBytes(K, cInfo.w & 0xffff, cInfo.w >> 16, cCh);
+            uint32_t bytes = cFullBytes;
+            if (cCh >= cNFull)
+                bytes = cInfo.w >= 0 ? (uint32_t)chunkBytes(K, cInfo.w & 0xffff, cInfo.w >> 16, cCh) : 0u;
             if (bytes) {
                 mbarArriveExpectTx(bar, bytes);
                 tmaLoad1D(ringBuf + (uint32_t)(slot * CELLS + lane) * a.chunkSlotBytes, cSrc, bytes, bar, pol);
@@ -503,9 +513,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 for (int c = 0; c < CB; ++c) IS[c] = fma(acc[k][c], u[c], IS[c]);
             }
             // gamma: dm for the first surviving stencil          (WENOCoeff.C:198-205)
+            // intPow (WENOCoeff.H:149-157): repeated multiplication in the reference's order
+            double pw[CB], bs[CB];
 #pragma unroll
-            for (int c = 0; c < CB; ++c)
-                g[c] = act ? (s == 0 ? a.dm : 1.0) / intPowD(a.eps + IS[c], a.pExp) : 0.0;
+            for (int c = 0; c < CB; ++c) {
+                bs[c] = a.eps + IS[c];
+                pw[c] = 1.0;
+            }
+            for (uint32_t e = 0; e < a.pExp; ++e)
+#pragma unroll
+                for (int c = 0; c < CB; ++c) pw[c] *= bs[c];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) g[c] = act ? (s == 0 ? a.dm : 1.0) / pw[c] : 0.0;
         }
         // weighted sum over the stencils of the cell: butterfly over its SS lanes
         // (WENOCoeff.C:207-220; the division by gammaSum is applied per face below)
@@ -647,7 +666,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             tp = 0;
             curTile = nextTile;
             if (curTile >= nTiles) break;
-            nextTile = grabTile();
+            pendingTile = grabTile();
+        } else if (tp == PPT / 2) {
+            nextTile = __shfl_sync(0xffffffffu, pendingTile, 0);
         }
         infoCur = infoNext;
         infoNext = infoNN;
