@@ -169,6 +169,24 @@ int wenoext_interpolate(wenoext_plan* plan, int scheme, int bounded, int nComp,
                         const double* vf, const double* faceFlux, const double* patchNbrField,
                         double* corr, double* faceValue, int memKind, void* stream);
 
+/* fvc::div(faceFlux, vf) with the WENO scheme, formed entirely on the device: what
+ * gaussConvectionScheme<Type>::fvcDiv builds from this scheme (OpenFOAM side of
+ * WENOUpwindFit.H:223-242), fvc::surfaceIntegrate(faceFlux * interpolate(vf)):
+ *   face value = weights()*vf_P + (1-weights())*vf_N + correction()   (internal and coupled faces)
+ *              = bndValue                                            (other patches)
+ *   div[cell]  = (sum over the cell's faces, ascending face index as OpenFOAM's face loops:
+ *                 +flux*value where the cell owns the face, -flux*value where it is the
+ *                 neighbour) / cellVolumes[cell]
+ * Only [nCells][nComp] returns to the host instead of [nFaces][nComp].
+ *   bndValue    [nFaces-nInternalFaces][nComp]  vf.boundaryField() on the patch faces (read on
+ *               non-coupled patches only)
+ *   cellVolumes [nCells]                        mesh.V()
+ *   div         [nCells][nComp] out
+ * Coupled patches need the value across the face: patchNbrField, or desc.patchNbrCell. */
+int wenoext_div(wenoext_plan* plan, int scheme, int bounded, int nComp, const double* vf,
+                const double* faceFlux, const double* patchNbrField, const double* bndValue,
+                const double* cellVolumes, double* div, int memKind, void* stream);
+
 /* In-process ranks (several plans in one process, on one or more GPUs; used by
  * the single-GPU tests of the multi-rank path): plans[r] must have myProc == r.
  * Exchanges become device-to-device copies; drive them with the split-phase

@@ -226,6 +226,29 @@ class Plan:
                                            kind, st))
         return out
 
+    def div(self, scheme, bounded, vf, faceFlux, bndValue, cellVolumes, patchNbrField=None, out=None,
+            stream=None):
+        """wenoext_div: fvc::div(faceFlux, vf) with the WENO scheme, formed on the device."""
+        nComp = 1 if vf.ndim == 1 else int(vf.shape[1])
+        pv, kind, kv = self._ptr(vf)
+        pf, _, kf = self._ptr(faceFlux)
+        pn, _, kn = self._ptr(patchNbrField)
+        pb, _, kb = self._ptr(bndValue)
+        pvol, _, kvol = self._ptr(cellVolumes)
+        if out is None:
+            if isinstance(vf, np.ndarray):
+                out = np.empty(vf.shape, dtype=np.float64)
+            else:
+                import torch
+                out = torch.empty(vf.shape, dtype=torch.float64, device=vf.device)
+        po, _, ko = self._ptr(out)
+        st = 0
+        if kind == MEM_DEVICE:
+            import torch
+            st = (stream if stream is not None else torch.cuda.current_stream(vf.device)).cuda_stream
+        check(lib().wenoext_div(self._h, scheme, int(bounded), nComp, pv, pf, pn, pb, pvol, po, kind, st))
+        return out
+
     def destroy(self):
         if self._h:
             lib().wenoext_plan_destroy(self._h)

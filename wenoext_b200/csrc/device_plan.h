@@ -173,6 +173,27 @@ struct PatchKernelArgs {
     int32_t scheme, bounded;
 };
 
+// fvc::surfaceIntegrate(flux * face value) per cell (wenoext_div)
+struct DivKernelArgs {
+    int32_t nCells, nInternalFaces, nComp;
+    const int32_t* cellFaceStart;  // [nCells+1]
+    const int32_t* cellFaces;      // faces of a cell in ascending face index
+    const int32_t* owner;          // [nFaces]
+    const int32_t* bfPatchType;    // [nBnd] FACE_* or -1 (not coupled)
+    const int32_t* bfNbrCell;      // [nBnd] flat value index across a coupled face, or null
+    const double* vf;              // [nCells][nComp]
+    const double* vals;            // packed values incl. halo (stride VS) of the LAST component batch
+    int32_t VS, c0, CB;
+    const double* flux;            // [nFaces]
+    const double* faceValue;       // [nInternalFaces][nComp] upwind value + correction
+    const double* corr;            // [nFaces][nComp]
+    const double* patchNbrField;   // nullable [nBnd][nComp]
+    const double* bndValue;        // [nBnd][nComp]
+    const double* cellVolumes;     // [nCells]
+    double* div;                   // [nCells][nComp]
+};
+void launchDivKernel(const DivKernelArgs& a, cudaStream_t st);
+
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st);
 size_t cellKernelSmemBytes(const CellKernelArgs& a);

@@ -740,6 +740,42 @@ __global__ void patch_kernel(const PatchKernelArgs a) {
     if (changed) a.corr[(size_t)f * a.nComp + cc] = v;
 }
 
+// fvc::surfaceIntegrate(faceFlux * interpolate(vf)) (wenoext_div): one thread per
+// (cell, component), faces in ascending index so the sum has OpenFOAM's order.
+__global__ void surface_integrate_kernel(const DivKernelArgs a) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)a.nCells * a.nComp) return;
+    const int cell = (int)(i / a.nComp), c = (int)(i - (int64_t)cell * a.nComp);
+    const double own = a.vf[i];
+    double sum = 0.0;
+    for (int k = a.cellFaceStart[cell]; k < a.cellFaceStart[cell + 1]; ++k) {
+        const int f = a.cellFaces[k];
+        const double fl = a.flux[f];
+        if (f < a.nInternalFaces) {
+            const double v = fl * a.faceValue[(size_t)f * a.nComp + c];
+            sum += a.owner[f] == cell ? v : -v;
+        } else {
+            const int bf = f - a.nInternalFaces;
+            double val;
+            if (a.bfPatchType[bf] >= 0) {
+                // coupled patch: weights() = pos(flux), value across from the caller or the halo
+                double nb = own;
+                if (a.patchNbrField)
+                    nb = a.patchNbrField[(size_t)bf * a.nComp + c];
+                else if (a.bfNbrCell && a.bfNbrCell[bf] >= 0 && a.bfNbrCell[bf] < a.nCells)
+                    nb = a.vf[(size_t)a.bfNbrCell[bf] * a.nComp + c];  // cyclic: a local cell
+                else if (a.bfNbrCell && a.bfNbrCell[bf] >= 0 && c >= a.c0 && c < a.c0 + a.CB)
+                    nb = a.vals[(size_t)a.bfNbrCell[bf] * a.VS + (c - a.c0)];  // halo value
+                val = (fl > 0 ? own : nb) + a.corr[(size_t)f * a.nComp + c];
+            } else {
+                val = a.bndValue[(size_t)bf * a.nComp + c];
+            }
+            sum += fl * val;
+        }
+    }
+    a.div[i] = sum / a.cellVolumes[cell];
+}
+
 }  // namespace
 
 size_t cellKernelSmemBytes(const CellKernelArgs& a) {
@@ -796,6 +832,12 @@ int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t sme
         case 19: return launchK<19, chunkCols(19)>(a, CB, gridBlocks, smemBytes, st);
         default: return 1;
     }
+}
+
+void launchDivKernel(const DivKernelArgs& a, cudaStream_t st) {
+    const int64_t n = (int64_t)a.nCells * a.nComp;
+    if (n <= 0) return;
+    surface_integrate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
 }
 
 void launchPatchKernel(const PatchKernelArgs& a, cudaStream_t st) {

@@ -403,6 +403,13 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     if (d->nInternalFaces) rc = rc ? rc : up(&dNei, d->neighbour, (size_t)d->nInternalFaces);
     rc = rc ? rc : up(&dCFS, d->cellFaceStart, (size_t)nC + 1);
     rc = rc ? rc : up(&dCF, d->cellFaces, (size_t)d->cellFaceStart[nC]);
+    {   // wenoext_div sums a cell's faces in ascending face index (OpenFOAM's loop order)
+        std::vector<int32_t> sorted(d->cellFaces, d->cellFaces + d->cellFaceStart[nC]);
+        for (int c = 0; c < nC; ++c)
+            std::sort(sorted.begin() + d->cellFaceStart[c], sorted.begin() + d->cellFaceStart[c + 1]);
+        rc = rc ? rc : upload(&P->cellFaceStartD, d->cellFaceStart, (size_t)nC + 1);
+        rc = rc ? rc : upload(&P->cellFacesSortedD, sorted.data(), sorted.size());
+    }
     rc = rc ? rc : upload(&P->bfPatchType, bfType.data(), bfType.size());
     rc = rc ? rc : upload(&P->bfPartner, bfPartner.data(), bfPartner.size());
     if (d->patchNbrCell && P->nBnd > 0)
@@ -535,7 +542,8 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
 extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (!P) return 0;
     cudaSetDevice(P->device);
-    void* ptrs[] = {P->tileCounter, P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
+    void* ptrs[] = {P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
+                    P->tileCounter, P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
                     P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
     for (void* p : ptrs)
@@ -1174,6 +1182,86 @@ extern "C" int wenoext_correction(wenoext_plan* P, int scheme, int bounded, int 
                                   void* stream) {
     return wenoext_interpolate(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, nullptr,
                                memKind, stream);
+}
+
+extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
+                           const double* faceFlux, const double* patchNbrField, const double* bndValue,
+                           const double* cellVolumes, double* div, int memKind, void* stream) {
+    if (!P || !vf || !faceFlux || !cellVolumes || !div || (P->nBnd > 0 && !bndValue)) {
+        setError("div: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (P->nProcs > 1 && !P->comm) {
+        setError("div: in-process peers are not supported (attach NCCL)");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (P->hasProcessor && !patchNbrField && (!P->hasNbrCell || nComp > 3)) {
+        setError("div: processor patches need patchNbrField (or desc.patchNbrCell with nComp <= 3)");
+        return WENOEXT_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(P->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t nV = (size_t)P->nCells * nComp, nF = (size_t)P->nFaces, nB = (size_t)P->nBnd * nComp;
+    if (int rc = ensureBuf(&P->d_corr, &P->d_corrCap, nF * nComp)) return rc;
+    if (int rc = ensureBuf(&P->d_fv, &P->d_fvCap, (size_t)P->nInt * nComp)) return rc;
+    const double *dvf = vf, *dflux = faceFlux, *dpnf = patchNbrField, *dbnd = bndValue, *dvol = cellVolumes;
+    double* ddiv = div;
+    if (memKind == WENOEXT_MEM_HOST) {
+        // stage everything once; the reconstruction below then runs on device pointers
+        if (int rc = ensureBuf(&P->s_vf, &P->s_vfCap, nV)) return rc;
+        if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
+        if (int rc = ensureBuf(&P->d_vol, &P->d_volCap, (size_t)P->nCells)) return rc;
+        if (int rc = ensureBuf(&P->d_div, &P->d_divCap, nV)) return rc;
+        CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(P->s_flux, faceFlux, nF * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(P->d_vol, cellVolumes, (size_t)P->nCells * 8, cudaMemcpyHostToDevice, st));
+        dvf = P->s_vf;
+        dflux = P->s_flux;
+        dvol = P->d_vol;
+        ddiv = P->d_div;
+        if (nB) {
+            if (int rc = ensureBuf(&P->d_bnd, &P->d_bndCap, nB)) return rc;
+            CUDA_TRY(cudaMemcpyAsync(P->d_bnd, bndValue, nB * 8, cudaMemcpyHostToDevice, st));
+            dbnd = P->d_bnd;
+            if (patchNbrField) {
+                if (int rc = ensureBuf(&P->s_pnf, &P->s_pnfCap, nB)) return rc;
+                CUDA_TRY(cudaMemcpyAsync(P->s_pnf, patchNbrField, nB * 8, cudaMemcpyHostToDevice, st));
+                dpnf = P->s_pnf;
+            }
+        }
+    }
+    if (int rc = wenoext_interpolate(P, scheme, bounded, nComp, dvf, dflux, dpnf, P->d_corr, P->d_fv,
+                                     WENOEXT_MEM_DEVICE, stream))
+        return rc;
+    DivKernelArgs a{};
+    a.nCells = P->nCells;
+    a.nInternalFaces = P->nInt;
+    a.nComp = nComp;
+    a.cellFaceStart = P->cellFaceStartD;
+    a.cellFaces = P->cellFacesSortedD;
+    a.owner = P->owner;
+    a.bfPatchType = P->bfPatchType;
+    a.bfNbrCell = P->bfNbrCell;
+    a.vf = dvf;
+    a.vals = P->vals;
+    a.VS = P->call.VS;
+    a.c0 = P->call.c0;
+    a.CB = P->call.CB;
+    a.flux = dflux;
+    a.faceValue = P->d_fv;
+    a.corr = P->d_corr;
+    a.patchNbrField = dpnf;
+    a.bndValue = dbnd;
+    a.cellVolumes = dvol;
+    a.div = ddiv;
+    launchDivKernel(a, st);
+    P->lastLaunches++;
+    CUDA_TRY(cudaGetLastError());
+    if (memKind == WENOEXT_MEM_HOST) {
+        CUDA_TRY(cudaMemcpyAsync(div, ddiv, nV * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    return 0;
 }
 
 // In-process ranks (tests / single-process multi-GPU): plans[r]->myProc == r.

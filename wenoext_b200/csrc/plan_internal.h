@@ -78,6 +78,11 @@ struct wenoext_plan {
     double* thetaPatch = nullptr;
     double* sendPatch = nullptr;  // in-process peers: snapshot of the patch values to send
     size_t patchCap = 0;
+    // wenoext_div: faces of a cell in ascending face index, device scratch
+    int32_t* cellFaceStartD = nullptr;
+    int32_t* cellFacesSortedD = nullptr;
+    double *d_corr = nullptr, *d_fv = nullptr, *d_bnd = nullptr, *d_vol = nullptr, *d_div = nullptr;
+    size_t d_corrCap = 0, d_fvCap = 0, d_bndCap = 0, d_volCap = 0, d_divCap = 0;
     // staging for host-pointer calls
     double *s_vf = nullptr, *s_flux = nullptr, *s_pnf = nullptr, *s_corr = nullptr,
            *s_fv = nullptr;
