@@ -10,10 +10,11 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 NPROC = {2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
-N = (24, 16, 16)
+# small: plain host path; large with 2 slabs: the slab-pipelined host path of parallel plans
+MESHES = {"small": ((24, 16, 16), None), "large": ((64, 32, 32), "2")}
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, mesh):
     import torch
     import torch.distributed as dist
 
@@ -21,6 +22,9 @@ def _worker(rank, world, port, q):
     from tests import helpers as H
     from tests.oracle_binding import Oracle, correction_multirank
 
+    N, slabs = MESHES[mesh]
+    if slabs:
+        os.environ["WENOEXT_E2E_SLABS"] = slabs
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -53,8 +57,9 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("mesh", ["small", "large"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_nccl_ranks_match_oracle(world):
+def test_nccl_ranks_match_oracle(world, mesh):
     import torch
     import torch.multiprocessing as mp
     if torch.cuda.device_count() < world:
@@ -64,7 +69,7 @@ def test_nccl_ranks_match_oracle(world):
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, mesh)) for r in range(world)]
     for p in procs:
         p.start()
     got = dict(q.get(timeout=300) for _ in procs)

@@ -193,6 +193,8 @@ struct DivKernelArgs {
     double* div;                   // [nCells][nComp]
 };
 void launchDivKernel(const DivKernelArgs& a, cudaStream_t st);
+void launchGatherRows(const double* src, const int32_t* rows, int64_t n, int nComp, double* dst,
+                      cudaStream_t st);
 
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st);

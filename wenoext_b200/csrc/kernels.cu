@@ -740,6 +740,15 @@ __global__ void patch_kernel(const PatchKernelArgs a) {
     if (changed) a.corr[(size_t)f * a.nComp + cc] = v;
 }
 
+// dst[i][:] = src[rows[i]][:] (faces written late by boundary cells, sent to the host compactly)
+__global__ void gather_rows_kernel(const double* __restrict__ src, const int32_t* __restrict__ rows,
+                                   int64_t n, int nComp, double* __restrict__ dst) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * nComp) return;
+    const int64_t r = i / nComp;
+    dst[i] = src[(size_t)rows[r] * nComp + (i - r * nComp)];
+}
+
 // fvc::surfaceIntegrate(faceFlux * interpolate(vf)) (wenoext_div): one thread per
 // (cell, component), faces in ascending index so the sum has OpenFOAM's order.
 __global__ void surface_integrate_kernel(const DivKernelArgs a) {
@@ -832,6 +841,12 @@ int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t sme
         case 19: return launchK<19, chunkCols(19)>(a, CB, gridBlocks, smemBytes, st);
         default: return 1;
     }
+}
+
+void launchGatherRows(const double* src, const int32_t* rows, int64_t n, int nComp, double* dst,
+                      cudaStream_t st) {
+    if (n <= 0) return;
+    gather_rows_kernel<<<(unsigned)((n * nComp + 255) / 256), 256, 0, st>>>(src, rows, n, nComp, dst);
 }
 
 void launchDivKernel(const DivKernelArgs& a, cudaStream_t st) {

@@ -466,10 +466,10 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         }
     }
     // interior / boundary cell lists (overlap of the halo exchange)
+    std::vector<int32_t> li, lb;
     if (!rc) {
         std::vector<uint8_t> hasHalo(nC);
         cudaMemcpy(hasHalo.data(), dHasHalo, (size_t)nC, cudaMemcpyDeviceToHost);
-        std::vector<int32_t> li, lb;
         for (int c = 0; c < nC; ++c) (hasHalo[c] ? lb : li).push_back(c);
         P->nInterior = (int32_t)li.size();
         P->nBoundaryCells = (int32_t)lb.size();
@@ -512,6 +512,35 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
             }
         }
     }
+    // Parallel plans: slabs over the interior cell list; faces of boundary cells are fixed up.
+    if (!rc && P->nProcs > 1 && P->nBoundaryCells > 0) {
+        int S = 8;
+        if (const char* e = getenv("WENOEXT_E2E_SLABS")) S = std::max(1, atoi(e));
+        const int nI = P->nInterior;
+        if (nI < S * 8192) S = 1;
+        if (S > 1) {
+            std::vector<int32_t> ext((size_t)nC * 3);
+            cudaMemcpy(ext.data(), dCellExt, ext.size() * sizeof(int32_t), cudaMemcpyDeviceToHost);
+            const int per = ((nI + S - 1) / S + 31) / 32 * 32;
+            P->slabEnd.clear();
+            for (int k = 0; k < S; ++k) P->slabEnd.push_back(std::min(nI, (k + 1) * per));
+            while (P->slabEnd.size() > 1 && P->slabEnd[P->slabEnd.size() - 2] >= nI) P->slabEnd.pop_back();
+            S = (int)P->slabEnd.size();
+            P->doneFaces.assign(S, 0);
+            int lo = P->nInt, j = nI;
+            for (int k = S - 1; k >= 0; --k) {
+                for (; j > P->slabEnd[k]; --j) lo = std::min(lo, ext[(size_t)li[j - 1] * 3 + 1]);
+                P->doneFaces[k] = std::min(lo, P->nInt);
+            }
+            for (int c : lb)
+                for (int i = d->cellFaceStart[c]; i < d->cellFaceStart[c + 1]; ++i)
+                    if (d->cellFaces[i] < P->nInt) P->fixFacesH.push_back(d->cellFaces[i]);
+            std::sort(P->fixFacesH.begin(), P->fixFacesH.end());
+            P->fixFacesH.erase(std::unique(P->fixFacesH.begin(), P->fixFacesH.end()), P->fixFacesH.end());
+            if (!P->fixFacesH.empty())
+                rc = rc ? rc : upload(&P->fixFacesD, P->fixFacesH.data(), P->fixFacesH.size());
+        }
+    }
     for (void* t : temps) cudaFree(t);
     if (dHasHalo) cudaFree(dHasHalo);
     if (dCellExt) cudaFree(dCellExt);
@@ -542,7 +571,8 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
 extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (!P) return 0;
     cudaSetDevice(P->device);
-    void* ptrs[] = {P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
+    if (P->h_fix) cudaFreeHost(P->h_fix);
+    void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
                     P->tileCounter, P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
                     P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
@@ -852,7 +882,7 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
     return 0;
 }
 
-static int phase0(wenoext_plan* P) {
+static int phase0(wenoext_plan* P, bool launchInterior = true) {
     const wenoext_call& c = P->call;
     const bool parallel = P->nProcs > 1;
     launchPackValues(c.vf, P->nCells, c.nComp, c.c0, c.CB, c.VS, P->vals, c.st);
@@ -881,6 +911,7 @@ static int phase0(wenoext_plan* P) {
         CUDA_TRY(cudaEventRecord(P->evB, P->commStream));
     }
     // interior cells overlap the exchange (the reference waits first, WENOCoeff.C:295)
+    if (!launchInterior) return 0;
     return launchCells(P, P->cellListInterior, P->nInterior);
 }
 
@@ -980,8 +1011,9 @@ static int phase2(wenoext_plan* P) {
 // ---------------------------------------------------------------------------
 // public per-step entry points
 // ---------------------------------------------------------------------------
-static bool usePipeline(const wenoext_plan* P, int nComp) {
-    return P->nProcs == 1 && P->slabEnd.size() > 1 && nComp <= 3;
+static bool usePipeline(const wenoext_plan* P, int nComp, bool wantFaceValue) {
+    if (P->slabEnd.size() <= 1 || nComp > 3) return false;
+    return P->nProcs == 1 || (P->comm != nullptr && !wantFaceValue);
 }
 
 static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
@@ -1018,7 +1050,7 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
         if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
         if (int rc = ensureBuf(&P->s_corr, &P->s_corrCap, nO)) return rc;
         // (the pipelined path copies slab by slab, see pipelinedHostCall)
-        const bool pipelined = usePipeline(P, nComp);
+        const bool pipelined = usePipeline(P, nComp, fv != nullptr);
         if (!pipelined) {
             CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
             CUDA_TRY(cudaMemcpyAsync(P->s_flux, flux, nF * 8, cudaMemcpyHostToDevice, st));
@@ -1152,6 +1184,81 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
     return 0;
 }
 
+// The same for a parallel plan (one process per GPU, NCCL): inputs are copied up front
+// (the halo pack needs all cell values), the interior cell list is processed in slabs with
+// the D2H copy of the faces they finalise overlapped, then boundary cells and coupled
+// patches as usual. Internal faces written late by boundary cells travel in a compact
+// buffer and are scattered into the result on the host.
+static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const double* flux,
+                                     const double* pnf, double* corr) {
+    wenoext_call& c = P->call;
+    const int S = (int)P->slabEnd.size();
+    const int nComp = c.nComp;
+    if (!P->sIn) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&P->sIn, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&P->sOut, cudaStreamNonBlocking));
+    }
+    while ((int)P->evSlab.size() < 2 * S + 2) {
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        P->evSlab.push_back(e);
+    }
+    const size_t nFix = P->fixFacesH.size();
+    if (nFix) {
+        if (int rc = ensureBuf(&P->d_fix, &P->d_fixCap, nFix * nComp)) return rc;
+        if (P->h_fixCap < nFix * nComp) {
+            if (P->h_fix) cudaFreeHost(P->h_fix);
+            P->h_fix = nullptr;
+            CUDA_TRY(cudaMallocHost((void**)&P->h_fix, nFix * nComp * 8));
+            P->h_fixCap = nFix * nComp;
+        }
+    }
+    cudaEvent_t evStart = P->evSlab[2 * S], evEnd = P->evSlab[2 * S + 1];
+    CUDA_TRY(cudaEventRecord(evStart, c.st));
+    CUDA_TRY(cudaStreamWaitEvent(P->sIn, evStart, 0));
+    CUDA_TRY(cudaStreamWaitEvent(P->sOut, evStart, 0));
+    CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.vf), vf, (size_t)P->nCells * nComp * 8,
+                             cudaMemcpyHostToDevice, P->sIn));
+    CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.flux), flux, (size_t)P->nFaces * 8,
+                             cudaMemcpyHostToDevice, P->sIn));
+    if (pnf && P->nBnd)
+        CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.pnf), pnf, (size_t)P->nBnd * nComp * 8,
+                                 cudaMemcpyHostToDevice, P->sIn));
+    CUDA_TRY(cudaEventRecord(P->evSlab[0], P->sIn));
+    CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[0], 0));
+    if (int rc = phase0(P, false)) return rc;  // pack, exchange #1 on the communication stream
+    int sent = 0, item0 = 0;
+    for (int k = 0; k < S; ++k) {
+        if (int rc = launchCells(P, P->cellListInterior, P->slabEnd[k] - item0, item0)) return rc;
+        item0 = P->slabEnd[k];
+        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], c.st));
+        const int done = P->doneFaces[k];
+        if (k < S - 1 && done > sent) {
+            CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
+            CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                                     (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+            sent = done;
+        }
+    }
+    if (int rc = phase1(P)) return rc;  // boundary cells, exchange #2
+    if (int rc = phase2(P)) return rc;  // coupled patches
+    launchGatherRows(c.corr, P->fixFacesD, (int64_t)nFix, nComp, P->d_fix, c.st);
+    if (nFix) P->lastLaunches++;
+    CUDA_TRY(cudaEventRecord(evEnd, c.st));
+    CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
+    if (nFix)
+        CUDA_TRY(cudaMemcpyAsync(P->h_fix, P->d_fix, nFix * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                             (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    CUDA_TRY(cudaStreamSynchronize(P->sOut));
+    CUDA_TRY(cudaStreamSynchronize(c.st));
+    for (size_t i = 0; i < nFix; ++i) {
+        const size_t f = (size_t)P->fixFacesH[i];
+        for (int k = 0; k < nComp; ++k) corr[f * nComp + k] = P->h_fix[i * nComp + k];
+    }
+    return 0;
+}
+
 extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int nComp,
                                    const double* vf, const double* faceFlux,
                                    const double* patchNbrField, double* corr, double* faceValue,
@@ -1163,9 +1270,10 @@ extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int
     if (int rc = prepareCall(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, faceValue,
                              memKind, stream))
         return rc;
-    if (memKind == WENOEXT_MEM_HOST && usePipeline(P, nComp)) {
+    if (memKind == WENOEXT_MEM_HOST && usePipeline(P, nComp, faceValue != nullptr)) {
         setBatch(P, 0);
-        return pipelinedHostCall(P, vf, faceFlux, patchNbrField, corr, faceValue);
+        if (P->nProcs == 1) return pipelinedHostCall(P, vf, faceFlux, patchNbrField, corr, faceValue);
+        return pipelinedHostCallParallel(P, vf, faceFlux, patchNbrField, corr);
     }
     for (int c0 = 0; c0 < nComp; c0 += 3) {
         setBatch(P, c0);

@@ -91,6 +91,14 @@ struct wenoext_plan {
     // needs vf[0, needVf[k]) and flux[0, needFlux[k]); afterwards the internal faces
     // [0, doneFaces[k]) are final
     std::vector<int32_t> slabEnd, needVf, needFlux, doneFaces;
+    // parallel plans: slabs run over the interior cell list; internal faces of boundary
+    // cells are finalised last and travel compactly (fixFaces), scattered on the host
+    std::vector<int32_t> fixFacesH;
+    int32_t* fixFacesD = nullptr;
+    double* d_fix = nullptr;
+    size_t d_fixCap = 0;
+    double* h_fix = nullptr;  // pinned
+    size_t h_fixCap = 0;
     cudaStream_t sIn = nullptr, sOut = nullptr;
     std::vector<cudaEvent_t> evSlab;  // [2 * slabs]: inputs arrived, slab computed
     // WENODict factors
