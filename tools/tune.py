@@ -1,5 +1,5 @@
 """Launch-geometry sweep of the fused cell kernel on one case (developer tool).
-Usage: python tools/tune.py N ORDER NCOMP "cells,warps,chunkslots,smemKB[,metaPasses]" ...   (0 = auto)"""
+Usage: python tools/tune.py N ORDER NCOMP "cellsPerWarp,warps,ringSteps,smemKB" ...   (0 = auto)"""
 import os
 import sys
 import time
@@ -20,10 +20,10 @@ vf = torch.from_numpy(vf_h).cuda()
 phi = torch.from_numpy(phi_h).cuda()
 ref = None
 for cfg in sys.argv[4:]:
-    vals = [int(x) for x in cfg.split(",")] + [0]
-    G, groups, slots, smem, mp = vals[:5]
+    vals = [int(x) for x in cfg.split(",")] + [0, 0, 0]
+    G, groups, slots, smem = vals[:4]
     for k, v in (("WENOEXT_CELLS", G), ("WENOEXT_WARPS", groups), ("WENOEXT_SLOTS", slots),
-                 ("WENOEXT_SMEM_KB", smem), ("WENOEXT_META_PASSES", mp)):
+                 ("WENOEXT_SMEM_KB", smem)):
         if v > 0:
             os.environ[k] = str(v)
         else:
@@ -42,6 +42,6 @@ for cfg in sys.argv[4:]:
     if ref is None:
         ref = o
     err = np.abs(o - ref).max()
-    print(f"cfg cells={G} warps={groups} slots={slots} smemKB={smem} metaPasses={mp}: {ms:.4f} ms  {gbs:.0f} GB/s  "
+    print(f"cfg cellsPerWarp={G} warps={groups} ringSteps={slots} smemKB={smem}: {ms:.4f} ms  {gbs:.0f} GB/s  "
           f"frac {gbs / 6547.8:.3f}  maxdiff_vs_first {err:.2e}", flush=True)
     plan.destroy()

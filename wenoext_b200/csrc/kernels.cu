@@ -9,21 +9,23 @@
 // Every internal face is written by exactly one cell (its upwind cell), so the
 // kernel is cell-centric and nothing but the per-face result goes back to HBM.
 //
-// Structure: persistent CTAs (one per SM). One producer warp streams whole cell
-// records (device_plan.h) into a shared-memory ring with 1-D TMA bulk copies
-// (cp.async.bulk ... mbarrier::complete_tx, SASS UBLKCP): the small meta part
-// and the matrix part complete on separate mbarriers, so the gather of stencil
-// values overlaps the arrival of the matrices. Consumer warps take CELLS cells per
-// pass and give one lane to every (cell, stencil): the lane gathers its own
-// stencil's value differences straight into registers (software-pipelined global
-// loads), streams its matrix column by column from shared memory (128-bit loads,
-// stencil index fastest, so the lanes of a cell read consecutive words) and keeps
-// all K x CB coefficients in registers. Smoothness indicators and weights stay in
-// registers; the weighted sum over the stencils of a cell is a warp-shuffle
-// butterfly over the cell's lanes; afterwards every lane evaluates one face.
-// No scratch shared memory and no block-level barriers. The kernel is HBM-bound:
+// Structure: persistent CTAs (one per SM), 8 warps, each running its own pipeline.
+// A warp takes tiles of 16 consecutive cells from a global counter and processes 4
+// cells per pass, one lane per (cell, stencil). Lanes 0..3 issue 1-D TMA bulk copies
+// (cp.async.bulk ... mbarrier::complete_tx, SASS UBLKCP) of the parts of "their"
+// cell's record (device_plan.h) into the warp's private shared memory: head (this
+// pass and the next), tail, and a ring of matrix chunk steps that is refilled by the
+// warp itself as it consumes it. A lane gathers its own stencil's value differences
+// straight into registers (global loads issued two chunk steps ahead), streams its
+// matrix column by column from shared memory (128-bit loads, stencil index fastest, so
+// the lanes of a cell read consecutive words) and keeps all K x CB coefficients in
+// registers. Smoothness indicators and weights stay in registers; the weighted sum
+// over the stencils of a cell is a warp-shuffle butterfly over the cell's lanes;
+// afterwards every lane evaluates one face. No scratch shared memory, no block-level
+// barriers after start-up, no cross-warp synchronisation. The kernel is HBM-bound:
 // tensor cores are deliberately unused (independent 9x21 GEMVs, no operand reuse).
 #include <cuda_runtime.h>
+#include <cstdio>
 #include <stdint.h>
 
 #include "device_plan.h"
@@ -49,7 +51,8 @@ __device__ __forceinline__ void mbarArrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 #ifdef WENOEXT_KDEBUG
-__device__ int32_t* g_dbg = nullptr;
+// developer build: bounded wait, so that a protocol error shows up as wrong results and a
+// report instead of a hang
 __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
     for (long long it = 0; it < 4000000; ++it) {
         uint32_t ok;
@@ -62,9 +65,8 @@ __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
             : "memory");
         if (ok) return;
     }
-    if (g_dbg && atomicCAS(g_dbg, 0, 4) == 0) {
-        g_dbg[1] = (int)bar; g_dbg[2] = (int)parity; g_dbg[10] = blockIdx.x; g_dbg[11] = threadIdx.x;
-    }
+    printf("[kdebug] mbarrier wait timed out: bar %u parity %u block %d thread %d\n", bar, parity,
+           (int)blockIdx.x, (int)threadIdx.x);
 }
 #else
 __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
@@ -117,16 +119,6 @@ __device__ __forceinline__ int4 lds128i(uint32_t a) {
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                  : "r"(a));
     return v;
-}
-
-// WENOCoeff.H:149-157: repeated multiplication, exponent truncated to unsigned.
-// The first 8 factors are predicated (no loop) - p = 4 is the default.
-__device__ __forceinline__ double intPowD(double base, uint32_t e) {
-    double t = 1.0;
-#pragma unroll
-    for (uint32_t i = 0; i < 8; ++i) t = i < e ? t * base : t;
-    for (uint32_t i = 8; i < e; ++i) t *= base;
-    return t;
 }
 
 __device__ __forceinline__ uint64_t evictLastPolicy() {
