@@ -251,3 +251,28 @@ def test_pipelined_host_path_equals_device_path(sides, scheme, bounded, nComp):
     ref = Oracle("c").correction(case, scheme, bounded, vf, flux)
     assert H.normwise_err(host, ref) <= TOL
     plan.destroy()
+
+
+@pytest.mark.parametrize("env", [
+    {"WENOEXT_CELLS": "1"},                       # one cell per warp (meshes with > 8 stencils per cell)
+    {"WENOEXT_SLOTS": "1"},                       # ring of one chunk step: no prefetch at all
+    {"WENOEXT_SLOTS": "2", "WENOEXT_WARPS": "3"},
+    {"WENOEXT_SMEM_KB": "48"},                    # few warps fit
+    {"WENOEXT_GRID": "3"},                        # 3 CTAs take all tiles
+    {"WENOEXT_CELLS": "1", "WENOEXT_SLOTS": "2", "WENOEXT_WARPS": "5"},
+])
+@pytest.mark.parametrize("name", ["hex8", "tets_bc", "hex_o3", "cavity"])
+def test_launch_geometries(monkeypatch, env, name):
+    """The kernel's pipeline protocol must not depend on the launch geometry the plan
+    picks: force other cell-per-warp mappings, ring depths, warp and CTA counts."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    case = case_of(name)
+    plan = wx.Plan(case.desc)  # reads the overrides at creation
+    vf = _fields(case, 3, seed=2)
+    flux = H.rotating_flux(case)
+    for scheme, bounded in SCHEMES:
+        got = plan.correction(scheme, bounded, vf, flux)
+        ref = Oracle("c").correction(case, scheme, bounded, vf, flux)
+        assert H.normwise_err(got, ref) <= TOL, (env, name, scheme, bounded)
+    plan.destroy()
