@@ -30,6 +30,16 @@ def _mk(name):
         return wx.BoxCase((3, 3, 3), 2, tetSplit=6, bestConditioned=True, useClassCache=False)
     if name == "hex_o3":  # WENOUpwindFit 3 x: K=19, N=46
         return wx.BoxCase((7, 7, 7), 3, useClassCache=False)
+    if name == "hex_o1":  # order 1: K=3
+        return wx.BoxCase((8, 8, 8), 1, useClassCache=False)
+    if name == "hex_o4":  # order 4 in 3-D: K=34, one component per matrix read
+        return wx.BoxCase((10, 10, 10), 4, useClassCache=False)
+    if name == "quad_o1":  # 2-D order 1: K=2
+        return wx.BoxCase((12, 12, 1), 1, sides=(0, 0, 0, 0, 3, 3), useClassCache=False)
+    if name == "quad_o4":  # 2-D order 4: K=14
+        return wx.BoxCase((14, 14, 1), 4, sides=(0, 0, 0, 0, 3, 3), useClassCache=False)
+    if name == "quad_o5":  # 2-D order 5: K=20
+        return wx.BoxCase((14, 14, 1), 5, sides=(0, 0, 0, 0, 3, 3), useClassCache=False)
     if name == "cyclic":  # 3DMesh-cyclic-like: x cyclic
         return wx.BoxCase((8, 6, 6), 2, sides=(2, 2, 0, 0, 0, 0), useClassCache=False)
     if name == "cyclic2d":  # 2DMesh-cyclic-like
@@ -60,7 +70,7 @@ def _plan(case):
 
 
 @pytest.mark.parametrize("name", ["hex8", "cavity", "tets", "tets_bc", "hex_o3", "cyclic",
-                                  "cyclic2d"])
+                                  "cyclic2d", "hex_o1", "hex_o4", "quad_o1", "quad_o4", "quad_o5"])
 @pytest.mark.parametrize("scheme,bounded", SCHEMES)
 @pytest.mark.parametrize("nComp", [1, 3])
 def test_parity_host_buffers(name, scheme, bounded, nComp):

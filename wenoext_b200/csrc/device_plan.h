@@ -200,6 +200,7 @@ int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t sme
                      cudaStream_t st);
 size_t cellKernelSmemBytes(const CellKernelArgs& a);
 bool cellKernelSupportsK(int K);
+int cellKernelMaxCB(int K);  // components batched per matrix read
 int cellKernelMaxWarps();  // warps per CTA the kernel is compiled for
 void launchPatchKernel(const PatchKernelArgs& a, cudaStream_t st);
 void launchPackValues(const double* vf, int nCells, int nComp, int c0, int CB, int VS,

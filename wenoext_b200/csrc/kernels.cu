@@ -783,7 +783,13 @@ size_t cellKernelSmemBytes(const CellKernelArgs& a) {
     return (size_t)a.nWarps * ((size_t)a.warpBytes + (size_t)(3 + a.ringSteps) * 8);
 }
 
-bool cellKernelSupportsK(int K) { return K == 5 || K == 9 || K == 14 || K == 19; }
+// nDvt of the supported polynomial spaces (WENOBase.C:1133-1140): 3-D orders 1-4 are 3, 9,
+// 19, 34; 2-D orders 1-5 are 2, 5, 9, 14, 20
+bool cellKernelSupportsK(int K) {
+    return K == 2 || K == 3 || K == 5 || K == 9 || K == 14 || K == 19 || K == 20 || K == 34;
+}
+// components batched per matrix read: the K x CB coefficients live in registers
+int cellKernelMaxCB(int K) { return K <= 20 ? 3 : 1; }
 int cellKernelMaxWarps() { return MAX_THREADS / 32; }
 
 namespace {
@@ -803,34 +809,43 @@ int launchT(const CellKernelArgs& a, int gridBlocks, size_t smemBytes, cudaStrea
 }
 template <int K, int D>
 int launchK(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes, cudaStream_t st) {
-    if (a.cellsPerWarp == 4) {
-        switch (CB) {
-            case 1: return launchT<K, 1, 4, D>(a, gridBlocks, smemBytes, st);
-            case 2: return launchT<K, 2, 4, D>(a, gridBlocks, smemBytes, st);
-            default: return launchT<K, 3, 4, D>(a, gridBlocks, smemBytes, st);
+    if constexpr (K > 20) {  // cellKernelMaxCB(K) == 1
+        if (CB != 1) return 1;
+        if (a.cellsPerWarp == 4) return launchT<K, 1, 4, D>(a, gridBlocks, smemBytes, st);
+        return launchT<K, 1, 1, D>(a, gridBlocks, smemBytes, st);
+    } else {
+        if (a.cellsPerWarp == 4) {
+            switch (CB) {
+                case 1: return launchT<K, 1, 4, D>(a, gridBlocks, smemBytes, st);
+                case 2: return launchT<K, 2, 4, D>(a, gridBlocks, smemBytes, st);
+                default: return launchT<K, 3, 4, D>(a, gridBlocks, smemBytes, st);
+            }
         }
-    }
-    switch (CB) {
-        case 1: return launchT<K, 1, 1, D>(a, gridBlocks, smemBytes, st);
-        case 2: return launchT<K, 2, 1, D>(a, gridBlocks, smemBytes, st);
-        default: return launchT<K, 3, 1, D>(a, gridBlocks, smemBytes, st);
+        switch (CB) {
+            case 1: return launchT<K, 1, 1, D>(a, gridBlocks, smemBytes, st);
+            case 2: return launchT<K, 2, 1, D>(a, gridBlocks, smemBytes, st);
+            default: return launchT<K, 3, 1, D>(a, gridBlocks, smemBytes, st);
+        }
     }
 }
 }  // namespace
 
 // K (the polynomial space) is a template parameter because every lane keeps the
-// K x CB coefficients of its stencil in registers: 3-D order 2 and 2-D order 3: 9,
-// 3-D order 3: 19, 2-D order 2: 5, 2-D order 4: 14.
+// K x CB coefficients of its stencil in registers (cellKernelSupportsK lists the spaces).
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st) {
     if (a.nWarps * 32 > MAX_THREADS || a.nWarps < 1 || a.ringSteps < 1 || a.ringSteps > a.nChunks ||
         a.ringSteps > 29 || (a.cellsPerWarp != 4 && a.cellsPerWarp != 1))
         return 1;
     switch (a.K) {
+        case 2: return launchK<2, chunkCols(2)>(a, CB, gridBlocks, smemBytes, st);
+        case 3: return launchK<3, chunkCols(3)>(a, CB, gridBlocks, smemBytes, st);
         case 5: return launchK<5, chunkCols(5)>(a, CB, gridBlocks, smemBytes, st);
         case 9: return launchK<9, chunkCols(9)>(a, CB, gridBlocks, smemBytes, st);
         case 14: return launchK<14, chunkCols(14)>(a, CB, gridBlocks, smemBytes, st);
         case 19: return launchK<19, chunkCols(19)>(a, CB, gridBlocks, smemBytes, st);
+        case 20: return launchK<20, chunkCols(20)>(a, CB, gridBlocks, smemBytes, st);
+        case 34: return launchK<34, chunkCols(34)>(a, CB, gridBlocks, smemBytes, st);
         default: return 1;
     }
 }

@@ -295,7 +295,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
 
     // per-cell record sizes
     if (!cellKernelSupportsK(K)) {
-        setError("unsupported polynomial space (nDvt must be 5, 9, 14 or 19)");
+        setError("unsupported polynomial space (nDvt must be 2, 3, 5, 9, 14, 19, 20 or 34: orders 1-4 in 3-D, 1-5 in 2-D)");
         delete P;
         return WENOEXT_ERR_INVALID;
     }
@@ -1012,7 +1012,7 @@ static int phase2(wenoext_plan* P) {
 // public per-step entry points
 // ---------------------------------------------------------------------------
 static bool usePipeline(const wenoext_plan* P, int nComp, bool wantFaceValue) {
-    if (P->slabEnd.size() <= 1 || nComp > 3) return false;
+    if (P->slabEnd.size() <= 1 || nComp > cellKernelMaxCB(P->K)) return false;
     return P->nProcs == 1 || (P->comm != nullptr && !wantFaceValue);
 }
 
@@ -1098,7 +1098,7 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
 static void setBatch(wenoext_plan* P, int c0) {
     wenoext_call& c = P->call;
     c.c0 = c0;
-    c.CB = std::min(3, c.nComp - c0);
+    c.CB = std::min(cellKernelMaxCB(P->K), c.nComp - c0);
     c.VS = c.CB == 3 ? 4 : c.CB;
 }
 
@@ -1275,7 +1275,7 @@ extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int
         if (P->nProcs == 1) return pipelinedHostCall(P, vf, faceFlux, patchNbrField, corr, faceValue);
         return pipelinedHostCallParallel(P, vf, faceFlux, patchNbrField, corr);
     }
-    for (int c0 = 0; c0 < nComp; c0 += 3) {
+    for (int c0 = 0; c0 < nComp; c0 += cellKernelMaxCB(P->K)) {
         setBatch(P, c0);
         if (int rc = phase0(P)) return rc;
         if (int rc = phase1(P)) return rc;
@@ -1303,7 +1303,7 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
         setError("div: in-process peers are not supported (attach NCCL)");
         return WENOEXT_ERR_INVALID;
     }
-    if (P->hasProcessor && !patchNbrField && (!P->hasNbrCell || nComp > 3)) {
+    if (P->hasProcessor && !patchNbrField && (!P->hasNbrCell || nComp > cellKernelMaxCB(P->K))) {
         setError("div: processor patches need patchNbrField (or desc.patchNbrCell with nComp <= 3)");
         return WENOEXT_ERR_INVALID;
     }
@@ -1389,8 +1389,8 @@ extern "C" int wenoext_attach_local(wenoext_plan** plans, int nRanks) {
 extern "C" int wenoext_correction_begin(wenoext_plan* P, int scheme, int bounded, int nComp,
                                         const double* vf, const double* faceFlux,
                                         const double* patchNbrField, double* corr, void* stream) {
-    if (nComp > 3) {
-        setError("split-phase correction supports nComp <= 3");
+    if (nComp > cellKernelMaxCB(P->K)) {
+        setError("split-phase correction supports one component batch (nComp <= 3, 1 at order 4 in 3-D)");
         return WENOEXT_ERR_INVALID;
     }
     if (int rc = prepareCall(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, corr, nullptr,
