@@ -34,7 +34,6 @@ namespace wenoext {
 
 namespace {
 
-constexpr int TILE = 16;          // consecutive work items a warp takes at a time
 constexpr int MAX_THREADS = 256;  // 8 warps per CTA (up to 255 registers per thread)
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) {
@@ -150,7 +149,8 @@ template <int K, int CB, int CELLS, int D>
 __global__ void __launch_bounds__(MAX_THREADS, 1)
     weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
-    constexpr int SS = 32 / CELLS;  // stencil lanes per cell
+    constexpr int SS = 32 / CELLS;  // stencil lanes per cell (8, 6 with two idle lanes, or 32)
+    constexpr int TILE = CELLS == 1 ? 16 : 4 * CELLS;  // consecutive work items a warp takes at a time
     constexpr int KP = K / 2;       // coefficient pairs per column
     constexpr bool ODD = (K & 1) != 0;
     const int NW = a.nWarps;
@@ -279,15 +279,40 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     // arrivals, so the pipeline can run past the last pass without anything in flight)
 
     // ---- consumer side: CELLS cells per pass, one lane per (cell, stencil) ----
-    const int cslot = lane / SS;
+    const int cslot = lane / SS;  // (== CELLS for the idle lanes of the 6-lane mapping)
     const int s = lane - cslot * SS;
+    // lanes (s+1, s+2, s+3) mod SS of the own cell: all-reduce over a group of 6
+    const int rot1 = (cslot * SS + (s + 1) % SS) & 31, rot2 = (cslot * SS + (s + 2) % SS) & 31,
+              rot3 = (cslot * SS + (s + 3) % SS) & 31;
+    // sum / max / min over the SS lanes of a cell, result on every lane of the cell
+    auto groupSum = [&](double v) {
+        if constexpr ((SS & (SS - 1)) == 0) {
+#pragma unroll
+            for (int m = 1; m < SS; m <<= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+            return v;
+        } else {
+            static_assert(SS == 6 || (SS & (SS - 1)) == 0, "lane groups of 6, 8 or 32");
+            const double t = v + __shfl_sync(0xffffffffu, v, rot3);  // pairs (s, s+3)
+            return t + __shfl_sync(0xffffffffu, t, rot1) + __shfl_sync(0xffffffffu, t, rot2);
+        }
+    };
+    auto groupMax = [&](double v) {
+        if constexpr ((SS & (SS - 1)) == 0) {
+#pragma unroll
+            for (int m = 1; m < SS; m <<= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, m));
+            return v;
+        } else {
+            const double t = fmax(v, __shfl_sync(0xffffffffu, v, rot3));
+            return fmax(t, fmax(__shfl_sync(0xffffffffu, t, rot1), __shfl_sync(0xffffffffu, t, rot2)));
+        }
+    };
     const bool fit01 = a.scheme == 1;
     const bool fitBounded = a.scheme == 0 && a.bounded;
     int rs = 0;           // ring slot of the next step to consume
     uint32_t rpar = 0;    // its mbarrier phase parity
 
     for (int i = 0;; ++i) {
-        const int item = workItem(0, cslot);
+        const int item = cslot < CELLS ? workItem(0, cslot) : -1;
         const bool valid = item >= 0;
         const int hb = i & 1;
         const uint32_t rec = headBuf + (uint32_t)(hb * CELLS + cslot) * a.headSlotBytes;
@@ -525,15 +550,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
             for (int c = 0; c < CB; ++c) acc[k][c] *= g[c];
 #pragma unroll
-        for (int m = 1; m < SS; m <<= 1) {
+        for (int k = 0; k < K; ++k)
 #pragma unroll
-            for (int k = 0; k < K; ++k)
+            for (int c = 0; c < CB; ++c) acc[k][c] = groupSum(acc[k][c]);
 #pragma unroll
-                for (int c = 0; c < CB; ++c)
-                    acc[k][c] += __shfl_xor_sync(0xffffffffu, acc[k][c], m);
-#pragma unroll
-            for (int c = 0; c < CB; ++c) g[c] += __shfl_xor_sync(0xffffffffu, g[c], m);
-        }
+        for (int c = 0; c < CB; ++c) g[c] = groupSum(g[c]);
         // now acc = sum_s gamma_s c_s and g = gammaSum on every lane of the cell
 
         // phase 3: faces, one (or more) per lane
@@ -585,14 +606,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 }
             }
 #pragma unroll
-            for (int m = 1; m < SS; m <<= 1)
-#pragma unroll
-                for (int c = 0; c < CB; ++c) {
-                    const double omx = __shfl_xor_sync(0xffffffffu, mx[c], m);
-                    const double omn = __shfl_xor_sync(0xffffffffu, mn[c], m);
-                    mx[c] = omx > mx[c] ? omx : mx[c];
-                    mn[c] = omn < mn[c] ? omn : mn[c];
-                }
+            for (int c = 0; c < CB; ++c) {
+                mx[c] = groupMax(mx[c]);
+                mn[c] = -groupMax(-mn[c]);
+            }
 #pragma unroll
             for (int c = 0; c < CB; ++c) {
                 const double psi = cen[c];
@@ -811,9 +828,17 @@ template <int K, int D>
 int launchK(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes, cudaStream_t st) {
     if constexpr (K > 20) {  // cellKernelMaxCB(K) == 1
         if (CB != 1) return 1;
+        if (a.cellsPerWarp == 5) return launchT<K, 1, 5, D>(a, gridBlocks, smemBytes, st);
         if (a.cellsPerWarp == 4) return launchT<K, 1, 4, D>(a, gridBlocks, smemBytes, st);
         return launchT<K, 1, 1, D>(a, gridBlocks, smemBytes, st);
     } else {
+        if (a.cellsPerWarp == 5) {
+            switch (CB) {
+                case 1: return launchT<K, 1, 5, D>(a, gridBlocks, smemBytes, st);
+                case 2: return launchT<K, 2, 5, D>(a, gridBlocks, smemBytes, st);
+                default: return launchT<K, 3, 5, D>(a, gridBlocks, smemBytes, st);
+            }
+        }
         if (a.cellsPerWarp == 4) {
             switch (CB) {
                 case 1: return launchT<K, 1, 4, D>(a, gridBlocks, smemBytes, st);
@@ -835,7 +860,7 @@ int launchK(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes, c
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st) {
     if (a.nWarps * 32 > MAX_THREADS || a.nWarps < 1 || a.ringSteps < 1 || a.ringSteps > a.nChunks ||
-        a.ringSteps > 29 || (a.cellsPerWarp != 4 && a.cellsPerWarp != 1))
+        a.ringSteps > 27 || (a.cellsPerWarp != 5 && a.cellsPerWarp != 4 && a.cellsPerWarp != 1))
         return 1;
     switch (a.K) {
         case 2: return launchK<2, chunkCols(2)>(a, CB, gridBlocks, smemBytes, st);

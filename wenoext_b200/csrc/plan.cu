@@ -810,9 +810,10 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
     a.chunkSlotBytes = bankStride(chunkBytes(P->K, P->maxSt, (GATHER_AHEAD + 1) * D, 0));
     const size_t budget =
         (size_t)std::min(P->smemLimit, P->cfgSmemKB > 0 ? P->cfgSmemKB * 1024 : P->smemLimit) - 64;
-    int cpw = P->maxSt <= 8 ? 4 : 1;
+    // lanes per cell: 6 (five cells per warp, tets and 2-D meshes), 8 (hexes) or 32
+    int cpw = P->maxSt <= 6 ? 5 : (P->maxSt <= 8 ? 4 : 1);
     if (P->cfgCells > 0) cpw = P->cfgCells;
-    if ((cpw != 4 && cpw != 1) || P->maxSt > 32 / cpw) {
+    if ((cpw != 5 && cpw != 4 && cpw != 1) || P->maxSt > 32 / cpw) {
         setError("unsupported stencil shape (more than 32 stencils per cell)");
         return WENOEXT_ERR_INVALID;
     }
