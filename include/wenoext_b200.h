@@ -247,6 +247,40 @@ int wenoext_setup_set_send_halo(wenoext_setup* s, int32_t proc, const int32_t* i
 int wenoext_setup_geometry(wenoext_setup* s, const double** cellCentres,
                            const double** faceAreaVec);
 
+/* ---------------------------------------------------------------------------
+ * The reference's on-disk cache constant/WENOBase<order>/ (SURVEY.md 8f-2): the
+ * eleven files of WENOBase::writeList / readList (WENOBase.C:1196-1312; matrixDB.C:
+ * 276-415; BlazeIO.C:30-134; List3D.H:295-351) in OpenFOAM's BINARY stream framing.
+ * A cache written by the reference (one per processor directory) can drive the GPU
+ * path without re-running the preprocessing, and a cache written here can be read
+ * by the reference's readList.
+ * ------------------------------------------------------------------------- */
+/* labelBytes 4 or 8 (WM_LABEL_SIZE/8); simdDoubles: Blaze's row padding of the host
+ * that will read the files (8 AVX-512, 4 AVX/AVX2, 2 SSE2, 1 none; 0 = 8). */
+int wenoext_cache_write(wenoext_setup* s, const char* dir, int labelBytes, int simdDoubles);
+
+/* The mesh addressing the cache does not hold; the reference takes it from the
+ * fvMesh (mesh.owner(), mesh.neighbour(), mesh.cells(), mesh.boundary()). */
+typedef struct wenoext_mesh_desc {
+    int32_t nCells, nFaces, nInternalFaces;
+    const int32_t* owner;         /* [nFaces] */
+    const int32_t* neighbour;     /* [nInternalFaces] */
+    const int32_t* cellFaceStart; /* mesh.cells() CSR [nCells+1]; NULL: derived from owner/
+                                     neighbour as primitiveMesh::calcCells does (owned faces
+                                     in ascending order, then neighboured faces) */
+    const int32_t* cellFaces;
+    int32_t nPatches;
+    const wenoext_patch* patches;
+    const int32_t* patchNbrCell; /* optional, see wenoext_plan_desc; may be NULL */
+} wenoext_mesh_desc;
+
+/* labelBytes 0 = detect. The result is a wenoext_setup like wenoext_setup_box's
+ * (wenoext_setup_desc gives the plan descriptor); its geometry arrays are empty. */
+int wenoext_cache_read(const char* dir, const wenoext_mesh_desc* mesh, int32_t myProc,
+                       int labelBytes, wenoext_setup** out);
+/* Mesh addressing of a setup as a wenoext_mesh_desc (pointers valid until destroy). */
+int wenoext_setup_mesh(wenoext_setup* s, wenoext_mesh_desc* mesh);
+
 #ifdef __cplusplus
 }
 #endif

@@ -140,3 +140,16 @@ extern "C" int weno_oracle_blaze_getWENOPol(void* h, int nComp, double p_, doubl
     return weno_oracle_blaze_getWENOPol_range(h, nComp, p_, dm_, epsilon_, vf, haloData,
                                               coeffsWeighted, 0, o->d->nCells);
 }
+
+/* Memory image of a row-major blaze::DynamicMatrix<double> holding A (rows x cols): what
+ * BlazeIO.C:126-129 writes to the cache (M.data(), M.spacing()*M.rows() doubles). Returns
+ * the spacing; `out` receives the image if it has room for `cap` doubles. Pins the padded
+ * blob format of tests/test_wenobase_cache.py against the real container. */
+extern "C" int weno_oracle_blaze_image(int rows, int cols, const double* A, double* out, int cap) {
+    blaze::DynamicMatrix<double> M(rows, cols);
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j) M(i, j) = A[i * cols + j];
+    const int spacing = (int)M.spacing();
+    if (out && cap >= spacing * rows) memcpy(out, M.data(), sizeof(double) * spacing * rows);
+    return spacing;
+}

@@ -28,7 +28,7 @@ from ._capi import (MEM_DEVICE, MEM_HOST, PATCH_CYCLIC, PATCH_EMPTY, PATCH_GENER
                     PATCH_PROCESSOR, SCHEME_UPWINDFIT, SCHEME_UPWINDFIT01, WenoextError, check,
                     lib)
 
-__all__ = ["BoxCase", "WENOBase", "Plan", "WENOUpwindFit", "WENOUpwindFit01", "WenoextError",
+__all__ = ["BoxCase", "CachedCase", "WENOBase", "Plan", "WENOUpwindFit", "WENOUpwindFit01", "WenoextError",
            "exchange_halo_lists", "exchange_halo_lists_distributed", "attach_local",
            "correction_local", "nccl_unique_id", "SCHEME_UPWINDFIT", "SCHEME_UPWINDFIT01",
            "PATCH_GENERIC", "PATCH_PROCESSOR", "PATCH_CYCLIC", "PATCH_EMPTY"]
@@ -99,6 +99,17 @@ class BoxCase:
         self.C = _np_view(cc, (d.nCells, 3), np.float64)       # mesh.C()
         self.Sf = _np_view(sf, (d.nFaces, 3), np.float64)      # mesh.Sf()
 
+    def write_cache(self, directory, labelBytes=4, simdDoubles=8):
+        """WENOBase::writeList (WENOBase.C:1265-1312): the eleven files of
+        constant/WENOBase<order>/ in the reference's binary format."""
+        check(lib().wenoext_cache_write(self._h, str(directory).encode(), labelBytes, simdDoubles))
+
+    def mesh_desc(self):
+        """Mesh addressing (owner, neighbour, cells, patches) as a wenoext_mesh_desc."""
+        m = _capi.MeshDesc()
+        check(lib().wenoext_setup_mesh(self._h, C.byref(m)))
+        return m
+
     def halo_request(self, proc):
         ids, n = _capi.i32p(), C.c_int64()
         check(lib().wenoext_setup_halo_request(self._h, proc, C.byref(ids), C.byref(n)))
@@ -117,6 +128,51 @@ class BoxCase:
                 self._h = None
         except Exception:
             pass
+
+
+class CachedCase(BoxCase):
+    """A case whose WENOBase data come from an on-disk cache constant/WENOBase<order>/
+    (WENOBase::readList, WENOBase.C:1196-1262) instead of the preprocessing. The mesh
+    addressing is not in the cache; pass it as a wenoext_mesh_desc (`mesh`, e.g.
+    another case's mesh_desc()) or as arrays."""
+
+    def __init__(self, directory, mesh=None, owner=None, neighbour=None, patches=(), myProc=0,
+                 labelBytes=0, patchNbrCell=None, geometry=None, WENODict=None):
+        keep = []
+        if mesh is None:
+            owner = np.ascontiguousarray(owner, dtype=np.int32)
+            neighbour = np.ascontiguousarray(neighbour, dtype=np.int32)
+            parr = (_capi.Patch * max(1, len(patches)))(*[_capi.Patch(*p) for p in patches])
+            mesh = _capi.MeshDesc()
+            mesh.nCells = int(max(owner.max(), neighbour.max() if neighbour.size else -1)) + 1
+            mesh.nFaces, mesh.nInternalFaces = owner.size, neighbour.size
+            mesh.owner = owner.ctypes.data_as(_capi.i32p)
+            mesh.neighbour = neighbour.ctypes.data_as(_capi.i32p)
+            mesh.nPatches, mesh.patches = len(patches), parr
+            if patchNbrCell is not None:
+                pn = np.ascontiguousarray(patchNbrCell, dtype=np.int32)
+                mesh.patchNbrCell = pn.ctypes.data_as(_capi.i32p)
+                keep.append(pn)
+            keep += [owner, neighbour, parr]
+        h = C.c_void_p()
+        check(lib().wenoext_cache_read(str(directory).encode(), C.byref(mesh), myProc, labelBytes,
+                                       C.byref(h)))
+        self._h = h
+        self.myProc = myProc
+        self.WENODict = {"p": 4.0, "dm": 1000.0, "epsilon": 1e-40}
+        if WENODict:
+            self.WENODict.update(WENODict)
+        self._refresh()
+        self.order = self.desc.polOrder
+        self.nProcs = self.desc.nProcs
+        if geometry is not None:  # (C, Sf) for synthetic fields; not read by the hot path
+            self.C, self.Sf = geometry
+
+    def _refresh(self):
+        super()._refresh()
+        if self.C.size and not self.C.any():
+            self.C = None
+            self.Sf = None
 
 
 def exchange_halo_lists(cases):

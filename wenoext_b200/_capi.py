@@ -62,6 +62,12 @@ class SetupParams(C.Structure):
                 ("useClassCache", C.c_int32)]
 
 
+class MeshDesc(C.Structure):
+    _fields_ = [("nCells", C.c_int32), ("nFaces", C.c_int32), ("nInternalFaces", C.c_int32),
+                ("owner", i32p), ("neighbour", i32p), ("cellFaceStart", i32p), ("cellFaces", i32p),
+                ("nPatches", C.c_int32), ("patches", C.POINTER(Patch)), ("patchNbrCell", i32p)]
+
+
 # every symbol include/wenoext_b200.h declares: name -> (restype, argtypes)
 vp = C.c_void_p
 SYMBOLS = {
@@ -90,6 +96,9 @@ SYMBOLS = {
     "wenoext_setup_halo_request": (C.c_int, [vp, C.c_int32, C.POINTER(i32p), C.POINTER(C.c_int64)]),
     "wenoext_setup_set_send_halo": (C.c_int, [vp, C.c_int32, i32p, C.c_int64]),
     "wenoext_setup_geometry": (C.c_int, [vp, C.POINTER(f64p), C.POINTER(f64p)]),
+    "wenoext_cache_write": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
+    "wenoext_cache_read": (C.c_int, [C.c_char_p, C.POINTER(MeshDesc), C.c_int32, C.c_int, C.POINTER(vp)]),
+    "wenoext_setup_mesh": (C.c_int, [vp, C.POINTER(MeshDesc)]),
 }
 
 _lib = None

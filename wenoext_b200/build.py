@@ -21,6 +21,7 @@ CPP_SOURCES = [
     "setup/svd.cpp",
     "setup/weno_setup.cpp",
     "setup/box_fast.cpp",
+    "setup/wenobase_cache.cpp",
 ]
 
 
@@ -39,25 +40,44 @@ def _all_deps():
     return deps
 
 
+def _headers():
+    hs = [os.path.join(ROOT, "include", "wenoext_b200.h")]
+    for base, _, files in os.walk(CSRC):
+        hs += [os.path.join(base, f) for f in files if f.endswith(".h")]
+    return hs
+
+
 def build_product(force=False, verbose=False):
-    if not force and not _newer(LIB, _all_deps()):
-        return LIB
+    """Per-object incremental: an object is rebuilt when its source or a header it can see
+    changed (setup/*.cpp see only setup/*.h and the public header)."""
     objdir = os.path.join(ROOT, "build", "obj")
     os.makedirs(objdir, exist_ok=True)
-    objs = []
+    objs, rebuilt = [], False
     common = ["-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include")]
-    if os.environ.get("WENOEXT_KDEBUG"):  # developer aid: device-side bounds checks
+    kdebug = bool(os.environ.get("WENOEXT_KDEBUG"))
+    if kdebug:  # developer aid: device-side bounds checks
         common.append("-DWENOEXT_KDEBUG")
+    stamp = os.path.join(objdir, "kdebug.stamp")
+    if kdebug != os.path.exists(stamp):
+        force = True
+        (open(stamp, "w").close() if kdebug else os.remove(stamp))
     for src in CU_SOURCES + CPP_SOURCES:
+        path = os.path.join(CSRC, src)
         obj = os.path.join(objdir, src.replace("/", "_") + ".o")
-        cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo"] + common
-        if src.endswith(".cu"):
-            cmd += ["-Xptxas", "-v"] if verbose else []
-        cmd += ["-c", os.path.join(CSRC, src), "-o", obj]
-        subprocess.run(cmd, check=True)
+        hs = _headers()
+        if src.startswith("setup/"):
+            hs = [h for h in hs if os.sep + "setup" + os.sep in h or h.endswith("wenoext_b200.h")]
+        if force or _newer(obj, [path] + hs):
+            cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo"] + common
+            if src.endswith(".cu"):
+                cmd += ["-Xptxas", "-v"] if verbose else []
+            cmd += ["-c", path, "-o", obj]
+            subprocess.run(cmd, check=True)
+            rebuilt = True
         objs.append(obj)
-    cmd = ["nvcc", "-shared", "-o", LIB] + objs + ["-lpthread", "-ldl", "-cudart", "static"]
-    subprocess.run(cmd, check=True)
+    if rebuilt or not os.path.exists(LIB):
+        cmd = ["nvcc", "-shared", "-o", LIB] + objs + ["-lpthread", "-ldl", "-cudart", "static"]
+        subprocess.run(cmd, check=True)
     return LIB
 
 

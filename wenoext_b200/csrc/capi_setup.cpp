@@ -9,6 +9,7 @@
 #include "plan_internal.h"
 #include "setup/box_fast.h"
 #include "setup/weno_setup.h"
+#include "setup/wenobase_cache.h"
 
 using namespace wenoext;
 
@@ -156,5 +157,118 @@ extern "C" int wenoext_setup_geometry(wenoext_setup* s, const double** cellCentr
     if (!s) return WENOEXT_ERR_INVALID;
     if (cellCentres) *cellCentres = s->hp.cellCentres.data();
     if (faceAreaVec) *faceAreaVec = s->hp.faceAreaVec.data();
+    return 0;
+}
+
+// ---- constant/WENOBase<order>/ cache ----------------------
+
+extern "C" int wenoext_cache_write(wenoext_setup* s, const char* dir, int labelBytes, int simdDoubles) {
+    if (!s || !dir) {
+        setError("cache_write: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    try {
+        CacheFormat fmt;
+        fmt.labelBytes = labelBytes ? labelBytes : 4;
+        fmt.simdDoubles = simdDoubles ? simdDoubles : 8;
+        writeWenoBaseCache(s->hp, dir, fmt);
+    } catch (const std::exception& e) {
+        setError(std::string("cache_write: ") + e.what());
+        return WENOEXT_ERR_SETUP;
+    }
+    return 0;
+}
+
+extern "C" int wenoext_cache_read(const char* dir, const wenoext_mesh_desc* m, int32_t myProc,
+                                  int labelBytes, wenoext_setup** out) {
+    if (!dir || !m || !out) {
+        setError("cache_read: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    *out = nullptr;
+    try {
+        auto s = std::make_unique<wenoext_setup>();
+        HostPlan& h = s->hp;
+        CacheFormat fmt;
+        fmt.labelBytes = labelBytes;
+        readWenoBaseCache(dir, myProc, h, fmt);
+        if (m->nCells != h.nCells)
+            throw std::runtime_error("the cache holds " + std::to_string(h.nCells) + " cells, the mesh " +
+                                     std::to_string(m->nCells));
+        if (m->nFaces != h.nFaces)
+            throw std::runtime_error("the cache holds " + std::to_string(h.nFaces) + " faces, the mesh " +
+                                     std::to_string(m->nFaces));
+        if (m->nInternalFaces < 0 || m->nInternalFaces > m->nFaces || !m->owner ||
+            (m->nInternalFaces > 0 && !m->neighbour))
+            throw std::runtime_error("bad mesh addressing");
+        if (myProc < 0 || myProc >= std::max(1, h.nProcs)) throw std::runtime_error("myProc out of range");
+        h.nInternalFaces = m->nInternalFaces;
+        h.owner.assign(m->owner, m->owner + m->nFaces);
+        h.neighbour.assign(m->neighbour, m->neighbour + m->nInternalFaces);
+        for (int f = 0; f < m->nFaces; ++f)
+            if (h.owner[f] < 0 || h.owner[f] >= h.nCells) throw std::runtime_error("owner out of range");
+        for (int f = 0; f < m->nInternalFaces; ++f)
+            if (h.neighbour[f] < 0 || h.neighbour[f] >= h.nCells) throw std::runtime_error("neighbour out of range");
+        if (m->cellFaceStart && m->cellFaces) {
+            h.cellFaceStart.assign(m->cellFaceStart, m->cellFaceStart + h.nCells + 1);
+            h.cellFaces.assign(m->cellFaces, m->cellFaces + h.cellFaceStart[h.nCells]);
+        } else {
+            // primitiveMesh::calcCells (OpenFOAM): owned faces first, then neighboured ones
+            h.cellFaceStart.assign((size_t)h.nCells + 1, 0);
+            for (int f = 0; f < m->nFaces; ++f) ++h.cellFaceStart[h.owner[f] + 1];
+            for (int f = 0; f < m->nInternalFaces; ++f) ++h.cellFaceStart[h.neighbour[f] + 1];
+            for (int c = 0; c < h.nCells; ++c) h.cellFaceStart[c + 1] += h.cellFaceStart[c];
+            h.cellFaces.assign((size_t)h.cellFaceStart[h.nCells], 0);
+            std::vector<int32_t> fill(h.cellFaceStart.begin(), h.cellFaceStart.end() - 1);
+            for (int f = 0; f < m->nFaces; ++f) h.cellFaces[fill[h.owner[f]]++] = f;
+            for (int f = 0; f < m->nInternalFaces; ++f) h.cellFaces[fill[h.neighbour[f]]++] = f;
+        }
+        h.patches.clear();
+        for (int i = 0; i < m->nPatches; ++i) {
+            Patch p;
+            p.type = m->patches[i].type;
+            p.start = m->patches[i].start;
+            p.size = m->patches[i].size;
+            p.nbr = m->patches[i].nbr;
+            if (p.size < 0 || p.start < m->nInternalFaces || p.start + p.size > m->nFaces)
+                throw std::runtime_error("patch " + std::to_string(i) + " outside the boundary faces");
+            h.patches.push_back(p);
+        }
+        if (m->patchNbrCell) h.patchNbrCell.assign(m->patchNbrCell, m->patchNbrCell + (m->nFaces - m->nInternalFaces));
+        h.requestHaloCellID.assign((size_t)std::max(1, h.nProcs), {});
+        if (h.nProcs <= 1) {  // a serial cache has one-entry processor lists
+            h.nProcs = 1;
+            h.sendProcList.assign(1, -1);
+            h.receiveProcList.assign(1, -1);
+            h.receiveHaloSize.assign(1, 0);
+            h.sendHaloCellIDList.assign(1, {});
+        }
+        *out = s.release();
+    } catch (const std::exception& e) {
+        setError(std::string("cache_read: ") + e.what());
+        return WENOEXT_ERR_SETUP;
+    }
+    return 0;
+}
+
+extern "C" int wenoext_setup_mesh(wenoext_setup* s, wenoext_mesh_desc* m) {
+    if (!s || !m) {
+        setError("setup_mesh: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    HostPlan& h = s->hp;
+    memset(m, 0, sizeof(*m));
+    m->nCells = h.nCells;
+    m->nFaces = h.nFaces;
+    m->nInternalFaces = h.nInternalFaces;
+    m->owner = h.owner.data();
+    m->neighbour = h.neighbour.data();
+    m->cellFaceStart = h.cellFaceStart.data();
+    m->cellFaces = h.cellFaces.data();
+    s->patches.clear();
+    for (const Patch& p : h.patches) s->patches.push_back({p.type, p.start, p.size, p.nbr});
+    m->nPatches = (int32_t)s->patches.size();
+    m->patches = s->patches.data();
+    m->patchNbrCell = h.patchNbrCell.empty() ? nullptr : h.patchNbrCell.data();
     return 0;
 }

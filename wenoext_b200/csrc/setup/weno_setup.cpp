@@ -11,6 +11,7 @@
 
 #include "geometry_weno.h"
 #include "svd.h"
+#include "wenobase_cache.h"
 
 namespace wenoext {
 
@@ -239,14 +240,7 @@ double maxMag(const std::vector<double>& A) {
     for (double v : A) m = std::max(m, std::fabs(v));
     return m;
 }
-int32_t hashMatrix(const std::vector<double>& A) {
-    int32_t key = 0;
-    double mx = maxMag(A);
-    if (mx == 0) return key;
-    double mult = 1.0e6 / mx;
-    for (double v : A) key += (int32_t)(v * mult);
-    return key;
-}
+int32_t hashMatrix(const std::vector<double>& A) { return matrixKey(A.data(), A.size()); }
 }  // namespace
 
 int32_t detail::MatrixPool::insertNew(int32_t key, const std::vector<double>& A) {
