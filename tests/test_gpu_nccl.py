@@ -11,7 +11,9 @@ pytestmark = pytest.mark.gpu
 
 NPROC = {2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
 # small: plain host path; large with 2 slabs: the slab-pipelined host path of parallel plans
-MESHES = {"small": ((24, 16, 16), None), "large": ((64, 32, 32), "2")}
+# "nccl": exchange #1 by NCCL send/recv (WENOEXT_P2P=0) instead of the one-sided push over
+# peer memory that is the default with one process per GPU
+MESHES = {"small": ((24, 16, 16), None), "large": ((64, 32, 32), "2"), "nccl": ((24, 16, 16), None)}
 
 
 def _worker(rank, world, port, q, mesh):
@@ -25,6 +27,8 @@ def _worker(rank, world, port, q, mesh):
     N, slabs = MESHES[mesh]
     if slabs:
         os.environ["WENOEXT_E2E_SLABS"] = slabs
+    if mesh == "nccl":
+        os.environ["WENOEXT_P2P"] = "0"
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -50,6 +54,13 @@ def _worker(rank, world, port, q, mesh):
             out = torch.empty((mine.nFaces, 3), dtype=torch.float64, device="cuda")
             plan.correction(scheme, bounded, dvf, dfl, out=out)
             errs.append(H.normwise_err(out.cpu().numpy().reshape(ref.shape), ref))
+        # scalar field (value stride 1: four cells per 32-byte sector at the halo boundary)
+        svfs = [np.ascontiguousarray(v[:, 0]) for v in vfs]
+        ref = correction_multirank(Oracle("c"), cases, 0, 1, svfs, fls)[rank]
+        out = torch.empty((mine.nFaces,), dtype=torch.float64, device="cuda")
+        for _ in range(2):
+            plan.correction(0, 1, torch.from_numpy(svfs[rank]).cuda(), torch.from_numpy(fls[rank]).cuda(), out=out)
+        errs.append(H.normwise_err(out.cpu().numpy().reshape(ref.shape), ref))
         q.put((rank, errs))
         dist.barrier()
         plan.destroy()
@@ -57,7 +68,7 @@ def _worker(rank, world, port, q, mesh):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mesh", ["small", "large"])
+@pytest.mark.parametrize("mesh", ["small", "large", "nccl"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_nccl_ranks_match_oracle(world, mesh):
     import torch

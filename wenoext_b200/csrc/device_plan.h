@@ -125,8 +125,17 @@ struct CellKernelArgs {
     const RecInfo* recInfo;    // [nCells]
     const int32_t* cellList;   // nullable: work item -> cell
     int32_t workBase;          // first work item of this launch (slabs of one call)
-    int32_t* tileCounter;      // zeroed before the launch: next tile of 32 work items
+    int32_t* tileCounter;      // [2], zeroed before the launch: next tile of the two ranges
     int32_t nWork;
+    // Halo gate (parallel plans, interior and boundary cells in ONE launch): work items
+    // [0, gateItem) are interior cells, [gateItem, nWork) boundary cells, which read halo
+    // values. A warp that has run out of interior tiles goes on with boundary tiles
+    // (tileCounter[1]) if gateFlags[q] >= gateEpoch for all nGate senders (raised by their
+    // halo_push_kernel once exchange #1 has landed in `vals`) and stops otherwise; a
+    // follow-up launch with the same counters and nGate == 0 takes what is left.
+    // gateItem < 0: one range, no gate.
+    const int32_t* gateFlags;
+    int32_t nGate, gateEpoch, gateItem;
     int32_t K;
     int32_t nComp;             // stride of corr / faceValue / thetaPatch
     int32_t c0;                // first component of this batch
@@ -207,5 +216,17 @@ void launchPackValues(const double* vf, int nCells, int nComp, int c0, int CB, i
                       double* vals, cudaStream_t st);
 void launchPackHalo(const double* vals, int VS, const int32_t* sendIds, int64_t nSend,
                     double* sendBuf, cudaStream_t st);
+struct HaloPushArgs {
+    int32_t nPeers, VS, epoch;
+    const double* vals;        // this rank's packed values
+    const int32_t* sendIds;    // sendHaloCellIDList flattened, peer after peer
+    int64_t off[33];           // [nPeers+1] running count of cells pushed to peers 0..i-1
+    int64_t src0[32];          // first entry of peer i in sendIds
+    double* dst[32];           // receiver's value buffer at nCells + haloOffset(this rank)
+    int32_t* flag[32];         // receiver's flag for this rank
+    int32_t* done;             // block counter, zero between launches
+};
+void launchHaloPush(const HaloPushArgs& a, cudaStream_t st);
+void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st);
 
 }  // namespace wenoext

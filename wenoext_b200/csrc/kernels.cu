@@ -25,6 +25,7 @@
 // barriers after start-up, no cross-warp synchronisation. The kernel is HBM-bound:
 // tensor cores are deliberately unused (independent 9x21 GEMVs, no operand reuse).
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdio>
 #include <stdint.h>
 
@@ -82,6 +83,11 @@ __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
         : "memory");
 }
 #endif
+__device__ __forceinline__ int32_t ldAcquireSys(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ uint64_t evictFirstPolicy() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -176,7 +182,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     // counter (one tile ahead, so the atomic's latency is hidden). A CTA that starts late
     // (e.g. while a NCCL kernel holds its SM) simply takes fewer tiles.
     constexpr int PPT = TILE / CELLS;  // passes per tile
-    const int nTiles = (a.nWork + TILE - 1) / TILE;
+    // Two ranges of work items: A = [0, gateItem) (interior cells) and B = [gateItem, nWork)
+    // (boundary cells, whose stencils gather halo values); without a gate everything is A.
+    // Tiles of A come from tileCounter[0]. Once A is exhausted a warp looks at the halo flags
+    // (one per sending rank, raised by that rank's halo_push_kernel over NVLink once its
+    // values sit in this GPU's `vals`): all raised -> it goes on with tiles of B from
+    // tileCounter[1]; not yet -> it stops, and the host's follow-up launch (behind
+    // halo_wait_kernel, same counters, nGate == 0) takes what is left of B. The persistent
+    // grid never spins on a flag.
+    const bool split = a.gateItem >= 0;
+    const int nA = split ? a.gateItem : a.nWork;
+    const int nTilesA = (nA + TILE - 1) / TILE;
+    const int nTiles = nTilesA + (split ? (a.nWork - nA + TILE - 1) / TILE : 0);
     // The atomic's result stays untouched in lane 0 (pendingTile) for half a tile before
     // it is broadcast, so nobody ever waits for its latency.
     auto grabTile = [&]() {
@@ -184,7 +201,19 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         if (lane == 0) t = atomicAdd(a.tileCounter, 1);
         return t;
     };
-    int curTile = __shfl_sync(0xffffffffu, grabTile(), 0);
+    // lane 0's raw counter value -> tile index on every lane (>= nTiles: no more work)
+    auto resolveTile = [&](int raw) {
+        int t = __shfl_sync(0xffffffffu, raw, 0);
+        if (t < nTilesA) return t;
+        // range B: lane q looks at the flag of sender q (acquire: the halo gathers that follow
+        // must see what that sender pushed before it raised the flag)
+        bool ok = split;
+        if (lane < a.nGate) ok = ldAcquireSys(a.gateFlags + lane) >= a.gateEpoch;
+        const bool ready = __all_sync(0xffffffffu, ok);
+        if (lane == 0) t = ready ? nTilesA + atomicAdd(a.tileCounter + 1, 1) : nTiles;
+        return __shfl_sync(0xffffffffu, t, 0);
+    };
+    int curTile = resolveTile(grabTile());
     if (curTile >= nTiles) return;
     int pendingTile = grabTile();  // becomes nextTile at pass PPT / 2 of the current tile
     int nextTile = nTiles;
@@ -195,8 +224,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     auto workItem = [&](int k, int c) {
         const int t = tp + k;
         const int tile = t < PPT ? curTile : nextTile;
-        const int w = tile * TILE + (t & (PPT - 1)) * CELLS + c;
-        return (tile < nTiles && w < a.nWork) ? a.workBase + w : -1;
+        const int off = (t & (PPT - 1)) * CELLS + c;
+        const bool inA = tile < nTilesA;
+        const int w = inA ? tile * TILE + off : nA + (tile - nTilesA) * TILE + off;
+        return (tile < nTiles && w < (inA ? nA : a.nWork)) ? a.workBase + w : -1;
     };
     auto workToCell = [&](int w) { return a.cellList ? __ldg(a.cellList + w) : w; };
 
@@ -677,7 +708,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             if (curTile >= nTiles) break;
             pendingTile = grabTile();
         } else if (tp == PPT / 2) {
-            nextTile = __shfl_sync(0xffffffffu, pendingTile, 0);
+            nextTile = resolveTile(pendingTile);
         }
         infoCur = infoNext;
         infoNext = infoNN;
@@ -899,6 +930,54 @@ void launchPackValues(const double* vf, int nCells, int nComp, int c0, int CB, i
     if (n <= 0) return;
     pack_values_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(vf, nCells, nComp, c0, CB, VS,
                                                                     vals);
+}
+
+// Exchange #1 as a one-sided push (one process per GPU, peers' buffers mapped with CUDA
+// IPC): sendHaloData of WENOCoeff.C:254-258 is written straight into each receiver's value
+// buffer over NVLink, behind its local cells, where the receiver's gathers expect it. The
+// last block to finish raises the receivers' flags (threadfence + block counter), so a
+// raised flag means every value of this step has arrived.
+__global__ void halo_push_kernel(const __grid_constant__ HaloPushArgs a) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t total = a.off[a.nPeers] * a.VS;
+    if (i < total) {
+        const int64_t k = i / a.VS;
+        const int c = (int)(i - k * a.VS);
+        int p = 0;
+        while (k >= a.off[p + 1]) ++p;
+        const int64_t j = k - a.off[p];
+        a.dst[p][j * a.VS + c] = a.vals[(size_t)a.sendIds[a.src0[p] + j] * a.VS + c];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(a.done, 1) == (int)gridDim.x - 1) {
+        *a.done = 0;
+        __threadfence_system();
+        for (int p = 0; p < a.nPeers; ++p)
+            asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(a.flag[p]), "r"(a.epoch) : "memory");
+    }
+}
+void launchHaloPush(const HaloPushArgs& a, cudaStream_t st) {
+    const int64_t total = a.off[a.nPeers] * a.VS;
+    halo_push_kernel<<<(unsigned)std::max<int64_t>(1, (total + 255) / 256), 256, 0, st>>>(a);
+}
+
+// Host-side stream order behind the halo: one lane per sending rank waits for its flag.
+// Nothing this GPU still has to do is needed for the flags to rise (the senders push on
+// their own), so the wait cannot deadlock; it traps instead of hanging if a peer died.
+__global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch) {
+    if ((int)threadIdx.x >= n) return;
+    long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (ldAcquireSys(flags + threadIdx.x) < epoch) {
+        __nanosleep(200);
+        long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 20000000000ll) __trap();
+    }
+}
+void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st) {
+    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch);
 }
 
 void launchPackHalo(const double* vals, int VS, const int32_t* sendIds, int64_t nSend,

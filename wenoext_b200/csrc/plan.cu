@@ -242,6 +242,8 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     if (const char* e = getenv("WENOEXT_SLOTS")) P->cfgSlots = atoi(e);
     if (const char* e = getenv("WENOEXT_GRID")) P->cfgGrid = atoi(e);
     if (const char* e = getenv("WENOEXT_SMEM_KB")) P->cfgSmemKB = atoi(e);
+    if (const char* e = getenv("WENOEXT_MERGE")) P->cfgMerge = atoi(e);
+    if (const char* e = getenv("WENOEXT_P2P")) P->cfgP2P = atoi(e);
 
     // coefficient enumeration: n-outer, m, l-inner (WENOUpwindFit.C:304-319)
     const int s1 = d->polOrder + 1;
@@ -474,8 +476,12 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         P->nInterior = (int32_t)li.size();
         P->nBoundaryCells = (int32_t)lb.size();
         if (P->nBoundaryCells > 0) {
-            rc = rc ? rc : upload(&P->cellListInterior, li.data(), li.size());
-            rc = rc ? rc : upload(&P->cellListBoundary, lb.data(), lb.size());
+            // one allocation, boundary list right behind the interior list, so that a single
+            // launch can run over both (halo gate of the cell kernel)
+            std::vector<int32_t> all(li);
+            all.insert(all.end(), lb.begin(), lb.end());
+            rc = rc ? rc : upload(&P->cellListInterior, all.data(), all.size());
+            P->cellListBoundary = P->cellListInterior + li.size();
         }
     }
     // Slabs for the pipelined host-buffer path (serial plans): what a prefix of the cells
@@ -573,11 +579,18 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     cudaSetDevice(P->device);
     if (P->h_fix) cudaFreeHost(P->h_fix);
     void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
-                    P->tileCounter, P->records, P->recInfo, P->cellListInterior, P->cellListBoundary, P->owner,
+                    P->tileCounter, P->haloFlags, P->pushDone, P->records, P->recInfo, P->cellListInterior, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
                     P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
     for (void* p : ptrs)
-        if (p) cudaFree(p);
+        if (p && p != P->valsIpc[0] && p != P->valsIpc[1]) cudaFree(p);
+    for (auto& pp : P->pushPeers) {
+        for (double* v : pp.vals)
+            if (v) cudaIpcCloseMemHandle(v);
+        if (pp.flags) cudaIpcCloseMemHandle(pp.flags);
+    }
+    for (double* v : P->valsIpc)
+        if (v) cudaFree(v);
     if (P->comm) {
         if (NcclApi* n = ncclApi()) n->CommDestroy(P->comm);
     }
@@ -619,6 +632,7 @@ NcclApi* ncclApi() {
     api.Recv = (decltype(api.Recv))sym("ncclRecv");
     api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
     api.GroupEnd = (decltype(api.GroupEnd))sym("ncclGroupEnd");
+    api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
     api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
     if (!api.GetUniqueId || !api.CommInitRank || !api.Send || !api.Recv || !api.GroupStart ||
         !api.GroupEnd) {
@@ -648,6 +662,134 @@ extern "C" int wenoext_nccl_unique_id(char id[128]) {
     return 0;
 }
 
+// One-sided halo push (plan_internal.h: p2p). Every rank exports its two value buffers and
+// its flag array with CUDA IPC; handles and the tables a sender needs (where its values go in
+// the receiver's buffer, which flag is its own) travel in one ncclAllGather. All ranks take
+// the same decision: if any rank cannot take part, everybody stays with NCCL send/recv.
+namespace {
+struct P2PBlobHead {
+    cudaIpcMemHandle_t hVals[2], hFlags;
+    int32_t ok, nCells;
+};
+}  // namespace
+
+static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
+    if (!n->AllGather) return 0;
+    const int R = P->nProcs, me = P->myProc;
+    // senders and receivers of this rank; the double buffering relies on a symmetric
+    // relation (whoever sends to me also receives from me)
+    std::vector<int32_t> slotOf(R, -1);
+    int32_t ok = 1, nRecv = 0, nSend = 0;
+    for (int p = 0; p < R; ++p) {
+        const bool snd = P->sendProcList[p] != -1 && P->sendOff[p + 1] > P->sendOff[p];
+        const bool rcv = P->receiveProcList[p] != -1 && P->haloOff[p + 1] > P->haloOff[p];
+        if (snd != rcv || (snd && p == me)) ok = 0;
+        if (rcv) slotOf[p] = nRecv++;
+        if (snd) ++nSend;
+    }
+    if (nRecv > 32 || nSend > 32) ok = 0;
+    const size_t valsN = ((size_t)P->nCells + P->nHaloTotal) * 4;
+    bool allocOk = true;
+    for (int i = 0; i < 2; ++i)
+        allocOk = allocOk && cudaMalloc((void**)&P->valsIpc[i], std::max<size_t>(valsN, 1) * 8) == cudaSuccess;
+    allocOk = allocOk && cudaMalloc((void**)&P->haloFlags, 32 * sizeof(int32_t)) == cudaSuccess;
+    allocOk = allocOk && cudaMalloc((void**)&P->pushDone, sizeof(int32_t)) == cudaSuccess;
+    P2PBlobHead head{};
+    if (allocOk) {
+        cudaMemset(P->haloFlags, 0, 32 * sizeof(int32_t));
+        cudaMemset(P->pushDone, 0, sizeof(int32_t));
+        allocOk = cudaIpcGetMemHandle(&head.hVals[0], P->valsIpc[0]) == cudaSuccess &&
+                  cudaIpcGetMemHandle(&head.hVals[1], P->valsIpc[1]) == cudaSuccess &&
+                  cudaIpcGetMemHandle(&head.hFlags, P->haloFlags) == cudaSuccess;
+    }
+    if (!allocOk) {
+        cudaGetLastError();
+        ok = 0;
+    }
+    head.ok = ok;
+    head.nCells = P->nCells;
+    // blob: head | haloBase[R] (int64: where sender q's values start in my buffer) | slot[R]
+    const size_t blob = sizeof(P2PBlobHead) + (size_t)R * 8 + (size_t)R * 4;
+    const size_t blobPad = (blob + 15) / 16 * 16;
+    std::vector<unsigned char> mine(blobPad, 0), all(blobPad * R, 0);
+    memcpy(mine.data(), &head, sizeof(head));
+    for (int q = 0; q < R; ++q) {
+        const int64_t base = (int64_t)P->nCells + P->haloOff[q];
+        memcpy(mine.data() + sizeof(head) + (size_t)q * 8, &base, 8);
+        memcpy(mine.data() + sizeof(head) + (size_t)R * 8 + (size_t)q * 4, &slotOf[q], 4);
+    }
+    unsigned char *dMine = nullptr, *dAll = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&dMine, blobPad));
+    CUDA_TRY(cudaMalloc((void**)&dAll, blobPad * R));
+    auto gather = [&](const void* src, void* dst, size_t bytes) -> int {
+        CUDA_TRY(cudaMemcpy(dMine, src, bytes, cudaMemcpyHostToDevice));
+        NCCL_TRY(n, n->AllGather(dMine, dAll, bytes, /*ncclChar*/ 0, P->comm, P->commStream));
+        CUDA_TRY(cudaStreamSynchronize(P->commStream));
+        CUDA_TRY(cudaMemcpy(dst, dAll, bytes * R, cudaMemcpyDeviceToHost));
+        return 0;
+    };
+    int rc = gather(mine.data(), all.data(), blobPad);
+    bool use = rc == 0;
+    auto headOf = [&](int p) {
+        P2PBlobHead h;
+        memcpy(&h, all.data() + (size_t)p * blobPad, sizeof(h));
+        return h;
+    };
+    for (int p = 0; use && p < R; ++p) use = headOf(p).ok != 0;
+    // map the receivers' buffers
+    int32_t opened = use ? 1 : 0;
+    if (use) {
+        for (int p = 0; p < R && opened; ++p) {
+            if (!(P->sendProcList[p] != -1 && P->sendOff[p + 1] > P->sendOff[p])) continue;
+            const P2PBlobHead h = headOf(p);
+            wenoext_plan::PushPeer pp;
+            pp.proc = p;
+            const unsigned char* tab = all.data() + (size_t)p * blobPad + sizeof(P2PBlobHead);
+            memcpy(&pp.haloBase, tab + (size_t)me * 8, 8);
+            memcpy(&pp.slot, tab + (size_t)R * 8 + (size_t)me * 4, 4);
+            bool o = pp.slot >= 0;
+            for (int i = 0; i < 2 && o; ++i)
+                o = cudaIpcOpenMemHandle((void**)&pp.vals[i], h.hVals[i], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            o = o && cudaIpcOpenMemHandle((void**)&pp.flags, h.hFlags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            P->pushPeers.push_back(pp);  // (closed in plan_destroy, also when partly opened)
+            if (!o) {
+                cudaGetLastError();
+                opened = 0;
+            }
+        }
+    }
+    // second agreement: every rank could map what it needs
+    if (rc == 0) {
+        std::vector<int32_t> st(4, opened), stAll((size_t)4 * R, 0);
+        rc = gather(st.data(), stAll.data(), 16);
+        for (int p = 0; p < R; ++p) use = use && stAll[(size_t)4 * p] != 0;
+    }
+    cudaFree(dMine);
+    cudaFree(dAll);
+    if (rc) return rc;
+    if (!use) {
+        for (auto& pp : P->pushPeers) {
+            for (double*& v : pp.vals)
+                if (v) cudaIpcCloseMemHandle(v), v = nullptr;
+            if (pp.flags) cudaIpcCloseMemHandle(pp.flags), pp.flags = nullptr;
+        }
+        P->pushPeers.clear();
+        for (double*& v : P->valsIpc)
+            if (v) cudaFree(v), v = nullptr;
+        if (getenv("WENOEXT_VERBOSE")) fprintf(stderr, "[wenoext rank %d] halo push unavailable, using NCCL send/recv\n", me);
+        return 0;
+    }
+    P->nRecvPeers = nRecv;
+    if (P->vals && P->vals != P->valsIpc[0] && P->vals != P->valsIpc[1]) cudaFree(P->vals);
+    P->vals = P->valsIpc[0];
+    P->valsCap = valsN;
+    P->p2p = true;
+    if (getenv("WENOEXT_VERBOSE"))
+        fprintf(stderr, "[wenoext rank %d] halo push over peer memory: %d senders, %zu receivers\n", me, nRecv,
+                P->pushPeers.size());
+    return 0;
+}
+
 extern "C" int wenoext_attach_nccl(wenoext_plan* P, const char id[128], int rank, int nRanks) {
     if (!P || !id) {
         setError("attach_nccl: NULL argument");
@@ -663,7 +805,17 @@ extern "C" int wenoext_attach_nccl(wenoext_plan* P, const char id[128], int rank
     NcclId nid;
     memcpy(nid.internal, id, 128);
     NCCL_TRY(n, n->CommInitRank(&P->comm, nRanks, nid, rank));
-    CUDA_TRY(cudaStreamCreateWithFlags(&P->commStream, cudaStreamNonBlocking));
+    {
+        // highest priority: when the exchange kernel and the persistent cell kernel become
+        // ready together, the exchange gets its SMs first (the cell kernel leaves no room for
+        // a second resident CTA, and late cell CTAs just take fewer tiles)
+        int prLow = 0, prHigh = 0;
+        CUDA_TRY(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
+        if (const char* e = getenv("WENOEXT_COMM_PRIO"))
+            if (atoi(e) == 0) prHigh = prLow;
+        CUDA_TRY(cudaStreamCreateWithPriority(&P->commStream, cudaStreamNonBlocking, prHigh));
+    }
+    if (P->cfgP2P) return setupHaloPush(P, n);
     return 0;
 }
 
@@ -729,7 +881,7 @@ extern "C" int wenoext_kernel_time(wenoext_plan* P, double* msSum, int* nLaunche
         CUDA_TRY(cudaEventSynchronize(P->timeEvents[i + 1]));
         CUDA_TRY(cudaEventElapsedTime(&ms, P->timeEvents[i], P->timeEvents[i + 1]));
         *msSum += (double)ms;
-        if (getenv("WENOEXT_TIMING_VERBOSE") && i < 12) {  // developer aid
+        if (getenv("WENOEXT_TIMING_VERBOSE") && i < 200) {  // developer aid
             float gap = 0;
             if (i >= 2) cudaEventElapsedTime(&gap, P->timeEvents[i - 1], P->timeEvents[i]);
             fprintf(stderr, "[wenoext rank %d] cell-kernel launch %zu: %.4f ms (gap before: %.4f ms)\n",
@@ -759,18 +911,27 @@ static int ensureBuf(double** p, size_t* cap, size_t n) {
     return 0;
 }
 
-static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase = 0) {
+// gateItem >= 0: work items from gateItem on are boundary cells behind the halo gate
+// (device_plan.h); followUp: second launch of such a pair, counters kept, gate known open
+static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase = 0,
+                       int gateItem = -1, bool followUp = false) {
     if (nWork <= 0) return 0;
     const wenoext_call& c = P->call;
     CellKernelArgs a{};
     a.records = P->records;
     a.recInfo = P->recInfo;
     a.cellList = list;
-    if (!P->tileCounter) CUDA_TRY(cudaMalloc((void**)&P->tileCounter, sizeof(int32_t)));
-    CUDA_TRY(cudaMemsetAsync(P->tileCounter, 0, sizeof(int32_t), c.st));
+    if (!P->tileCounter) CUDA_TRY(cudaMalloc((void**)&P->tileCounter, 2 * sizeof(int32_t)));
+    if (!followUp) CUDA_TRY(cudaMemsetAsync(P->tileCounter, 0, 2 * sizeof(int32_t), c.st));
     a.tileCounter = P->tileCounter;
     a.workBase = workBase;
     a.nWork = nWork;
+    a.gateItem = gateItem;
+    if (gateItem >= 0 && !followUp) {
+        a.gateFlags = P->haloFlags;
+        a.nGate = P->nRecvPeers;
+        a.gateEpoch = P->haloEpoch;
+    }
     a.K = P->K;
     a.nComp = c.nComp;
     a.c0 = c.c0;
@@ -846,7 +1007,7 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
     a.ringSteps = ring;
     a.warpBytes = (int32_t)warpBytesFor(ring);
     const size_t smem = cellKernelSmemBytes(a);
-    const int nTiles = (nWork + 31) / 32;
+    const int nTiles = ((followUp ? nWork - gateItem : nWork) + 31) / 32;
     int grid = std::min(P->cfgGrid > 0 ? P->cfgGrid : P->nSM, nTiles);
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     if (P->timing) {
@@ -886,9 +1047,45 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
 static int phase0(wenoext_plan* P, bool launchInterior = true) {
     const wenoext_call& c = P->call;
     const bool parallel = P->nProcs > 1;
+    if (P->p2p) {
+        // values of step k live in buffer k & 1: a sender may already push step k+1 while this
+        // rank still reads step k (it cannot be further ahead: it needs this rank's step-k+1
+        // halo, pushed after this rank's step k, to finish its own step k+1)
+        ++P->haloEpoch;
+        P->vals = P->valsIpc[P->haloEpoch & 1];
+    }
     launchPackValues(c.vf, P->nCells, c.nComp, c.c0, c.CB, c.VS, P->vals, c.st);
     P->lastLaunches++;
     if (!parallel) return 0;
+    P->mergedLaunch = false;
+    if (P->p2p) {
+        if (!P->pushPeers.empty()) {
+            HaloPushArgs a{};
+            a.nPeers = (int32_t)P->pushPeers.size();
+            a.VS = c.VS;
+            a.epoch = P->haloEpoch;
+            a.vals = P->vals;
+            a.sendIds = P->sendIds;
+            a.done = P->pushDone;
+            for (int i = 0; i < a.nPeers; ++i) {
+                const auto& pp = P->pushPeers[i];
+                a.src0[i] = P->sendOff[pp.proc];
+                a.off[i + 1] = a.off[i] + (P->sendOff[pp.proc + 1] - P->sendOff[pp.proc]);
+                a.dst[i] = pp.vals[P->haloEpoch & 1] + pp.haloBase * c.VS;
+                a.flag[i] = pp.flags + pp.slot;
+            }
+            launchHaloPush(a, c.st);
+            P->lastLaunches++;
+        }
+        if (!launchInterior) return 0;
+        // One launch for interior and boundary cells when the halo region of `vals` starts on
+        // a 32-byte sector (the gathers use the non-coherent path: no sector that an interior
+        // gather can have pulled into an L1 may hold halo values).
+        P->mergedLaunch = P->cfgMerge && P->nBoundaryCells > 0 && ((int64_t)P->nCells * c.VS) % 4 == 0;
+        if (P->mergedLaunch)
+            return launchCells(P, P->cellListInterior, P->nInterior + P->nBoundaryCells, 0, P->nInterior);
+        return launchCells(P, P->cellListInterior, P->nInterior);
+    }
     if (P->nSendTotal > 0) {
         launchPackHalo(P->vals, c.VS, P->sendIds, P->nSendTotal, P->sendBuf, c.st);
         P->lastLaunches++;
@@ -922,7 +1119,10 @@ static int phase1(wenoext_plan* P) {
     if (!parallel) {
         if (int rc = launchCells(P, nullptr, P->nCells)) return rc;
     } else {
-        if (P->comm) {
+        if (P->p2p) {
+            launchHaloWait(P->haloFlags, P->nRecvPeers, P->haloEpoch, c.st);
+            if (P->nRecvPeers > 0) P->lastLaunches++;
+        } else if (P->comm) {
             CUDA_TRY(cudaStreamWaitEvent(c.st, P->evB, 0));
         } else {
             // in-process peers: pull my halo segments out of the owners' send buffers
@@ -936,7 +1136,16 @@ static int phase1(wenoext_plan* P) {
                                          (size_t)nr * c.VS * 8, cudaMemcpyDeviceToDevice, c.st));
             }
         }
-        if (int rc = launchCells(P, P->cellListBoundary, P->nBoundaryCells)) return rc;
+        if (P->mergedLaunch) {
+            // whatever the first launch left of the boundary cells (normally nothing: the
+            // exchange lands long before the interior cells are done)
+            if (int rc = launchCells(P, P->cellListInterior, P->nInterior + P->nBoundaryCells, 0,
+                                     P->nInterior, true))
+                return rc;
+        } else if (int rc = launchCells(P, P->cellListBoundary, P->nBoundaryCells)) {
+            return rc;
+        }
+        P->mergedLaunch = false;
     }
     if (P->hasProcessor) {
         CUDA_TRY(cudaEventRecord(P->evC, c.st));

@@ -28,6 +28,7 @@ struct NcclApi {
     int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
 NcclApi* ncclApi();  // nullptr (and last error set) if libnccl cannot be loaded
@@ -57,6 +58,27 @@ struct wenoext_plan {
     int32_t* cellListInterior = nullptr;
     int32_t* cellListBoundary = nullptr;
     int32_t nInterior = 0, nBoundaryCells = 0;
+    // One process per GPU: exchange #1 as a one-sided push into the receivers' value buffers
+    // (CUDA IPC over NVLink, halo_push_kernel) instead of NCCL send/recv, so that no
+    // communication kernel competes with the persistent cell kernel for SMs. Interior and
+    // boundary cells then go in one launch, the boundary tiles behind the halo gate.
+    bool p2p = false;
+    double* valsIpc[2] = {nullptr, nullptr};  // double-buffered value buffers the peers write into
+    int32_t* haloFlags = nullptr;             // [nRecvPeers]: epoch of the last halo each sender delivered
+    int32_t nRecvPeers = 0;
+    int32_t* pushDone = nullptr;              // block counter of halo_push_kernel
+    struct PushPeer {
+        int32_t proc = 0;
+        double* vals[2] = {nullptr, nullptr};  // peer's valsIpc, mapped here
+        int32_t* flags = nullptr;              // peer's haloFlags, mapped here
+        int64_t haloBase = 0;                  // peer's nCells + its haloOff[this rank]
+        int32_t slot = 0;                      // this rank's index among the peer's senders
+    };
+    std::vector<PushPeer> pushPeers;
+    int32_t haloEpoch = 0;
+    bool mergedLaunch = false;  // this call's boundary cells already went with the interior launch
+    int cfgMerge = 1;           // WENOEXT_MERGE=0: separate interior / boundary launches
+    int cfgP2P = 1;             // WENOEXT_P2P=0: NCCL send/recv for exchange #1
     // faces / patches
     int32_t* owner = nullptr;
     int32_t* bfPatchType = nullptr;

@@ -8,6 +8,9 @@
 #include <string>
 #include <stdexcept>
 #include <thread>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 #include "geometry_weno.h"
 #include "svd.h"
@@ -334,6 +337,15 @@ HostPlan buildPlanGeneric(const PolyMesh& gm, const std::vector<int32_t>& cellPr
         for (int c = 0; c < gm.nCells; ++c) procLocalId[c] = cnt[cellProc[c]]++;
     }
 
+    const bool timing = getenv("WENOEXT_SETUP_TIMING") != nullptr;
+    auto t0 = std::chrono::steady_clock::now();
+    auto mark = [&](const char* what) {
+        if (!timing) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[wenoext setup] %-28s %8.3f s\n", what, std::chrono::duration<double>(t1 - t0).count());
+        t0 = t1;
+    };
+    mark("local mesh");
     // steps 1-4 per local cell, threaded; inserted into the pool in cell order
     const int nLocal = lm.nCells;
     std::vector<CellSetup> cells(nLocal);
@@ -356,6 +368,7 @@ HostPlan buildPlanGeneric(const PolyMesh& gm, const std::vector<int32_t>& cellPr
             if (!e.empty()) throw std::runtime_error(e);
     }
 
+    mark("stencils + pseudo-inverses");
     // correctParallelRun (WENOBase.C:1030-1126): halo ids in order of first
     // appearance over the (uncut) central lists
     hp.receiveProcList.assign(nProcs, -1);
@@ -438,18 +451,36 @@ HostPlan buildPlanGeneric(const PolyMesh& gm, const std::vector<int32_t>& cellPr
         hp.cellStencilStart.push_back((int64_t)hp.stencilMatrix.size());
     }
 
-    // step 5: B, intBasTrans, refFacAr on the local mesh (WENOBase.C:820-854)
+    mark("flatten + matrixDB");
+    // step 5: B, intBasTrans, refFacAr on the local mesh (WENOBase.C:820-854); cells are
+    // independent: a cell writes its own B, the side of each face it sits on, and refFacAr of
+    // the faces it owns
     hp.B.assign((size_t)nLocal * K * K, 0.0);
     const int s1 = prm.polOrder + 1;
     hp.intBasTrans.assign((size_t)lm.nFaces() * 2 * s1 * s1 * s1, 0.0);
     hp.refFacAr.assign(lm.nFaces(), 0.0);
-    for (int c = 0; c < nLocal; ++c) {
-        const CellSetup& cs = cells[c];
-        std::vector<double> B = geom::getB(lm, c, prm.polOrder, K, cs.JInv, cs.refPoint, hp.dim);
-        std::copy(B.begin(), B.end(), hp.B.begin() + (size_t)c * K * K);
-        geom::surfIntTransCell(lm, c, prm.polOrder, cs.volI, cs.JInv, cs.refPoint,
-                               hp.intBasTrans.data(), hp.refFacAr.data());
+    {
+        std::vector<std::thread> th;
+        std::vector<std::string> err(nThreads);
+        for (int t = 0; t < nThreads; ++t)
+            th.emplace_back([&, t]() {
+                try {
+                    for (int c = t; c < nLocal; c += nThreads) {
+                        const CellSetup& cs = cells[c];
+                        std::vector<double> B = geom::getB(lm, c, prm.polOrder, K, cs.JInv, cs.refPoint, hp.dim);
+                        std::copy(B.begin(), B.end(), hp.B.begin() + (size_t)c * K * K);
+                        geom::surfIntTransCell(lm, c, prm.polOrder, cs.volI, cs.JInv, cs.refPoint,
+                                               hp.intBasTrans.data(), hp.refFacAr.data());
+                    }
+                } catch (const std::exception& e) {
+                    err[t] = e.what();
+                }
+            });
+        for (auto& x : th) x.join();
+        for (auto& e : err)
+            if (!e.empty()) throw std::runtime_error(e);
     }
+    mark("B + face integrals");
     return hp;
 }
 
