@@ -20,7 +20,8 @@
 //                                (GA = GATHER_AHEAD)
 //     pad to 16 B                                          -> headBytes
 //   TAIL (needed after the matrix phase)
-//     double B[K*K]              B()[cell], row-major
+//     double Bs[K*(K+1)/2]       B()[cell] folded for the quadratic form: row k holds
+//                                B[k][k], then B[k][q] + B[q][k] for q > k (symTriSize)
 //     double faceD[nFc][K+1]     own-side intBasTrans()[f][side] compacted in sumFlux
 //                                enumeration order (WENOUpwindFit.C:304-319), refFacAr()[f]
 //     double quirk[K]            intBasTrans()[cellI][1] compacted (WENOUpwindFit01.C:125)
@@ -62,6 +63,8 @@ struct RecInfo {
 
 // columns per matrix chunk (also the unroll depth of the kernel's column loop)
 __host__ __device__ constexpr int chunkCols(int K) { return K <= 9 ? 3 : 2; }
+// c^T B c = sum_k c_k (B_kk c_k + sum_{q>k} (B_kq + B_qk) c_q): K(K+1)/2 folded entries
+__host__ __device__ constexpr int symTriSize(int K) { return K * (K + 1) / 2; }
 // the gather indices of chunk ch + GATHER_AHEAD travel with chunk ch (the kernel
 // issues the gathers of a column GATHER_AHEAD chunk steps before it needs the value)
 constexpr int GATHER_AHEAD = 2;
@@ -109,7 +112,7 @@ __host__ __device__ inline RecHeader recLayout(int K, int nSt, int Nmax, int nFc
     h.oIdx = o;
     o += 4 * clampCols(Nmax, GATHER_AHEAD * D) * nSt;
     h.headBytes = (o + 15) & ~15;
-    h.tailBytes = (8 * (K * K + nFc * (K + 1) + K) + 15) & ~15;
+    h.tailBytes = (8 * (symTriSize(K) + nFc * (K + 1) + K) + 15) & ~15;
     return h;
 }
 __host__ __device__ inline int64_t recMatrixBytes(int K, int nSt, int Nmax) {

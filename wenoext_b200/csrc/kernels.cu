@@ -88,6 +88,21 @@ __device__ __forceinline__ int32_t ldAcquireSys(const int32_t* p) {
     asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+// 1/x for normal, finite x of moderate magnitude: hardware seed (about 20 bits) and two
+// Newton steps, accurate to about 1 ulp; no special-case path. Used where the operand is a
+// sum of weights or a face area; x outside [1e-290, 1e290] goes through the IEEE division.
+__device__ __forceinline__ double fastRcp(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    return fma(r, e, r);
+}
+__device__ __forceinline__ double safeRcp(double x) {
+    const double ax = fabs(x);
+    return (ax > 1e-290 && ax < 1e290) ? fastRcp(x) : 1.0 / x;
+}
 __device__ __forceinline__ uint64_t evictFirstPolicy() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -448,6 +463,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const bool borrow = uniform && N == 0;
         const uint32_t pS = __shfl_sync(0xffffffffu, pairStride, srcLane);
         const uint32_t pStr = borrow ? pS : pairStride;
+        // whose matrix this lane reads: its own (cell slot, stencil), or the lender's; on a
+        // uniform mesh the lender's cell has Nmax == Nw
+        const int cslotE = borrow ? srcLane / SS : cslot;
+        const uint32_t sE = (uint32_t)(borrow ? srcLane % SS : s);
+        const int NmaxE = borrow ? Nw : Nmax;
         auto step = [&](const int ch, double (&nx)[D][CB]) {
             const int j0 = ch * D;
             double cu[D][CB];
@@ -462,16 +482,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             // gathers of the columns two steps ahead (their indices travel with this chunk)
             if (j0 + GATHER_AHEAD * D < Nw)
                 gather(chunk + (uint32_t)chunkIdxOffset(K, nSt, cols), j0 + GATHER_AHEAD * D, nx);
-            uint32_t Ap = chunk + (uint32_t)s * 16;
-            uint32_t Sp = chunk + (uint32_t)cols * KP * pairStride + (uint32_t)s * 8;
-            {
-                const uint32_t ApS = __shfl_sync(0xffffffffu, Ap, srcLane);
-                const uint32_t SpS = __shfl_sync(0xffffffffu, Sp, srcLane);
-                if (borrow) {
-                    Ap = ApS;
-                    Sp = SpS;
-                }
-            }
+            const uint32_t chunkE = ringBuf + (uint32_t)(rs * CELLS + cslotE) * a.chunkSlotBytes;
+            uint32_t Ap = chunkE + sE * 16;
+            uint32_t Sp = chunkE + (uint32_t)max(0, min(D, NmaxE - j0)) * KP * pStr + sE * 8;
             const int colsW = min(D, Nw - j0);  // warp-wide column count of this step
             if (uniform && colsW == D) {
                 // full step, no predicates
@@ -545,15 +558,19 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             double IS[CB];
 #pragma unroll
             for (int c = 0; c < CB; ++c) IS[c] = 0.0;
-            const uint32_t Bb = tail;
+            // B arrives folded (diagonal, then B[k][q] + B[q][k] for q > k, device_plan.h):
+            // IS = sum_k c_k (B_kk c_k + sum_{q>k} (B_kq + B_qk) c_q), K(K+1)/2 products per
+            // component instead of K^2
+            uint32_t Bb = tail;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 double u[CB];
 #pragma unroll
                 for (int c = 0; c < CB; ++c) u[c] = 0.0;
 #pragma unroll
-                for (int q = 0; q < K; ++q) {
-                    const double bq = lds64(Bb + (uint32_t)(k * K + q) * 8);
+                for (int q = k; q < K; ++q) {
+                    const double bq = lds64(Bb);
+                    Bb += 8;
 #pragma unroll
                     for (int c = 0; c < CB; ++c) u[c] = fma(bq, acc[q][c], u[c]);
                 }
@@ -572,7 +589,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                 for (int c = 0; c < CB; ++c) pw[c] *= bs[c];
 #pragma unroll
-            for (int c = 0; c < CB; ++c) g[c] = act ? (s == 0 ? a.dm : 1.0) / pw[c] : 0.0;
+            for (int c = 0; c < CB; ++c) g[c] = act ? (s == 0 ? a.dm : 1.0) * safeRcp(pw[c]) : 0.0;
         }
         // weighted sum over the stencils of the cell: butterfly over its SS lanes
         // (WENOCoeff.C:207-220; the division by gammaSum is applied per face below)
@@ -589,14 +606,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         // now acc = sum_s gamma_s c_s and g = gammaSum on every lane of the cell
 
         // phase 3: faces, one (or more) per lane
-        const uint32_t fdBase = tail + (uint32_t)(K * K) * 8;
+        const uint32_t fdBase = tail + (uint32_t)symTriSize(K) * 8;
         const uint32_t quirkA = fdBase + (uint32_t)(nFc * (K + 1)) * 8;
         // sumFlux with this cell's weighted polynomial (WENOUpwindFit.C:293-323)
         // (sum_s gamma_s c_s) / gammaSum / refFacAr is evaluated with reciprocals
         // (one division per component and one per face instead of two per value)
         double invG[CB];
 #pragma unroll
-        for (int c = 0; c < CB; ++c) invG[c] = nSt > 0 ? 1.0 / g[c] : 0.0;  // Cell::empty -> zero
+        for (int c = 0; c < CB; ++c) invG[c] = nSt > 0 ? safeRcp(g[c]) : 0.0;  // Cell::empty -> zero
         auto polyAt = [&](uint32_t basis, double refFacAr, double (&out)[CB]) {
             double S[CB];
 #pragma unroll
@@ -607,7 +624,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                 for (int c = 0; c < CB; ++c) S[c] = fma(acc[k][c], bk, S[c]);
             }
-            const double rinv = 1.0 / refFacAr;
+            const double rinv = safeRcp(refFacAr);
 #pragma unroll
             for (int c = 0; c < CB; ++c) out[c] = (S[c] * invG[c]) * rinv;
         };
@@ -687,7 +704,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                         for (int c = 0; c < CB; ++c) {
                             const double dpsi = fabs(cen[c] - psiN[c]);
-                            if (fabs(out[c]) > dpsi) out[c] = fmin(dpsi / fabs(out[c]), 1.0) * out[c];
+                            if (fabs(out[c]) > dpsi) out[c] = fmin(dpsi * safeRcp(fabs(out[c])), 1.0) * out[c];
                         }
                     }
                 }

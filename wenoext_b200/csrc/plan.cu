@@ -76,7 +76,7 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
     int32_t* Ns = reinterpret_cast<int32_t*>(rec + sizeof(RecHeader));
     int32_t* faceI = reinterpret_cast<int32_t*>(rec + lay.oFace);
     double* Bm = reinterpret_cast<double*>(rec + lay.headBytes);
-    double* faceD = Bm + K * K;
+    double* faceD = Bm + symTriSize(K);
     double* quirk = faceD + (size_t)nFc * (K + 1);
     const int D = chunkCols(K);
     unsigned char* chunks = rec + lay.headBytes + lay.tailBytes;
@@ -131,7 +131,13 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
             live++;
         }
     }
-    for (int i = lane; i < K * K; i += 32) Bm[i] = a.B[(size_t)cell * K * K + i];
+    // B folded for the quadratic form (device_plan.h): diagonal, then B[k][q] + B[q][k]
+    for (int i = lane; i < K * K; i += 32) {
+        const int k = i / K, q = i - k * K;
+        if (q < k) continue;
+        const double* Bc = a.B + (size_t)cell * K * K;
+        Bm[k * K - k * (k - 1) / 2 + (q - k)] = q == k ? Bc[i] : Bc[i] + Bc[q * K + k];
+    }
     for (int k = lane; k < K; k += 32)
         quirk[k] = cell < a.nFaces ? a.intBasTrans[((size_t)cell * 2 + 1) * a.cube + a.enumIdx[k]] : 0.0;
     int fOut = 0;
