@@ -230,6 +230,10 @@ typedef struct wenoext_setup_params {
     int32_t checkCondition;  /* default 1 */
     int32_t nThreads;        /* 0 = all */
     int32_t useClassCache;   /* 1: translation-invariant cell classes computed once */
+    int32_t gpuPinv;         /* 1: pseudo-inverses of all stencils in one batch on the GPU
+                                (wenoext_pinv_batched) instead of per stencil on the host;
+                                generic path without bestConditioned only */
+    int32_t device;          /* CUDA device of that batch */
 } wenoext_setup_params;
 
 typedef struct wenoext_setup wenoext_setup;
@@ -246,6 +250,16 @@ int wenoext_setup_set_send_halo(wenoext_setup* s, int32_t proc, const int32_t* i
 /* mesh geometry for building synthetic fields: C() [nCells][3], Sf() [nFaces][3] */
 int wenoext_setup_geometry(wenoext_setup* s, const double** cellCentres,
                            const double** faceAreaVec);
+
+/* Batched truncated pseudo-inverse on the GPU: what WENOBase::calcMatrix gets
+ * from OpenFOAM's SVD(A, minCondition) and VSinvUt() (WENOBase.C:527, :575), for nMat matrices at
+ * once (one-sided Jacobi, one warp per matrix). A_i is rows[i] x n row-major at A + start[i]
+ * (stencil cells x nDvt); Ainv_i is n x rows[i] row-major at Ainv + start[i]. nZeros[i] = number of
+ * singular values <= minCondition * max, condition[i] = max/min over the others (may be NULL),
+ * converged[i] = 0 if 60 sweeps did not suffice. Host pointers. */
+int wenoext_pinv_batched(int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
+                         const double* A, double minCondition, double* Ainv, int32_t* nZeros,
+                         double* condition, int32_t* converged, int device);
 
 /* ---------------------------------------------------------------------------
  * The reference's on-disk cache constant/WENOBase<order>/ (SURVEY.md 8f-2): the

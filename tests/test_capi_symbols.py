@@ -1,0 +1,63 @@
+"""The C-ABI library loads and exports every function include/wenoext_b200.h declares, the
+ctypes binding covers exactly that set, and without a GPU the compute entry points fail
+loudly instead of falling back to anything."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import wenoext_b200 as wx
+from wenoext_b200 import _capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    txt = open(os.path.join(ROOT, "include", "wenoext_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"^(?:int|const char\*)\s+(wenoext_\w+)\s*\(", txt, flags=re.M)))
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    names = declared_functions()
+    assert len(names) >= 29
+    raw = C.CDLL(_capi.LIB_PATH)
+    for nm in names:
+        assert hasattr(raw, nm), f"{nm} declared in the header but not exported"
+    assert sorted(_capi.SYMBOLS) == names
+    wx.lib()  # sets restype/argtypes for all of them, raises on a missing one
+
+
+def test_struct_layouts_match_the_header(tmp_path):
+    """sizeof of every public struct as gcc lays it out from the header == the ctypes mirror"""
+    import subprocess
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "wenoext_b200.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(wenoext_patch),sizeof(wenoext_plan_desc),sizeof(wenoext_plan_info),sizeof(wenoext_box_spec),'
+                   'sizeof(wenoext_setup_params),sizeof(wenoext_mesh_desc),sizeof(int));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(t) for t in (_capi.Patch, _capi.PlanDesc, _capi.PlanInfo, _capi.BoxSpec, _capi.SetupParams,
+                                  _capi.MeshDesc, C.c_int)]
+    assert got == want
+
+
+def test_no_gpu_means_loud_failure():
+    if wx.lib().wenoext_device_count() > 0:
+        pytest.skip("a GPU is present")
+    case = wx.BoxCase((4, 4, 4), 2)
+    with pytest.raises(wx.WenoextError):
+        wx.Plan(case.desc)
+    z = np.zeros(9)
+    rows = np.array([1], dtype=np.int32)
+    start = np.array([0, 9], dtype=np.int64)
+    zi = np.zeros(1, dtype=np.int32)
+    rc = wx.lib().wenoext_pinv_batched(1, 9, rows.ctypes.data_as(_capi.i32p), start.ctypes.data_as(_capi.i64p),
+                                       z.ctypes.data_as(_capi.f64p), 1e-5, z.ctypes.data_as(_capi.f64p),
+                                       zi.ctypes.data_as(_capi.i32p), None, zi.ctypes.data_as(_capi.i32p), 0)
+    assert rc != 0
+    with pytest.raises(wx.WenoextError):
+        wx.BoxCase((4, 4, 4), 2, useClassCache=False, gpuPinv=True)

@@ -54,7 +54,7 @@ class BoxCase:
     def __init__(self, n, order, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0),
                  sides=(0, 0, 0, 0, 0, 0), nProc=(1, 1, 1), myProc=0, tetSplit=0,
                  extendRatio=2.5, bestConditioned=False, maxCondition=1e-5, checkCondition=True,
-                 nThreads=0, useClassCache=True, WENODict=None):
+                 nThreads=0, useClassCache=True, WENODict=None, gpuPinv=False, device=0):
         L = lib()
         box = _capi.BoxSpec()
         box.n[:] = list(n)
@@ -64,7 +64,7 @@ class BoxCase:
         box.tetSplit = tetSplit
         box.nProc[:] = list(nProc)
         prm = _capi.SetupParams(order, extendRatio, int(bestConditioned), maxCondition,
-                                int(checkCondition), nThreads, int(useClassCache))
+                                int(checkCondition), nThreads, int(useClassCache), int(gpuPinv), device)
         h = C.c_void_p()
         check(L.wenoext_setup_box(C.byref(box), C.byref(prm), myProc, C.byref(h)))
         self._h = h

@@ -59,7 +59,7 @@ class SetupParams(C.Structure):
     _fields_ = [("polOrder", C.c_int32), ("extendRatio", C.c_double),
                 ("bestConditioned", C.c_int32), ("maxCondition", C.c_double),
                 ("checkCondition", C.c_int32), ("nThreads", C.c_int32),
-                ("useClassCache", C.c_int32)]
+                ("useClassCache", C.c_int32), ("gpuPinv", C.c_int32), ("device", C.c_int32)]
 
 
 class MeshDesc(C.Structure):
@@ -96,6 +96,8 @@ SYMBOLS = {
     "wenoext_setup_halo_request": (C.c_int, [vp, C.c_int32, C.POINTER(i32p), C.POINTER(C.c_int64)]),
     "wenoext_setup_set_send_halo": (C.c_int, [vp, C.c_int32, i32p, C.c_int64]),
     "wenoext_setup_geometry": (C.c_int, [vp, C.POINTER(f64p), C.POINTER(f64p)]),
+    "wenoext_pinv_batched": (C.c_int, [C.c_int32, C.c_int32, i32p, i64p, f64p, C.c_double, f64p, i32p, f64p,
+                                        i32p, C.c_int]),
     "wenoext_cache_write": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
     "wenoext_cache_read": (C.c_int, [C.c_char_p, C.POINTER(MeshDesc), C.c_int32, C.c_int, C.POINTER(vp)]),
     "wenoext_setup_mesh": (C.c_int, [vp, C.POINTER(MeshDesc)]),

@@ -52,6 +52,7 @@ extern "C" int wenoext_setup_box(const wenoext_box_spec* box, const wenoext_setu
         sp.maxCondition = prm->maxCondition > 0 ? prm->maxCondition : 1e-5;
         sp.checkCondition = prm->checkCondition != 0;
         sp.nThreads = prm->nThreads;
+        sp.gpuPinvDevice = prm->gpuPinv ? prm->device : -1;
         auto s = std::make_unique<wenoext_setup>();
         if (prm->useClassCache && !spec.tetSplit) {
             s->hp = buildPlanBoxFast(spec, np, myProc, sp);

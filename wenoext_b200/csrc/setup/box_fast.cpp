@@ -134,8 +134,10 @@ HostPlan buildPlanBoxFast(const BoxSpec& spec, const int32_t nProc[3], int32_t m
         sm = makeBoxMesh(ss);
         K = detail::computeNDvt(sm, prm.polOrder, dim);
         cls.assign(sm.nCells, ClassData());
+        SetupParams prmHost = prm;  // a few hundred class cells: not worth a device batch
+        prmHost.gpuPinvDevice = -1;
         parallelFor(sm.nCells, nThreads,
-                    [&](int c) { cls[c].cs = detail::computeCell(sm, c, K, dim, prm); });
+                    [&](int c) { cls[c].cs = detail::computeCell(sm, c, K, dim, prmHost); });
         // the stencils of a clipped axis must stay strictly inside the reach
         bool ok = true;
         for (int c = 0; c < sm.nCells && ok; ++c) {

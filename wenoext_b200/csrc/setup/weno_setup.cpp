@@ -13,6 +13,7 @@
 #include <cstdlib>
 
 #include "geometry_weno.h"
+#include "pinv_device.h"
 #include "svd.h"
 #include "wenobase_cache.h"
 
@@ -183,6 +184,12 @@ void calcMatrix(const PolyMesh& gm, int g, int stencilI, int nDvt, const int dim
         }
         std::copy(it->second.begin(), it->second.end(), A.begin() + (size_t)(cj - 1) * nDvt);
     }
+    if (prm.gpuPinvDevice >= 0 && !prm.bestConditioned) {
+        // deferred: the batch over all stencils of the mesh runs on the device (finishPending)
+        cs.Ainv[stencilI] = std::move(A);
+        cs.pending[stencilI] = 1;
+        return;
+    }
     SvdResult cur = svd(A, nCells, nDvt, prm.maxCondition);
     if (prm.bestConditioned) {
         bool haveBest = false;
@@ -224,6 +231,7 @@ CellSetup detail::computeCell(const PolyMesh& gm, int g, int nDvt, const int dim
     collectCentral(gm, g, nDvt, nStencils, prm.extendRatio, cs.JInv, cs.refPoint, cs.central);
     splitStencil(gm, g, nDvt, prm.extendRatio, cs);
     cs.Ainv.resize(cs.globalID.size());
+    cs.pending.assign(cs.globalID.size(), 0);
     std::map<int32_t, std::vector<double>> rowCache;
     for (size_t s = 0; s < cs.globalID.size(); ++s)
         if (cs.globalID[s][0] != CELL_DELETED) calcMatrix(gm, g, (int)s, nDvt, dim, prm, cs, rowCache);
@@ -237,6 +245,59 @@ CellSetup detail::computeCell(const PolyMesh& gm, int g, int nDvt, const int dim
 
 // matrixDB stand-in (libWENOEXT/WENOBase/matrixDB.C:75-199): tolerance-based
 // de-duplication, same key, same search window, same comparison.
+void detail::finishPending(std::vector<CellSetup>& cells, int nDvt, const SetupParams& prm) {
+    std::vector<int32_t> rows;
+    std::vector<int64_t> start(1, 0);
+    std::vector<double> A;
+    std::vector<std::pair<int32_t, int32_t>> where;
+    size_t total = 0, count = 0;
+    for (const CellSetup& cs : cells)
+        for (size_t s = 0; s < cs.pending.size(); ++s)
+            if (cs.pending[s]) total += cs.Ainv[s].size(), ++count;
+    A.reserve(total);
+    rows.reserve(count);
+    start.reserve(count + 1);
+    where.reserve(count);
+    for (size_t c = 0; c < cells.size(); ++c)
+        for (size_t s = 0; s < cells[c].pending.size(); ++s)
+            if (cells[c].pending[s]) {
+                const auto& a = cells[c].Ainv[s];
+                rows.push_back((int32_t)(a.size() / nDvt));
+                A.insert(A.end(), a.begin(), a.end());
+                start.push_back((int64_t)A.size());
+                where.push_back({(int32_t)c, (int32_t)s});
+            }
+    if (where.empty()) return;
+    const int32_t nMat = (int32_t)where.size();
+    std::vector<double> P(A.size());
+    std::vector<int32_t> nZeros(nMat), conv(nMat);
+    std::string err;
+    if (pinvBatchedDevice(prm.gpuPinvDevice, nMat, nDvt, rows.data(), start.data(), A.data(), prm.maxCondition,
+                          P.data(), nZeros.data(), nullptr, conv.data(), err))
+        throw std::runtime_error(err);
+    for (int32_t i = 0; i < nMat; ++i) {
+        CellSetup& cs = cells[where[i].first];
+        const int s = where[i].second;
+        cs.pending[s] = 0;
+        // the decisions calcMatrix takes after the SVD (WENOBase.C:527-597)
+        if (!conv[i]) throw std::runtime_error("calcMatrix: could not calculate SVD");
+        if (prm.checkCondition && s == 0 && nZeros[i] != 0) {
+            cs.globalID[s].assign(1, CELL_DELETED);
+            cs.empty = true;
+            cs.Ainv[s].clear();
+            continue;
+        }
+        cs.Ainv[s].assign(P.begin() + start[i], P.begin() + start[i + 1]);
+    }
+    // LSMatrixCheck (WENOBase.C:1327-1347)
+    for (CellSetup& cs : cells) {
+        int valid = 0;
+        for (const auto& st : cs.globalID)
+            if (st[0] != CELL_DELETED) valid++;
+        if (prm.checkCondition && valid == 0) cs.empty = true;
+    }
+}
+
 namespace {
 double maxMag(const std::vector<double>& A) {
     double m = 0;
@@ -368,7 +429,11 @@ HostPlan buildPlanGeneric(const PolyMesh& gm, const std::vector<int32_t>& cellPr
             if (!e.empty()) throw std::runtime_error(e);
     }
 
-    mark("stencils + pseudo-inverses");
+    mark(prm.gpuPinvDevice >= 0 ? "stencils + LS matrices" : "stencils + pseudo-inverses");
+    if (prm.gpuPinvDevice >= 0) {
+        detail::finishPending(cells, K, prm);
+        mark("pseudo-inverses (device batch)");
+    }
     // correctParallelRun (WENOBase.C:1030-1126): halo ids in order of first
     // appearance over the (uncut) central lists
     hp.receiveProcList.assign(nProcs, -1);
