@@ -292,6 +292,12 @@ typedef struct wenoext_mesh_desc {
  * (wenoext_setup_desc gives the plan descriptor); its geometry arrays are empty. */
 int wenoext_cache_read(const char* dir, const wenoext_mesh_desc* mesh, int32_t myProc,
                        int labelBytes, wenoext_setup** out);
+/* The same from an OpenFOAM case (or processor<N>) directory: constant/WENOBase<polOrder>/ plus
+ * the mesh addressing from constant/polyMesh/{owner, neighbour, boundary} (FoamFile header,
+ * ascii or binary; processor / cyclic / empty patches recognised, everything else is a patch
+ * with zero correction). No OpenFOAM needed. */
+int wenoext_case_read(const char* caseDir, int32_t polOrder, int32_t myProc, int labelBytes,
+                      wenoext_setup** out);
 /* Mesh addressing of a setup as a wenoext_mesh_desc (pointers valid until destroy). */
 int wenoext_setup_mesh(wenoext_setup* s, wenoext_mesh_desc* mesh);
 

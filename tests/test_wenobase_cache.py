@@ -230,3 +230,95 @@ def test_gpu_correction_from_cache_is_bitwise_equal(tmp_path, name):
         ref = Oracle("c").correction(back, scheme._scheme, True, vf, phi)
         assert H.normwise_err(got, ref) < 1e-12
     wx.WENOBase.clear()
+
+
+# ---- case directories: constant/polyMesh/{owner,neighbour,boundary} + constant/WENOBase<order> ----
+FOAM_BANNER = ("/*--------------------------------*- C++ -*----------------------------------*\\\n"
+               "| =========                 |                                                 |\n"
+               "| \\\\      /  F ield         | OpenFOAM: The Open Source CFD Toolbox           |\n"
+               "\\*---------------------------------------------------------------------------*/\n")
+SEP = "// * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * * //\n\n"
+
+
+def _foam_header(cls, obj, fmt, note=None, arch=None):
+    h = FOAM_BANNER + "FoamFile\n{\n    version     2.0;\n    format      %s;\n" % fmt
+    if arch:
+        h += '    arch        "%s";\n' % arch
+    h += "    class       %s;\n" % cls
+    if note:
+        h += '    note        "%s";\n' % note
+    h += '    location    "constant/polyMesh";\n    object      %s;\n}\n' % obj
+    return h + SEP
+
+
+def write_polymesh(case, d, binary=False, labelBytes=4, with_note=True):
+    """what blockMesh / decomposePar leave in constant/polyMesh for the addressing"""
+    os.makedirs(d, exist_ok=True)
+    note = (f"nPoints:0  nCells:{case.nCells}  nFaces:{case.nFaces}  nInternalFaces:{case.nInternalFaces}"
+            if with_note else None)
+    for name, arr in (("owner", case.owner), ("neighbour", case.neighbour)):
+        if binary:
+            arch = f"LSB;label={8 * labelBytes};scalar=64"
+            raw = arr.astype("<i4" if labelBytes == 4 else "<i8").tobytes()
+            body = _foam_header("labelList", name, "binary", note, arch).encode() + b"\n%d\n(" % arr.size + raw + b")\n"
+        else:
+            body = (_foam_header("labelList", name, "ascii", note) + "\n%d\n(\n" % arr.size +
+                    "\n".join(str(int(v)) for v in arr) + "\n)\n").encode()
+        with open(os.path.join(d, name), "wb") as f:
+            f.write(body + b"\n\n// ************************************************************************* //\n")
+    kinds = {wx.PATCH_GENERIC: "wall", wx.PATCH_EMPTY: "empty", wx.PATCH_CYCLIC: "cyclic",
+             wx.PATCH_PROCESSOR: "processor"}
+    txt = _foam_header("polyBoundaryMesh", "boundary", "ascii") + "%d\n(\n" % len(case.patches)
+    for i, (typ, start, size, nbr) in enumerate(case.patches):
+        txt += "    patch%d\n    {\n        type            %s;\n" % (i, kinds[typ])
+        if typ == wx.PATCH_GENERIC:
+            txt += "        inGroups        1(wall);\n"
+        if typ == wx.PATCH_CYCLIC:
+            txt += "        inGroups        1(cyclic);\n        matchTolerance  0.0001;\n"
+            txt += "        transform       unknown; // comment inside\n        neighbourPatch  patch%d;\n" % nbr
+        if typ == wx.PATCH_PROCESSOR:
+            txt += "        inGroups        1(processor);\n        myProcNo        %d;\n" % case.myProc
+            txt += "        neighbProcNo    %d;\n" % nbr
+        txt += "        nFaces          %d;\n        startFace       %d;\n    }\n" % (size, start)
+    txt += ")\n\n// ************************************************************************* //\n"
+    with open(os.path.join(d, "boundary"), "w") as f:
+        f.write(txt)
+
+
+@pytest.mark.parametrize("name", ["hex3d", "cavity2d", "cyclic", "tets_bestConditioned"])
+@pytest.mark.parametrize("binary,labelBytes,note", [(False, 4, True), (True, 4, False), (True, 8, True)])
+def test_case_directory(tmp_path, name, binary, labelBytes, note):
+    case = wx.BoxCase(**CASES[name])
+    root = tmp_path / "case"
+    write_polymesh(case, root / "constant" / "polyMesh", binary, labelBytes, note)
+    case.write_cache(root / "constant" / f"WENOBase{case.order}", labelBytes=labelBytes)
+    back = wx.CachedCase.from_case(root, case.order)
+    a, b = _arrays(case), _arrays(back)
+    assert back.patches == case.patches
+    for k in ("owner", "neighbour", "cfs", "css", "ses", "sid", "B", "ibt", "rfa"):
+        assert np.array_equal(a[k], b[k]), k
+    with pytest.raises(wx.WenoextError, match=f"WENOBase{case.order + 1}"):  # no cache for that order
+        wx.CachedCase.from_case(root, case.order + 1)
+
+
+def test_case_directory_two_ranks(tmp_path):
+    cases = [wx.BoxCase((8, 6, 6), 2, nProc=(2, 1, 1), myProc=r) for r in range(2)]
+    wx.exchange_halo_lists(cases)
+    for r, case in enumerate(cases):
+        root = tmp_path / f"processor{r}"
+        write_polymesh(case, root / "constant" / "polyMesh")
+        case.write_cache(root / "constant" / "WENOBase2")
+        back = wx.CachedCase.from_case(root, 2, myProc=r)
+        assert back.patches == case.patches
+        assert any(p[0] == wx.PATCH_PROCESSOR and p[3] == 1 - r for p in back.patches)
+        assert back.desc.nProcs == 2
+
+
+def test_case_directory_mismatch(tmp_path):
+    case = wx.BoxCase((4, 4, 4), 2)
+    other = wx.BoxCase((5, 4, 4), 2)
+    root = tmp_path / "case"
+    write_polymesh(other, root / "constant" / "polyMesh")
+    case.write_cache(root / "constant" / "WENOBase2")
+    with pytest.raises(wx.WenoextError, match="do not belong together"):
+        wx.CachedCase.from_case(root, 2)

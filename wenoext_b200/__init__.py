@@ -137,8 +137,16 @@ class CachedCase(BoxCase):
     another case's mesh_desc()) or as arrays."""
 
     def __init__(self, directory, mesh=None, owner=None, neighbour=None, patches=(), myProc=0,
-                 labelBytes=0, patchNbrCell=None, geometry=None, WENODict=None):
+                 labelBytes=0, patchNbrCell=None, geometry=None, WENODict=None, caseOrder=None):
         keep = []
+        if caseOrder is not None:
+            # `directory` is an OpenFOAM case (or processor<N>) directory: the cache from
+            # constant/WENOBase<order>/, the addressing from constant/polyMesh/
+            h = C.c_void_p()
+            check(lib().wenoext_case_read(str(directory).encode(), caseOrder, myProc, labelBytes,
+                                          C.byref(h)))
+            self._finish(h, myProc, WENODict, geometry)
+            return
         if mesh is None:
             owner = np.ascontiguousarray(owner, dtype=np.int32)
             neighbour = np.ascontiguousarray(neighbour, dtype=np.int32)
@@ -157,6 +165,14 @@ class CachedCase(BoxCase):
         h = C.c_void_p()
         check(lib().wenoext_cache_read(str(directory).encode(), C.byref(mesh), myProc, labelBytes,
                                        C.byref(h)))
+        self._finish(h, myProc, WENODict, geometry)
+
+    @classmethod
+    def from_case(cls, caseDir, order, myProc=0, **kw):
+        """`caseDir/constant/WENOBase<order>/` + `caseDir/constant/polyMesh/`."""
+        return cls(caseDir, caseOrder=order, myProc=myProc, **kw)
+
+    def _finish(self, h, myProc, WENODict, geometry):
         self._h = h
         self.myProc = myProc
         self.WENODict = {"p": 4.0, "dm": 1000.0, "epsilon": 1e-40}

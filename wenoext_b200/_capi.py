@@ -100,6 +100,7 @@ SYMBOLS = {
                                         i32p, C.c_int]),
     "wenoext_cache_write": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
     "wenoext_cache_read": (C.c_int, [C.c_char_p, C.POINTER(MeshDesc), C.c_int32, C.c_int, C.POINTER(vp)]),
+    "wenoext_case_read": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int, C.POINTER(vp)]),
     "wenoext_setup_mesh": (C.c_int, [vp, C.POINTER(MeshDesc)]),
 }
 

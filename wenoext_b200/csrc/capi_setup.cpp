@@ -273,3 +273,42 @@ extern "C" int wenoext_setup_mesh(wenoext_setup* s, wenoext_mesh_desc* m) {
     m->patchNbrCell = h.patchNbrCell.empty() ? nullptr : h.patchNbrCell.data();
     return 0;
 }
+
+extern "C" int wenoext_case_read(const char* caseDir, int32_t polOrder, int32_t myProc, int labelBytes,
+                                 wenoext_setup** out) {
+    if (!caseDir || !out) {
+        setError("case_read: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    *out = nullptr;
+    try {
+        auto s = std::make_unique<wenoext_setup>();
+        HostPlan& h = s->hp;
+        CacheFormat fmt;
+        fmt.labelBytes = labelBytes;
+        const std::string dir(caseDir);
+        readWenoBaseCache(dir + "/constant/WENOBase" + std::to_string(polOrder), myProc, h, fmt);
+        if (h.polOrder != polOrder)
+            throw std::runtime_error("the cache was written for order " + std::to_string(h.polOrder));
+        const int32_t nCellsCache = h.nCells, nFacesCache = h.nFaces;
+        readPolyMeshAddressing(dir + "/constant/polyMesh", h);
+        if (h.nCells != nCellsCache || h.nFaces != nFacesCache)
+            throw std::runtime_error("cache (" + std::to_string(nCellsCache) + " cells, " + std::to_string(nFacesCache) +
+                                     " faces) and polyMesh (" + std::to_string(h.nCells) + ", " +
+                                     std::to_string(h.nFaces) + ") do not belong together");
+        if (myProc < 0 || myProc >= std::max(1, h.nProcs)) throw std::runtime_error("myProc out of range");
+        h.requestHaloCellID.assign((size_t)std::max(1, h.nProcs), {});
+        if (h.nProcs <= 1) {
+            h.nProcs = 1;
+            h.sendProcList.assign(1, -1);
+            h.receiveProcList.assign(1, -1);
+            h.receiveHaloSize.assign(1, 0);
+            h.sendHaloCellIDList.assign(1, {});
+        }
+        *out = s.release();
+    } catch (const std::exception& e) {
+        setError(std::string("case_read: ") + e.what());
+        return WENOEXT_ERR_SETUP;
+    }
+    return 0;
+}

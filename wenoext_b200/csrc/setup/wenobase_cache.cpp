@@ -549,4 +549,206 @@ void readWenoBaseCache(const std::string& dir, int32_t myProc, HostPlan& hp, Cac
     }
 }
 
+
+// ------------------------------------------------- constant/polyMesh reader ----
+namespace {
+
+struct FoamIn : In {
+    using In::In;
+    void skip() {  // whitespace and C/C++ comments
+        for (;;) {
+            skipWs();
+            if (pos + 1 < n && p[pos] == '/' && p[pos + 1] == '/') {
+                while (pos < n && p[pos] != '\n') ++pos;
+            } else if (pos + 1 < n && p[pos] == '/' && p[pos + 1] == '*') {
+                pos += 2;
+                while (pos + 1 < n && !(p[pos] == '*' && p[pos + 1] == '/')) ++pos;
+                pos = std::min(n, pos + 2);
+            } else {
+                return;
+            }
+        }
+    }
+    static bool punct(unsigned char c) { return c == '{' || c == '}' || c == '(' || c == ')' || c == ';'; }
+    // next token: a punctuation character, a "quoted string" or a word
+    std::string token() {
+        skip();
+        if (pos >= n) bad("unexpected end of file");
+        if (punct(p[pos])) return std::string(1, (char)p[pos++]);
+        size_t q = pos;
+        if (p[q] == '"') {
+            ++q;
+            while (q < n && p[q] != '"') ++q;
+            q = std::min(n, q + 1);
+        } else {
+            while (q < n && !punct(p[q]) && p[q] != ' ' && p[q] != '\n' && p[q] != '\t' && p[q] != '\r') ++q;
+        }
+        std::string t((const char*)p + pos, q - pos);
+        pos = q;
+        return t;
+    }
+    char peek() {
+        skip();
+        return pos < n ? (char)p[pos] : '\0';
+    }
+    // `key value ... ;` entries of a dictionary body up to the closing brace; sub-dictionaries
+    // and lists inside values are kept as flat text
+    std::map<std::string, std::string> dictBody() {
+        std::map<std::string, std::string> d;
+        for (;;) {
+            std::string key = token();
+            if (key == "}") return d;
+            std::string val;
+            int depth = 0;
+            bool subDict = false;  // `key { ... }` ends at its brace, without a semicolon
+            for (;;) {
+                std::string t = token();
+                if (t == ";" && depth == 0) break;
+                if (t == "{" && depth == 0 && val.empty()) subDict = true;
+                if (t == "(" || t == "{") ++depth;
+                if (t == ")" || t == "}") {
+                    if (depth == 0) bad("unbalanced dictionary entry '" + key + "'");
+                    --depth;
+                }
+                if (!val.empty()) val += ' ';
+                val += t;
+                if (subDict && depth == 0) break;
+            }
+            d[key] = val;
+        }
+    }
+    std::map<std::string, std::string> foamFileHeader() {
+        if (token() != "FoamFile") bad("FoamFile header expected");
+        if (token() != "{") bad("'{' expected after FoamFile");
+        return dictBody();
+    }
+};
+
+// labelList file (owner / neighbour)
+void readFoamLabelList(const std::string& path, std::vector<int32_t>& out, std::string* note) {
+    FoamIn in(path);
+    auto hdr = in.foamFileHeader();
+    if (note) *note = hdr.count("note") ? hdr["note"] : "";
+    const bool binary = hdr.count("format") && hdr["format"] == "binary";
+    in.skip();
+    if (binary) {
+        int lb = 0;
+        if (hdr.count("arch")) {
+            const std::string& a = hdr["arch"];
+            if (a.find("label=64") != std::string::npos) lb = 8;
+            if (a.find("label=32") != std::string::npos) lb = 4;
+        }
+        const size_t save = in.pos;
+        for (int tryLb : {lb ? lb : 4, lb ? lb : 8}) {
+            try {
+                in.pos = save;
+                in.labelBytes = tryLb;
+                in.labelList(out);
+                in.skip();
+                return;
+            } catch (const std::runtime_error&) {
+                if (tryLb == (lb ? lb : 8)) throw;
+            }
+        }
+    }
+    const long long cnt = in.count();
+    out.clear();
+    if (in.peek() == '{') {  // uniform list N{v}
+        in.expect('{');
+        const long long v = in.integer();
+        in.skip();
+        in.expect('}');
+        out.assign((size_t)cnt, (int32_t)v);
+        return;
+    }
+    in.skip();
+    in.expect('(');
+    out.reserve((size_t)cnt);
+    for (long long i = 0; i < cnt; ++i) {
+        in.skip();
+        out.push_back((int32_t)in.integer());
+    }
+    in.skip();
+    in.expect(')');
+}
+
+}  // namespace
+
+void readPolyMeshAddressing(const std::string& dir, HostPlan& hp) {
+    std::string note;
+    readFoamLabelList(dir + "/owner", hp.owner, &note);
+    readFoamLabelList(dir + "/neighbour", hp.neighbour, nullptr);
+    hp.nFaces = (int32_t)hp.owner.size();
+    hp.nInternalFaces = (int32_t)hp.neighbour.size();
+    if (hp.nInternalFaces > hp.nFaces) fail("polyMesh: more neighbours than faces");
+    // nCells: from the header note OpenFOAM writes ("nPoints:.. nCells:.. nFaces:.."), else max + 1
+    int32_t nCells = -1;
+    const size_t at = note.find("nCells:");
+    if (at != std::string::npos) nCells = (int32_t)atol(note.c_str() + at + 7);
+    int32_t mx = -1;
+    for (int32_t c : hp.owner) mx = std::max(mx, c);
+    for (int32_t c : hp.neighbour) mx = std::max(mx, c);
+    if (nCells < 0) nCells = mx + 1;
+    if (mx >= nCells) fail("polyMesh: owner/neighbour refer to cells beyond nCells");
+    for (int32_t c : hp.owner)
+        if (c < 0) fail("polyMesh: negative owner");
+    hp.nCells = nCells;
+    // mesh.cells() as primitiveMesh::calcCells builds it: owned faces, then neighboured ones
+    hp.cellFaceStart.assign((size_t)nCells + 1, 0);
+    for (int f = 0; f < hp.nFaces; ++f) ++hp.cellFaceStart[hp.owner[f] + 1];
+    for (int f = 0; f < hp.nInternalFaces; ++f) ++hp.cellFaceStart[hp.neighbour[f] + 1];
+    for (int c = 0; c < nCells; ++c) hp.cellFaceStart[c + 1] += hp.cellFaceStart[c];
+    hp.cellFaces.assign((size_t)hp.cellFaceStart[nCells], 0);
+    {
+        std::vector<int32_t> fill(hp.cellFaceStart.begin(), hp.cellFaceStart.end() - 1);
+        for (int f = 0; f < hp.nFaces; ++f) hp.cellFaces[fill[hp.owner[f]]++] = f;
+        for (int f = 0; f < hp.nInternalFaces; ++f) hp.cellFaces[fill[hp.neighbour[f]]++] = f;
+    }
+    // boundary: N ( name { ... } ... )
+    FoamIn in(dir + "/boundary");
+    in.foamFileHeader();
+    in.skip();
+    const long long nP = in.count();
+    in.skip();
+    in.expect('(');
+    hp.patches.clear();
+    std::vector<std::string> nbrName;
+    for (long long i = 0; i < nP; ++i) {
+        Patch pt;
+        pt.name = in.token();
+        if (in.token() != "{") in.bad("'{' expected after patch name " + pt.name);
+        auto d = in.dictBody();
+        if (!d.count("nFaces") || !d.count("startFace")) in.bad("patch " + pt.name + " lacks nFaces/startFace");
+        pt.size = (int32_t)atol(d["nFaces"].c_str());
+        pt.start = (int32_t)atol(d["startFace"].c_str());
+        const std::string type = d.count("type") ? d["type"] : "patch";
+        std::string nb;
+        if (type == "processor" || type == "processorCyclic") {
+            pt.type = PATCH_PROCESSOR;
+            if (!d.count("neighbProcNo")) in.bad("processor patch " + pt.name + " lacks neighbProcNo");
+            pt.nbr = (int32_t)atol(d["neighbProcNo"].c_str());
+        } else if (type == "cyclic") {
+            pt.type = PATCH_CYCLIC;
+            if (!d.count("neighbourPatch")) in.bad("cyclic patch " + pt.name + " lacks neighbourPatch");
+            nb = d["neighbourPatch"];
+        } else if (type == "empty") {
+            pt.type = PATCH_EMPTY;
+        } else {
+            pt.type = PATCH_GENERIC;
+        }
+        if (pt.size < 0 || pt.start < hp.nInternalFaces || pt.start + pt.size > hp.nFaces)
+            in.bad("patch " + pt.name + " lies outside the boundary faces");
+        hp.patches.push_back(pt);
+        nbrName.push_back(nb);
+    }
+    in.skip();
+    in.expect(')');
+    for (size_t i = 0; i < hp.patches.size(); ++i) {
+        if (hp.patches[i].type != PATCH_CYCLIC) continue;
+        for (size_t j = 0; j < hp.patches.size(); ++j)
+            if (hp.patches[j].name == nbrName[i]) hp.patches[i].nbr = (int32_t)j;
+        if (hp.patches[i].nbr < 0) fail("polyMesh: cyclic patch " + hp.patches[i].name + " has no partner " + nbrName[i]);
+    }
+}
+
 }  // namespace wenoext

@@ -46,6 +46,16 @@ void writeWenoBaseCache(const HostPlan& hp, const std::string& dir, const CacheF
 // On return fmt holds the label size found and the row padding of the first matrix.
 void readWenoBaseCache(const std::string& dir, int32_t myProc, HostPlan& hp, CacheFormat& fmt);
 
+// constant/polyMesh/{owner, neighbour, boundary} of an OpenFOAM case (or processor) directory:
+// the mesh addressing the cache does not hold. FoamFile header, `format ascii` or `binary`
+// (label size from the header's `arch` entry, else detected); `boundary` is a list of
+// dictionaries with type / nFaces / startFace (+ neighbProcNo, neighbourPatch). Patch types
+// map to the kinds the hot path distinguishes (WENOUpwindFit.C:433, :478, :493): processor
+// and processorCyclic -> PATCH_PROCESSOR, cyclic -> PATCH_CYCLIC, empty -> PATCH_EMPTY, anything
+// else (wall, patch, symmetry, cyclicAMI ...) -> PATCH_GENERIC (zero correction, as the
+// reference leaves them).
+void readPolyMeshAddressing(const std::string& polyMeshDir, HostPlan& hp);
+
 // matrixDB::hashMatrix (matrixDB.C:171-199), shared with the setup's MatrixPool.
 int32_t matrixKey(const double* A, size_t n);
 
