@@ -130,4 +130,47 @@ wenoext_plan* makePlan(const fvMesh& mesh, const WENOBase& wb, label polOrder, i
         FatalErrorInFunction << "wenoext_b200: " << wenoext_last_error() << exit(FatalError);
     return plan;
 }
+
+// Second way to the same plan: parse the cache the stock library wrote to
+// constant/WENOBase<order>/ (WENOBase::writeList, WENOBase.C:1265-1312) instead of walking the
+// accessors; only the mesh addressing comes from the fvMesh. See INTEGRATION.md section 4.
+wenoext_plan* planFromCache(const fvMesh& mesh, const label polOrder, const int device)
+{
+    std::vector<wenoext_patch> patches;
+    forAll(mesh.boundary(), patchI)
+    {
+        const fvPatch& p = mesh.boundary()[patchI];
+        wenoext_patch q{WENOEXT_PATCH_GENERIC, int32_t(p.start()), int32_t(p.size()), -1};
+        if (isA<processorFvPatch>(p))
+        {
+            q.type = WENOEXT_PATCH_PROCESSOR;
+            q.nbr = refCast<const processorFvPatch>(p).neighbProcNo();
+        }
+        else if (isA<cyclicFvPatch>(p))
+        {
+            q.type = WENOEXT_PATCH_CYCLIC;
+            q.nbr = refCast<const cyclicFvPatch>(p).neighbPatchID();
+        }
+        else if (isA<emptyFvPatch>(p)) q.type = WENOEXT_PATCH_EMPTY;
+        patches.push_back(q);
+    }
+    // labels are 32-bit here (WM_LABEL_SIZE=32); with 64-bit labels copy owner/neighbour to int32 first
+    wenoext_mesh_desc m{};
+    m.nCells = mesh.nCells(); m.nFaces = mesh.nFaces(); m.nInternalFaces = mesh.nInternalFaces();
+    m.owner = mesh.owner().cdata(); m.neighbour = mesh.neighbour().cdata();
+    m.nPatches = patches.size(); m.patches = patches.data();
+
+    const fileName dir = mesh.time().path()/"constant"/("WENOBase" + Foam::name(polOrder));
+    wenoext_setup* s = nullptr;
+    if (wenoext_cache_read(dir.c_str(), &m, Pstream::myProcNo(), 0, &s) != WENOEXT_OK)
+        FatalErrorInFunction << "wenoext_b200: " << wenoext_last_error() << exit(FatalError);
+    wenoext_plan_desc d;
+    wenoext_setup_desc(s, &d);
+    wenoext_plan* plan = nullptr;
+    const int rc = wenoext_plan_create(&d, device, &plan);
+    wenoext_setup_destroy(s);
+    if (rc != WENOEXT_OK)
+        FatalErrorInFunction << "wenoext_b200: " << wenoext_last_error() << exit(FatalError);
+    return plan;
+}
 }}
