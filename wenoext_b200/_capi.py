@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwenoext_b200.so")
+# WENOEXT_LIB: developer aid, an alternative build of the same library (kernel variants)
+LIB_PATH = os.environ.get("WENOEXT_LIB") or os.path.join(_HERE, "libwenoext_b200.so")
 
 # constants of include/wenoext_b200.h
 CELL_LOCAL, CELL_DELETED, CELL_EMPTY = -1, -4, -10

@@ -57,6 +57,7 @@ def build_product(force=False, verbose=False):
     kdebug = bool(os.environ.get("WENOEXT_KDEBUG"))
     if kdebug:  # developer aid: device-side bounds checks
         common.append("-DWENOEXT_KDEBUG")
+    common += os.environ.get("WENOEXT_CFLAGS", "").split()  # developer aid: kernel variants
     stamp = os.path.join(objdir, "kdebug.stamp")
     if kdebug != os.path.exists(stamp):
         force = True

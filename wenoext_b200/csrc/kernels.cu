@@ -153,11 +153,17 @@ __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&
     if constexpr (CB == 1) {
         asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v[0]) : "l"(p), "l"(pol));
     } else {
+        if constexpr (CB == 3) {
+            // a 3-vector sits in a 32-byte slot (VS = 4): one 256-bit load, the pad is dropped
+            double pad;
+            asm volatile("ld.global.nc.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;"
+                         : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(pad)
+                         : "l"(p), "l"(pol));
+            return;
+        }
         asm volatile("ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
                      : "=d"(v[0]), "=d"(v[1])
                      : "l"(p), "l"(pol));
-        if constexpr (CB == 3)
-            asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v[2]) : "l"(p + 2), "l"(pol));
     }
 }
 
