@@ -493,15 +493,27 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     // Slabs for the pipelined host-buffer path (serial plans): what a prefix of the cells
     // reads (cell values, fluxes) and which faces are final once it has been processed.
     if (!rc && P->nProcs == 1) {
-        int S = 8;
+        int S = 12;
         if (const char* e = getenv("WENOEXT_E2E_SLABS")) S = std::max(1, atoi(e));
         if (nC < S * 8192) S = 1;
         if (S > 1) {
             std::vector<int32_t> ext((size_t)nC * 3);
             cudaMemcpy(ext.data(), dCellExt, ext.size() * sizeof(int32_t), cudaMemcpyDeviceToHost);
-            const int per = ((nC + S - 1) / S + 31) / 32 * 32;
+            // Tapered slabs: what cannot overlap is the H2D copy in front of the first slab and
+            // the D2H copy behind the last one, so those two are small (weights 1, 2, 4, 8 ... 8,
+            // 4, 2, 1); WENOEXT_E2E_TAPER=0: equal slabs
+            std::vector<double> wgt(S, 8.0);
+            const char* tp = getenv("WENOEXT_E2E_TAPER");
+            if (S >= 6 && !(tp && atoi(tp) == 0))
+                for (int k = 0; k < 3; ++k) wgt[k] = wgt[S - 1 - k] = (double)(1 << k);
+            double tot = 0, run = 0;
+            for (double w : wgt) tot += w;
             P->slabEnd.clear();
-            for (int k = 0; k < S; ++k) P->slabEnd.push_back(std::min(nC, (k + 1) * per));
+            for (int k = 0; k < S; ++k) {
+                run += wgt[k];
+                const int64_t e = (int64_t)((double)nC * run / tot);
+                P->slabEnd.push_back(k == S - 1 ? nC : (int32_t)std::min<int64_t>(nC, (e + 31) / 32 * 32));
+            }
             while (P->slabEnd.size() > 1 && P->slabEnd[P->slabEnd.size() - 2] >= nC) P->slabEnd.pop_back();
             S = (int)P->slabEnd.size();
             P->needVf.assign(S, 0);
