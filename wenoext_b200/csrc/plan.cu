@@ -614,6 +614,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     }
     if (P->commStream) cudaStreamDestroy(P->commStream);
     if (P->sIn) cudaStreamDestroy(P->sIn);
+    if (P->sAlt) cudaStreamDestroy(P->sAlt);
     if (P->sOut) cudaStreamDestroy(P->sOut);
     for (cudaEvent_t e : P->evSlab) cudaEventDestroy(e);
     cudaEvent_t evs[] = {P->evA, P->evB, P->evC};
@@ -931,17 +932,23 @@ static int ensureBuf(double** p, size_t* cap, size_t n) {
 
 // gateItem >= 0: work items from gateItem on are boundary cells behind the halo gate
 // (device_plan.h); followUp: second launch of such a pair, counters kept, gate known open
+// `st`/`counterSlot`: launches of one call that may overlap (slabs on alternating streams) use
+// their own stream and their own pair of tile counters
 static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase = 0,
-                       int gateItem = -1, bool followUp = false) {
+                       int gateItem = -1, bool followUp = false, cudaStream_t st = nullptr,
+                       int counterSlot = 0) {
     if (nWork <= 0) return 0;
-    const wenoext_call& c = P->call;
+    wenoext_call c = P->call;
+    if (st) c.st = st;
     CellKernelArgs a{};
     a.records = P->records;
     a.recInfo = P->recInfo;
     a.cellList = list;
-    if (!P->tileCounter) CUDA_TRY(cudaMalloc((void**)&P->tileCounter, 2 * sizeof(int32_t)));
-    if (!followUp) CUDA_TRY(cudaMemsetAsync(P->tileCounter, 0, 2 * sizeof(int32_t), c.st));
-    a.tileCounter = P->tileCounter;
+    constexpr int kCounterSlots = 64;
+    if (!P->tileCounter) CUDA_TRY(cudaMalloc((void**)&P->tileCounter, kCounterSlots * 2 * sizeof(int32_t)));
+    int32_t* counter = P->tileCounter + 2 * (counterSlot % kCounterSlots);
+    if (!followUp) CUDA_TRY(cudaMemsetAsync(counter, 0, 2 * sizeof(int32_t), c.st));
+    a.tileCounter = counter;
     a.workBase = workBase;
     a.nWork = nWork;
     a.gateItem = gateItem;
@@ -1351,6 +1358,7 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         CUDA_TRY(cudaStreamCreateWithFlags(&P->sIn, cudaStreamNonBlocking));
         CUDA_TRY(cudaStreamCreateWithFlags(&P->sOut, cudaStreamNonBlocking));
     }
+    if (!P->sAlt) CUDA_TRY(cudaStreamCreateWithFlags(&P->sAlt, cudaStreamNonBlocking));
     while ((int)P->evSlab.size() < 2 * S + 2) {
         cudaEvent_t e;
         CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1361,6 +1369,7 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
     CUDA_TRY(cudaEventRecord(evStart, c.st));
     CUDA_TRY(cudaStreamWaitEvent(P->sIn, evStart, 0));
     CUDA_TRY(cudaStreamWaitEvent(P->sOut, evStart, 0));
+    CUDA_TRY(cudaStreamWaitEvent(P->sAlt, evStart, 0));
     double* dvf = const_cast<double*>(c.vf);
     double* dflux = const_cast<double*>(c.flux);
     if (pnf && P->nBnd)
@@ -1375,21 +1384,32 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         if (nf > haveFlux)
             CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
                                      cudaMemcpyHostToDevice, P->sIn));
-        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sIn));
-        CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * k], 0));
+        // the pack follows its copy on the input stream, so that a slab's kernel depends on
+        // one event only
         if (nv > haveVf) {
             launchPackValues(c.vf + (size_t)haveVf * nComp, nv - haveVf, nComp, c.c0, c.CB, c.VS,
-                             P->vals + (size_t)haveVf * c.VS, c.st);
+                             P->vals + (size_t)haveVf * c.VS, P->sIn);
             P->lastLaunches++;
         }
+        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sIn));
+        // slabs alternate between two streams: the CTAs of slab k+1 move onto the SMs as those
+        // of slab k run out of tiles, instead of waiting for the whole grid to drain (slabs
+        // write disjoint faces and only read the inputs)
+        cudaStream_t ks = (k & 1) ? P->sAlt : c.st;
+        CUDA_TRY(cudaStreamWaitEvent(ks, P->evSlab[2 * k], 0));
         haveVf = std::max(haveVf, nv);
         haveFlux = nf;
-        if (int rc = launchCells(P, nullptr, P->slabEnd[k] - cell0, cell0)) return rc;
+        if (int rc = launchCells(P, nullptr, P->slabEnd[k] - cell0, cell0, -1, false, ks, k)) return rc;
         cell0 = P->slabEnd[k];
-        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], c.st));
+        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], ks));
+        // (the output stream waits for every slab in order: doneFaces[k] counts on slabs <= k)
+        CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
+        if (k == S - 1 && S > 1) {  // join: what follows on the caller's stream needs all slabs
+            CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * k + 1], 0));
+            CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * (k - 1) + 1], 0));
+        }
         const int done = k == S - 1 ? sent : P->doneFaces[k];  // the rest follows the patch kernel
         if (done > sent) {
-            CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
             CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
                                      (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
             if (fv)

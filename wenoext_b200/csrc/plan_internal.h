@@ -122,6 +122,7 @@ struct wenoext_plan {
     double* h_fix = nullptr;  // pinned
     size_t h_fixCap = 0;
     cudaStream_t sIn = nullptr, sOut = nullptr;
+    cudaStream_t sAlt = nullptr;  // every second slab's kernel (overlaps the drain of the one before)
     std::vector<cudaEvent_t> evSlab;  // [2 * slabs]: inputs arrived, slab computed
     // WENODict factors
     double p = 4.0, dm = 1000.0, eps = 1e-40;
