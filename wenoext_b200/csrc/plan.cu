@@ -493,9 +493,13 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     // Slabs for the pipelined host-buffer path (serial plans): what a prefix of the cells
     // reads (cell values, fluxes) and which faces are final once it has been processed.
     if (!rc && P->nProcs == 1) {
-        int S = 12;
+        int S = 32;
         if (const char* e = getenv("WENOEXT_E2E_SLABS")) S = std::max(1, atoi(e));
-        if (nC < S * 8192) S = 1;
+        S = std::min(S, 64);  // (tile counter slots of overlapping launches)
+        if (!getenv("WENOEXT_E2E_SLABS"))
+            while (S > 1 && nC < S * 32768) S /= 2;  // a slab should be worth its launch
+        else if (nC < S * 8192)
+            S = 1;
         if (S > 1) {
             std::vector<int32_t> ext((size_t)nC * 3);
             cudaMemcpy(ext.data(), dCellExt, ext.size() * sizeof(int32_t), cudaMemcpyDeviceToHost);
