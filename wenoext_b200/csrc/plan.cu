@@ -554,6 +554,22 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
             for (int k = 0; k < S; ++k) P->slabEnd.push_back(std::min(nI, (k + 1) * per));
             while (P->slabEnd.size() > 1 && P->slabEnd[P->slabEnd.size() - 2] >= nI) P->slabEnd.pop_back();
             S = (int)P->slabEnd.size();
+            // what the items of slabs <= k read (cell values, fluxes): inputs can then arrive
+            // slab by slab as in the serial path
+            P->needVf.assign(S, 0);
+            P->needFlux.assign(S, 0);
+            {
+                int jj = 0, mv = 0, mf = 0;
+                for (int k = 0; k < S; ++k) {
+                    for (; jj < P->slabEnd[k]; ++jj) {
+                        const int cc = li[jj];
+                        mv = std::max(mv, std::max(ext[(size_t)cc * 3], cc) + 1);
+                        mf = std::max(mf, ext[(size_t)cc * 3 + 2] + 1);
+                    }
+                    P->needVf[k] = std::min(nC, mv);
+                    P->needFlux[k] = mf;
+                }
+            }
             P->doneFaces.assign(S, 0);
             int lo = P->nInt, j = nI;
             for (int k = S - 1; k >= 0; --k) {
@@ -1073,6 +1089,28 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
     return 0;
 }
 
+// exchange #1 as a one-sided push of this step's halo values into the receivers' buffers
+static void pushHalo(wenoext_plan* P, cudaStream_t st) {
+    if (P->pushPeers.empty()) return;
+    const wenoext_call& c = P->call;
+    HaloPushArgs a{};
+    a.nPeers = (int32_t)P->pushPeers.size();
+    a.VS = c.VS;
+    a.epoch = P->haloEpoch;
+    a.vals = P->vals;
+    a.sendIds = P->sendIds;
+    a.done = P->pushDone;
+    for (int i = 0; i < a.nPeers; ++i) {
+        const auto& pp = P->pushPeers[i];
+        a.src0[i] = P->sendOff[pp.proc];
+        a.off[i + 1] = a.off[i] + (P->sendOff[pp.proc + 1] - P->sendOff[pp.proc]);
+        a.dst[i] = pp.vals[P->haloEpoch & 1] + pp.haloBase * c.VS;
+        a.flag[i] = pp.flags + pp.slot;
+    }
+    launchHaloPush(a, st);
+    P->lastLaunches++;
+}
+
 static int phase0(wenoext_plan* P, bool launchInterior = true) {
     const wenoext_call& c = P->call;
     const bool parallel = P->nProcs > 1;
@@ -1088,24 +1126,7 @@ static int phase0(wenoext_plan* P, bool launchInterior = true) {
     if (!parallel) return 0;
     P->mergedLaunch = false;
     if (P->p2p) {
-        if (!P->pushPeers.empty()) {
-            HaloPushArgs a{};
-            a.nPeers = (int32_t)P->pushPeers.size();
-            a.VS = c.VS;
-            a.epoch = P->haloEpoch;
-            a.vals = P->vals;
-            a.sendIds = P->sendIds;
-            a.done = P->pushDone;
-            for (int i = 0; i < a.nPeers; ++i) {
-                const auto& pp = P->pushPeers[i];
-                a.src0[i] = P->sendOff[pp.proc];
-                a.off[i + 1] = a.off[i] + (P->sendOff[pp.proc + 1] - P->sendOff[pp.proc]);
-                a.dst[i] = pp.vals[P->haloEpoch & 1] + pp.haloBase * c.VS;
-                a.flag[i] = pp.flags + pp.slot;
-            }
-            launchHaloPush(a, c.st);
-            P->lastLaunches++;
-        }
+        pushHalo(P, c.st);
         if (!launchInterior) return 0;
         // One launch for interior and boundary cells when the halo region of `vals` starts on
         // a 32-byte sector (the gathers use the non-coherent path: no sector that an interior
@@ -1469,6 +1490,79 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
     CUDA_TRY(cudaEventRecord(evStart, c.st));
     CUDA_TRY(cudaStreamWaitEvent(P->sIn, evStart, 0));
     CUDA_TRY(cudaStreamWaitEvent(P->sOut, evStart, 0));
+    if (P->p2p && (int)P->needVf.size() == S && !getenv("WENOEXT_E2E_UPFRONT")) {
+        // With the one-sided halo push nothing on this rank waits for a rendezvous, so the
+        // inputs can arrive slab by slab as in the serial path: copy + pack on the input stream,
+        // the slab kernels on two alternating streams, and the push right behind the piece
+        // that completes the cell values (the peers need it only for their boundary cells).
+        if (!P->sAlt) CUDA_TRY(cudaStreamCreateWithFlags(&P->sAlt, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamWaitEvent(P->sAlt, evStart, 0));
+        ++P->haloEpoch;
+        P->vals = P->valsIpc[P->haloEpoch & 1];
+        P->mergedLaunch = false;
+        double* dvf = const_cast<double*>(c.vf);
+        double* dflux = const_cast<double*>(c.flux);
+        if (pnf && P->nBnd)
+            CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.pnf), pnf, (size_t)P->nBnd * nComp * 8,
+                                     cudaMemcpyHostToDevice, P->sIn));
+        int haveVf = 0, haveFlux = 0, sent = 0, item0 = 0;
+        bool pushed = false;
+        for (int k = 0; k < S; ++k) {
+            const int nv = k == S - 1 ? P->nCells : P->needVf[k];
+            const int nf = k == S - 1 ? P->nFaces : std::max(haveFlux, (int)P->needFlux[k]);
+            if (nv > haveVf) {
+                CUDA_TRY(cudaMemcpyAsync(dvf + (size_t)haveVf * nComp, vf + (size_t)haveVf * nComp,
+                                         (size_t)(nv - haveVf) * nComp * 8, cudaMemcpyHostToDevice, P->sIn));
+                launchPackValues(c.vf + (size_t)haveVf * nComp, nv - haveVf, nComp, c.c0, c.CB, c.VS,
+                                 P->vals + (size_t)haveVf * c.VS, P->sIn);
+                P->lastLaunches++;
+                haveVf = nv;
+            }
+            if (!pushed && haveVf == P->nCells) {
+                pushHalo(P, P->sIn);
+                pushed = true;
+            }
+            if (nf > haveFlux)
+                CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
+                                         cudaMemcpyHostToDevice, P->sIn));
+            haveFlux = nf;
+            CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sIn));
+            cudaStream_t ks = (k & 1) ? P->sAlt : c.st;
+            CUDA_TRY(cudaStreamWaitEvent(ks, P->evSlab[2 * k], 0));
+            if (int rc = launchCells(P, P->cellListInterior, P->slabEnd[k] - item0, item0, -1, false, ks, k))
+                return rc;
+            item0 = P->slabEnd[k];
+            CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], ks));
+            CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
+            if (k == S - 1) {  // join
+                CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * k + 1], 0));
+                if (S > 1) CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * (k - 1) + 1], 0));
+            }
+            const int done = P->doneFaces[k];
+            if (k < S - 1 && done > sent) {
+                CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                                         (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+                sent = done;
+            }
+        }
+        if (int rc = phase1(P)) return rc;  // halo wait, boundary cells, exchange #2
+        if (int rc = phase2(P)) return rc;  // coupled patches
+        launchGatherRows(c.corr, P->fixFacesD, (int64_t)nFix, nComp, P->d_fix, c.st);
+        if (nFix) P->lastLaunches++;
+        CUDA_TRY(cudaEventRecord(evEnd, c.st));
+        CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
+        if (nFix)
+            CUDA_TRY(cudaMemcpyAsync(P->h_fix, P->d_fix, nFix * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+        CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                                 (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+        CUDA_TRY(cudaStreamSynchronize(P->sOut));
+        CUDA_TRY(cudaStreamSynchronize(c.st));
+        for (size_t i = 0; i < nFix; ++i) {
+            const size_t f = (size_t)P->fixFacesH[i];
+            for (int k = 0; k < nComp; ++k) corr[f * nComp + k] = P->h_fix[i * nComp + k];
+        }
+        return 0;
+    }
     CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.vf), vf, (size_t)P->nCells * nComp * 8,
                              cudaMemcpyHostToDevice, P->sIn));
     CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.flux), flux, (size_t)P->nFaces * 8,
