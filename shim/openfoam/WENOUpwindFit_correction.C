@@ -1,10 +1,10 @@
-// Replacement body of WENOUpwindFit<Type>::correction (libWENOEXT/WENOUpwindFit/WENOUpwindFit.C:212-290)
-// calling the C ABI of libwenoext_b200.so. SOURCE ONLY (needs OpenFOAM). WENOUpwindFit01 is the
-// same with WENOEXT_SCHEME_UPWINDFIT01 and bounded = 1. See INTEGRATION.md.
-// in WENOUpwindFit.C, replacing the body at :212-290
-template<class Type>
+// correction() of the drop-in scheme classes (WENOUpwindFitB200.H): what replaces the body of
+// WENOUpwindFit<Type>::correction (libWENOEXT/WENOUpwindFit/WENOUpwindFit.C:212-290) and of
+// WENOUpwindFit01<Type>::correction (libWENOEXT/WENOUpwindFit01/WENOUpwindFit01.C:215-292) by one call
+// into libwenoext_b200.so. SOURCE ONLY (needs OpenFOAM). See INTEGRATION.md.
+template<class Type, bool Scheme01>
 Foam::tmp<Foam::GeometricField<Type, Foam::fvsPatchField, Foam::surfaceMesh>>
-Foam::WENOUpwindFit<Type>::correction
+Foam::WENOUpwindFitB200Base<Type, Scheme01>::correction
 (
     const GeometricField<Type, fvPatchField, volMesh>& vf
 ) const
@@ -35,7 +35,7 @@ Foam::WENOUpwindFit<Type>::correction
     }
     const int rc = wenoext_correction
     (
-        plan, WENOEXT_SCHEME_UPWINDFIT, int(limFac_), nComp,
+        plan, Scheme01 ? WENOEXT_SCHEME_UPWINDFIT01 : WENOEXT_SCHEME_UPWINDFIT, int(limFac_), nComp,
         reinterpret_cast<const double*>(vf.primitiveField().cdata()),    // Type[nCells] is AoS fp64 (-DWM_DP)
         flux.data(), limFac_ ? pnf.data() : nullptr, corr.data(), WENOEXT_MEM_HOST, nullptr
     );

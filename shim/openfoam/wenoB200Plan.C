@@ -22,7 +22,7 @@ struct Flat   // owns the temporaries the descriptor points to
     wenoext_plan_desc d{};
 };
 
-wenoext_plan* makePlan(const fvMesh& mesh, const WENOBase& wb, label polOrder, int device)
+wenoext_plan* planFromBase(const fvMesh& mesh, const WENOBase& wb, const label polOrder, const int device)
 {
     Flat f;
     const label nCells = mesh.nCells(), nFaces = mesh.nFaces(), nInt = mesh.nInternalFaces();
