@@ -27,6 +27,7 @@
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <stdint.h>
 
 #include "device_plan.h"
@@ -987,8 +988,10 @@ void launchHaloPush(const HaloPushArgs& a, cudaStream_t st) {
 
 // Host-side stream order behind the halo: one lane per sending rank waits for its flag.
 // Nothing this GPU still has to do is needed for the flags to rise (the senders push on
-// their own), so the wait cannot deadlock; it traps instead of hanging if a peer died.
-__global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch) {
+// their own), so the wait cannot deadlock. A sender may legitimately be late (a rank writing
+// results, say), so the patience is long: timeoutNs (WENOEXT_HALO_TIMEOUT_S, default 600 s;
+// 0 = wait for ever, like a blocking receive) before the launch fails instead of hanging.
+__global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch, long long timeoutNs) {
     if ((int)threadIdx.x >= n) return;
     long long t0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -996,11 +999,15 @@ __global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch) {
         __nanosleep(200);
         long long t1;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (t1 - t0 > 20000000000ll) __trap();
+        if (timeoutNs > 0 && t1 - t0 > timeoutNs) __trap();
     }
 }
 void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st) {
-    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch);
+    static const long long timeoutNs = [] {
+        const char* e = getenv("WENOEXT_HALO_TIMEOUT_S");
+        return (long long)((e ? atof(e) : 600.0) * 1e9);
+    }();
+    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch, timeoutNs);
 }
 
 void launchPackHalo(const double* vals, int VS, const int32_t* sendIds, int64_t nSend,
