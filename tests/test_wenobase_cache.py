@@ -322,3 +322,23 @@ def test_case_directory_mismatch(tmp_path):
     case.write_cache(root / "constant" / "WENOBase2")
     with pytest.raises(wx.WenoextError, match="do not belong together"):
         wx.CachedCase.from_case(root, 2)
+
+
+def test_polymesh_compact_and_commented_forms(tmp_path):
+    """ASCII lists on one line, a uniform list `N{v}`, comments between tokens and a
+    sub-dictionary inside a patch entry: all legal OpenFOAM, all must parse."""
+    case = wx.BoxCase((2, 1, 1), 2, useClassCache=False)  # 2 cells, 1 internal face, 10 boundary faces
+    root = tmp_path / "case"
+    pm = root / "constant" / "polyMesh"
+    write_polymesh(case, pm)
+    hdr = _foam_header("labelList", "owner", "ascii")
+    own = " ".join(str(int(v)) for v in case.owner)
+    (pm / "owner").write_text(hdr + f"{case.nFaces} // count\n( {own} ) /* done */\n")
+    (pm / "neighbour").write_text(_foam_header("labelList", "neighbour", "ascii") + "1{1}\n")
+    b = (pm / "boundary").read_text()
+    b = b.replace("        type            wall;", "        type            wall;\n        extra { a 1; b (1 2 3); }", 1)
+    (pm / "boundary").write_text(b)
+    case.write_cache(root / "constant" / "WENOBase2")
+    back = wx.CachedCase.from_case(root, 2)
+    assert np.array_equal(back.owner, case.owner) and np.array_equal(back.neighbour, case.neighbour)
+    assert back.patches == case.patches

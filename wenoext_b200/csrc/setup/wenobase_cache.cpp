@@ -477,7 +477,7 @@ void readWenoBaseCache(const std::string& dir, int32_t myProc, HostPlan& hp, Cac
         }
         in.end();
     }
-    const int K = hp.nDvt;
+    int K = hp.nDvt;  // 0 if the mesh has no live stencil at all: taken from B below
     // a live stencil's matrix has one column per entry after the cell itself (WENOBase.C:976-979)
     for (int64_t s = 0; s < nStencils; ++s) {
         const int64_t e0 = hp.stencilEntryStart[s], e1 = hp.stencilEntryStart[s + 1];
@@ -498,6 +498,10 @@ void readWenoBaseCache(const std::string& dir, int32_t myProc, HostPlan& hp, Cac
         for (int c = 0; c < hp.nCells; ++c) {
             const size_t before = hp.B.size();
             in.blazeRowMajor(hp.B, rows, cols, spacing);
+            if (K == 0 && rows > 0 && rows == cols) {
+                K = hp.nDvt = rows;
+                hp.B.insert(hp.B.begin(), (size_t)c * K * K, 0.0);  // default-constructed ones before it
+            }
             if (rows == 0 && cols == 0) {  // cells the setup skipped keep a default-constructed matrix
                 hp.B.resize(before + (size_t)K * K, 0.0);
             } else if (rows != K || cols != K) {
