@@ -137,6 +137,13 @@ struct CellKernelArgs {
     // halo_push_kernel once exchange #1 has landed in `vals`) and stops otherwise; a
     // follow-up launch with the same counters and nGate == 0 takes what is left.
     // gateItem < 0: one range, no gate.
+    // 2-D bulk copies (plan.cu: buildTmaMaps): CUtensorMap[2 + chunks] in global memory or
+    // nullptr; part p (0 head, 1 tail, 2 + ch chunk step ch) of the layout (tmaZ, tmaW) has
+    // tmaBytes[p] bytes per cell and starts tmaElemOff[p] 8-byte elements into the record
+    const void* tmaMaps;
+    uint32_t tmaZ;
+    int32_t tmaW;
+    uint32_t tmaBytes[18], tmaElemOff[18];
     const int32_t* gateFlags;
     int32_t nGate, gateEpoch, gateItem;
     int32_t K;

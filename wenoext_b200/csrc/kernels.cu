@@ -109,6 +109,26 @@ __device__ __forceinline__ uint64_t evictFirstPolicy() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
+// one lane of the (converged) warp
+__device__ __forceinline__ bool electOne() {
+    uint32_t p;
+    asm volatile(
+        "{\n.reg .pred q;\n"
+        "elect.sync _|q, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, q;\n}\n"
+        : "=r"(p));
+    return p != 0;
+}
+// 2-D TMA tile copy global -> shared: box of the tensor map at element (c0, row c1), rows land
+// densely one after the other; completion on an mbarrier
+__device__ __forceinline__ void tmaLoad2D(uint32_t dst, const void* map, int c0, int c1, uint32_t bar,
+                                          uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint "
+        "[%0], [%1, {%2, %3}], [%4], %5;" ::"r"(dst),
+        "l"(map), "r"(c0), "r"(c1), "r"(bar), "l"(policy)
+        : "memory");
+}
 // 1-D TMA bulk copy global -> shared, completion on an mbarrier
 __device__ __forceinline__ void tmaLoad1D(uint32_t dst, const void* src, uint32_t bytes,
                                           uint32_t bar, uint64_t policy) {
@@ -258,16 +278,42 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     const uint64_t polV = evictLastPolicy();
     const bool issuer = lane < CELLS;
     // RecInfo of cell `lane` of the pass k passes ahead; w < 0: no such cell
-    auto fetchInfo = [&](int k) {
+    // Fast passes: the CELLS cells are consecutive cells of the layout the tensor maps were
+    // built for (plan.cu: buildTmaMaps). One elected lane then fetches each part of all of them
+    // with ONE 2-D copy (box = part x CELLS rows of the record matrix); the rows land densely,
+    // so the slots of such a pass are tmaBytes[part] apart instead of the padded slot strides.
+    // fastOf: cell 0 of the pass, or -1 (per-lane 1-D copies, the general path).
+    const bool tma2d = CELLS == 4 && a.tmaMaps != nullptr;
+    auto fetchInfo = [&](int k, int& fastOf) {
         int4 v = make_int4(0, 0, 0, -1);
         const int w = issuer ? workItem(k, lane) : -1;
-        if (w >= 0) v = __ldg(reinterpret_cast<const int4*>(a.recInfo + workToCell(w)));
+        int cellIdx = -1;
+        if (w >= 0) {
+            cellIdx = workToCell(w);
+            v = __ldg(reinterpret_cast<const int4*>(a.recInfo + cellIdx));
+        }
+        fastOf = -1;
+        if (tma2d) {
+            const int c0 = __shfl_sync(0xffffffffu, cellIdx, 0);
+            const bool ok = !issuer || (cellIdx == c0 + lane && v.w == a.tmaW && (uint32_t)v.z == a.tmaZ);
+            if (__all_sync(0xffffffffu, ok) && c0 >= 0) fastOf = c0;
+        }
         return v;
+    };
+    auto issue2D = [&](uint32_t dst, int part, int cell0, uint32_t bar) {
+        if (issuer) mbarArriveExpectTx(bar, a.tmaBytes[part]);
+        if (electOne())
+            tmaLoad2D(dst, reinterpret_cast<const unsigned char*>(a.tmaMaps) + 128 * part, (int)a.tmaElemOff[part],
+                      cell0, bar, pol);
     };
     auto recPtr = [&](const int4& ri) {
         return a.records + (((uint64_t)(uint32_t)ri.y << 32) | (uint32_t)ri.x);
     };
-    auto issueHead = [&](const int4& ri, int hb) {
+    auto issueHead = [&](const int4& ri, int fastOf, int hb) {
+        if (fastOf >= 0) {
+            issue2D(headBuf + (uint32_t)(hb * CELLS) * a.headSlotBytes, 0, fastOf, bars + hb * 8);
+            return;
+        }
         if (!issuer) return;
         const uint32_t bar = bars + hb * 8;
         if (ri.w >= 0) {
@@ -278,7 +324,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             mbarArrive(bar);
         }
     };
-    auto issueTail = [&](const int4& ri) {
+    auto issueTail = [&](const int4& ri, int fastOf) {
+        if (fastOf >= 0) {
+            issue2D(tailBuf, 1, fastOf, barTail);
+            return;
+        }
         if (!issuer) return;
         const uint32_t bytes = ri.w >= 0 ? ((uint32_t)ri.z >> 16) : 0u;
         if (bytes) {
@@ -295,7 +345,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     int cCh = 0, cPass = 0;
     uint32_t cFullBytes = 0;  // size of a chunk with D columns and D index rows
     int cNFull = 0;           // chunks [0, cNFull) are full
-    auto cursorEnter = [&](const int4& ri) {
+    int cFast = -1;  // the cursor's pass is a fast pass: its cell 0
+    auto cursorEnter = [&](const int4& ri, int fastOf) {
+        cFast = fastOf;
         cInfo = ri;
         cSrc = recPtr(ri) + ((uint32_t)ri.z & 0xffffu) + ((uint32_t)ri.z >> 16);
         cCh = 0;
@@ -304,6 +356,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         cNFull = ri.w >= 0 ? max(0, Nmax / D - GATHER_AHEAD) : 0;
     };
     auto issueChunk = [&](int slot) {
+        if (cFast >= 0) {
+            const uint32_t bar = barRing + slot * 8;
+            if (a.tmaBytes[2 + cCh])
+                issue2D(ringBuf + (uint32_t)(slot * CELLS) * a.chunkSlotBytes, 2 + cCh, cFast, bar);
+            else if (issuer)
+                mbarArrive(bar);
+            ++cCh;
+            return;
+        }
         if (issuer) {
             const uint32_t bar = barRing + slot * 8;
             uint32_t bytes = cFullBytes;
@@ -320,13 +381,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         ++cCh;
     };
 
-    int4 infoCur = fetchInfo(0), infoNext = fetchInfo(1), infoNN = fetchInfo(2);
-    issueHead(infoCur, 0);
-    cursorEnter(infoCur);
+    int fCur, fNext, fNN;
+    int4 infoCur = fetchInfo(0, fCur), infoNext = fetchInfo(1, fNext), infoNN = fetchInfo(2, fNN);
+    issueHead(infoCur, fCur, 0);
+    cursorEnter(infoCur, fCur);
     for (int r = 0; r < R; ++r) issueChunk(r);  // R <= CH
     if (cCh == CH) {
         cPass = 1;
-        cursorEnter(infoNext);
+        cursorEnter(infoNext, fNext);
     }
     // (cells beyond the end of the work have info.w < 0: their copies degenerate to plain
     // arrivals, so the pipeline can run past the last pass without anything in flight)
@@ -368,15 +430,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const int item = cslot < CELLS ? workItem(0, cslot) : -1;
         const bool valid = item >= 0;
         const int hb = i & 1;
-        const uint32_t rec = headBuf + (uint32_t)(hb * CELLS + cslot) * a.headSlotBytes;
-        const uint32_t tail = tailBuf + (uint32_t)cslot * a.tailSlotBytes;
+        // slots of a fast pass are packed (the rows of a 2-D copy land densely)
+        const bool fastCur = fCur >= 0;
+        const uint32_t rec = headBuf + (uint32_t)(hb * CELLS) * a.headSlotBytes +
+                             (uint32_t)cslot * (fastCur ? a.tmaBytes[0] : (uint32_t)a.headSlotBytes);
+        const uint32_t tail = tailBuf + (uint32_t)cslot * (fastCur ? a.tmaBytes[1] : (uint32_t)a.tailSlotBytes);
         const int cell = valid ? workToCell(item) : 0;
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV);
 
         // the other head slot and the tail slot were last read by the previous pass
-        issueHead(infoNext, hb ^ 1);
-        issueTail(infoCur);
+        issueHead(infoNext, fNext, hb ^ 1);
+        issueTail(infoCur, fCur);
 
         mbarWait(bars + hb * 8, (uint32_t)(i >> 1) & 1u);
         int nSt = 0, nFc = 0, Nmax = 0;
@@ -484,12 +549,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 for (int c = 0; c < CB; ++c) cu[d][c] = nx[d][c] - cen[c];
             // this pass's chunk step ch
             mbarWait(barRing + rs * 8, rpar);
-            const uint32_t chunk = ringBuf + (uint32_t)(rs * CELLS + cslot) * a.chunkSlotBytes;
+            const uint32_t cStride = fastCur ? a.tmaBytes[2 + ch] : (uint32_t)a.chunkSlotBytes;
+            const uint32_t ringSlot = ringBuf + (uint32_t)(rs * CELLS) * a.chunkSlotBytes;
+            const uint32_t chunk = ringSlot + (uint32_t)cslot * cStride;
             const int cols = max(0, min(D, Nmax - j0));  // columns stored in this cell's chunk
             // gathers of the columns two steps ahead (their indices travel with this chunk)
             if (j0 + GATHER_AHEAD * D < Nw)
                 gather(chunk + (uint32_t)chunkIdxOffset(K, nSt, cols), j0 + GATHER_AHEAD * D, nx);
-            const uint32_t chunkE = ringBuf + (uint32_t)(rs * CELLS + cslotE) * a.chunkSlotBytes;
+            const uint32_t chunkE = ringSlot + (uint32_t)cslotE * cStride;
             uint32_t Ap = chunkE + sE * 16;
             uint32_t Sp = chunkE + (uint32_t)max(0, min(D, NmaxE - j0)) * KP * pStr + sE * 8;
             const int colsW = min(D, Nw - j0);  // warp-wide column count of this step
@@ -547,7 +614,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             issueChunk(rs);
             if (cCh == CH) {
                 ++cPass;
-                cursorEnter(cPass - i == 1 ? infoNext : infoNN);
+                if (cPass - i == 1)
+                    cursorEnter(infoNext, fNext);
+                else
+                    cursorEnter(infoNN, fNN);
             }
             if (++rs == R) {
                 rs = 0;
@@ -736,7 +806,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         }
         infoCur = infoNext;
         infoNext = infoNN;
-        infoNN = fetchInfo(2);
+        fCur = fNext;
+        fNext = fNN;
+        infoNN = fetchInfo(2, fNN);
     }
 }
 }  // namespace

@@ -1,5 +1,7 @@
 // Device plan creation (flatten + upload + on-device record expansion) and the
 // per-call orchestration of correction(). See include/wenoext_b200.h.
+#include <cuda.h>
+#include <cudaTypedefs.h>
 #include <cuda_runtime.h>
 #include <climits>
 #include <dlfcn.h>
@@ -8,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -189,6 +192,59 @@ __global__ void expand_records_kernel(const ExpandArgs a) {
 
 using namespace wenoext;
 
+// Tensor maps for the 2-D bulk copies of the cell kernel: the records as a matrix of
+// nCells rows of recStride bytes; the box of part p (head, tail, chunk step ch) of the
+// dominant layout is [bytes_p / 8 elements] x [4 cells]. One copy then serves the four cells
+// of a pass, instead of four per-lane copies behind a serialising loop. Failure of any step
+// just leaves the per-lane path in charge.
+static void buildTmaMaps(wenoext_plan* P) {
+    const int K = P->K, D = chunkCols(K);
+    const int nSt = P->tmaW & 0xffff, Nmax = P->tmaW >> 16;
+    const uint32_t headB = P->tmaZ & 0xffffu, tailB = P->tmaZ >> 16;
+    const int nCh = (Nmax + D - 1) / D;
+    if (nSt <= 0 || Nmax <= 0 || nCh + 2 > 18 || P->recStride % 16) return;
+    uint32_t bytes[18] = {0}, off[18] = {0};
+    bytes[0] = headB;
+    bytes[1] = tailB;
+    off[1] = headB;
+    uint32_t run = headB + tailB;
+    for (int ch = 0; ch < nCh; ++ch) {
+        bytes[2 + ch] = (uint32_t)chunkBytes(K, nSt, Nmax, ch);
+        off[2 + ch] = run;
+        run += bytes[2 + ch];
+    }
+    for (int p = 0; p < nCh + 2; ++p)
+        if (bytes[p] == 0 || bytes[p] % 16 || bytes[p] / 8 > 256 || off[p] % 16) return;
+    PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void**)&encode, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || !encode) {
+        cudaGetLastError();
+        return;
+    }
+    std::vector<CUtensorMap> maps(nCh + 2);
+    for (int p = 0; p < nCh + 2; ++p) {
+        const cuuint64_t gdim[2] = {(cuuint64_t)(P->recStride / 8), (cuuint64_t)P->nCells};
+        const cuuint64_t gstr[1] = {(cuuint64_t)P->recStride};
+        const cuuint32_t box[2] = {bytes[p] / 8, 4};
+        const cuuint32_t estr[2] = {1, 1};
+        if (encode(&maps[p], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, P->records, gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return;
+    }
+    if (cudaMalloc((void**)&P->tmaMaps, maps.size() * sizeof(CUtensorMap)) != cudaSuccess) {
+        cudaGetLastError();
+        P->tmaMaps = nullptr;
+        return;
+    }
+    cudaMemcpy(P->tmaMaps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice);
+    for (int p = 0; p < 18; ++p) {
+        P->tmaBytes[p] = bytes[p];
+        P->tmaElemOff[p] = off[p] / 8;
+    }
+}
+
 static int validateDesc(const wenoext_plan_desc* d) {
     if (!d) {
         setError("desc is NULL");
@@ -367,6 +423,37 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     }
     P->maxSt = std::max(P->maxSt, 1);
     P->recordBytesTotal = recOff;
+    // Uniform record stride (2-D bulk copies, see buildTmaMaps): when padding every record to the
+    // size of the largest costs next to nothing in footprint (nothing in traffic: parts are
+    // fetched with their own sizes), cell c's record starts at c * stride, and the same part
+    // of four consecutive cells is ONE strided box for the copy engine.
+    P->recStride = 0;
+    {
+        const int64_t stride = (P->maxRecordBytes + 15) / 16 * 16;
+        const char* e = getenv("WENOEXT_TMA2D");
+        // WENOEXT_TMA2D=0: off; =2: on whatever the padding costs (tests on small meshes)
+        const bool force = e && atoi(e) == 2;
+        if (nC > 0 && !(e && atoi(e) == 0) && (force || (double)stride * nC <= 1.05 * (double)recOff)) {
+            for (int c = 0; c < nC; ++c) recInfo[c].off = (int64_t)c * stride;
+            P->recStride = stride;
+            P->recordBytesTotal = stride * nC;
+        }
+    }
+    // the most frequent layout (interior cells): the one the 2-D copies are set up for
+    {
+        std::map<std::pair<uint32_t, int32_t>, int> freq;
+        for (int c = 0; c < nC; ++c)
+            if (recInfo[c].nSt > 0)
+                ++freq[{(uint32_t)recInfo[c].headBytes | ((uint32_t)recInfo[c].tailBytes << 16),
+                        (int32_t)recInfo[c].nSt | ((int32_t)recInfo[c].Nmax << 16)}];
+        int best = 0;
+        for (const auto& kv : freq)
+            if (kv.second > best) {
+                best = kv.second;
+                P->tmaZ = kv.first.first;
+                P->tmaW = kv.first.second;
+            }
+    }
     const int64_t nWritten = (int64_t)P->nInt + nCoupled;
     algFixed += nWritten * (8 * K + 24);
     flopsPerComp += nWritten * 2 * K;
@@ -473,6 +560,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
             rc = WENOEXT_ERR_CUDA;
         }
     }
+    if (!rc && P->recStride > 0) buildTmaMaps(P);
     // interior / boundary cell lists (overlap of the halo exchange)
     std::vector<int32_t> li, lb;
     if (!rc) {
@@ -617,7 +705,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     cudaSetDevice(P->device);
     if (P->h_fix) cudaFreeHost(P->h_fix);
     void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
-                    P->tileCounter, P->haloFlags, P->pushDone, P->records, P->recInfo, P->cellListInterior, P->owner,
+                    P->tileCounter, P->haloFlags, P->pushDone, P->tmaMaps, P->records, P->recInfo, P->cellListInterior, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
                     P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
     for (void* p : ptrs)
@@ -971,6 +1059,13 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
     a.tileCounter = counter;
     a.workBase = workBase;
     a.nWork = nWork;
+    a.tmaMaps = P->tmaMaps;
+    a.tmaZ = P->tmaZ;
+    a.tmaW = P->tmaW;
+    for (int p = 0; p < 18; ++p) {
+        a.tmaBytes[p] = P->tmaBytes[p];
+        a.tmaElemOff[p] = P->tmaElemOff[p];
+    }
     a.gateItem = gateItem;
     if (gateItem >= 0 && !followUp) {
         a.gateFlags = P->haloFlags;

@@ -55,6 +55,13 @@ struct wenoext_plan {
     int32_t* tileCounter = nullptr;  // work counter of the cell kernel, zeroed before every launch
     int64_t recordBytesTotal = 0, maxRecordBytes = 0, maxHeadBytes = 0, maxTailBytes = 0;
     int32_t maxSt = 0, maxFc = 0;
+    // 2-D bulk copies: uniform record stride (0: records packed, no fast path), the layout the
+    // tensor maps were built for, the maps (device) and the part table of that layout
+    int64_t recStride = 0;
+    uint32_t tmaZ = 0;
+    int32_t tmaW = 0;
+    void* tmaMaps = nullptr;
+    uint32_t tmaBytes[18] = {0}, tmaElemOff[18] = {0};
     int32_t* cellListInterior = nullptr;
     int32_t* cellListBoundary = nullptr;
     int32_t nInterior = 0, nBoundaryCells = 0;
