@@ -1,0 +1,209 @@
+/* REFERENCE BUILD HARNESS — TEST INFRASTRUCTURE ONLY (never linked into the product).
+ *
+ * Drives the reference's own, unmodified hot-path code — compiled by oracle/Makefile from
+ *   /root/reference/libWENOEXT/WENOUpwindFit/makeWENOUpwindFit.C      (-> WENOUpwindFit.H/.C, WENOCoeff.H/.C)
+ *   /root/reference/libWENOEXT/WENOUpwindFit01/makeWENOUpwindFit01.C  (-> WENOUpwindFit01.H/.C)
+ * against the OpenFOAM stand-in in oracle/of_stub/ — through the interface OpenFOAM itself would use:
+ * run-time selection by scheme name (makeSurfaceInterpolationScheme, makeWENOUpwindFit.C:37), the
+ * (mesh, faceFlux, Istream) constructor with the `<order> <bounded>` tokens (WENOUpwindFit.H:195-211),
+ * WENODict (WENOCoeff.C:70-89), then weights() and correction(vf) (WENOUpwindFit.H:223-242).
+ * A parallel run is emulated with one thread per MPI rank over the Pstream stand-in, so collectData
+ * (WENOCoeff.C:224-296) and swapData (WENOUpwindFit.C:326-385) run as written.
+ * Inputs: one wenoext_plan_desc per rank, i.e. the same flattened WENOBase content the GPU plan gets.
+ */
+#include "of_stub/WENOBase.H"
+#include "WENOCoeff.H"
+
+#include <atomic>
+#include <chrono>
+#include <thread>
+
+#include "../include/wenoext_b200.h"
+
+namespace Foam
+{
+// ---- definitions the stand-in headers declare
+const scalar pTraits<scalar>::zero = 0.0;
+const scalar pTraits<scalar>::one = 1.0;
+const char* const pTraits<scalar>::typeName = "scalar";
+#define OFSTUB_PTRAITS_DEF(T, N)                                            \
+    const T pTraits<T>::zero = T(VectorSpace<N>::uniform(0.0));            \
+    const T pTraits<T>::one = T(VectorSpace<N>::uniform(1.0));             \
+    const char* const pTraits<T>::typeName = #T;
+OFSTUB_PTRAITS_DEF(vector, 3)
+OFSTUB_PTRAITS_DEF(sphericalTensor, 1)
+OFSTUB_PTRAITS_DEF(symmTensor, 6)
+OFSTUB_PTRAITS_DEF(tensor, 9)
+
+OSstream& InfoStream()
+{
+    static OSstream s(std::cout, false);
+    return s;
+}
+error& FatalErrorStream()
+{
+    static thread_local error e;
+    return e;
+}
+bool isDir(const fileName&) { return false; }
+namespace stubPar
+{
+    Context& ctx()
+    {
+        static thread_local Context c;
+        return c;
+    }
+}
+
+IOdictionary::IOdictionary(const IOobject& io) : name_(io.name())
+{
+    const fvMesh* mesh = dynamic_cast<const fvMesh*>(&io.db());
+    if (mesh)
+    {
+        if (const auto* d = mesh->time().findDict(io.name())) entries_ = *d;
+    }
+}
+
+// ---- WENOBase facade
+namespace
+{
+    typedef std::map<std::pair<const fvMesh*, label>, std::unique_ptr<WENOBase>> BaseMap;
+    struct BaseRegistry
+    {
+        std::mutex m;
+        std::map<std::pair<const fvMesh*, label>, WENOBase*> map;
+    };
+    BaseRegistry& bases()
+    {
+        static BaseRegistry r;
+        return r;
+    }
+}
+
+WENOBase& WENOBase::instance(const fvMesh& mesh, const label polOrder)
+{
+    std::lock_guard<std::mutex> g(bases().m);
+    auto it = bases().map.find(std::make_pair(&mesh, polOrder));
+    if (it == bases().map.end())
+        throw std::runtime_error("WENOBase facade: no instance registered for this mesh and order "
+                                 + std::to_string(polOrder));
+    return *it->second;
+}
+
+void WENOBase::release(const fvMesh& mesh)
+{
+    std::lock_guard<std::mutex> g(bases().m);
+    for (auto it = bases().map.begin(); it != bases().map.end();)
+    {
+        if (it->first.first == &mesh)
+        {
+            delete it->second;
+            it = bases().map.erase(it);
+        }
+        else ++it;
+    }
+}
+
+WENOBase& WENOBase::fromDesc(const fvMesh& mesh, const wenoext_plan_desc& d)
+{
+    WENOBase* wb = new WENOBase;
+    const label K = d.nDvt, r1 = d.polOrder + 1;
+    wb->polOrder_ = d.polOrder;
+    wb->nDvt_ = K;
+    wb->dimList_.setSize(d.nCells);
+    wb->stencilsID_.setSize(d.nCells);
+    wb->cellToProcMap_.setSize(d.nCells);
+    wb->B_.setSize(d.nCells);
+    wb->LSmatrix_.LSmatrix_.setSize(d.nCells);
+    wb->LSmatrix_.DB_.resize(size_t(d.nUniqueMatrices));
+    for (int32_t m = 0; m < d.nUniqueMatrices; ++m)
+    {
+        const label N = d.matrixCols[m];
+        const size_t rows = size_t(K), cols = size_t(N);
+        matrixDB::DynamicMatrix M(rows, cols);
+        const double* src = d.matrixData + d.matrixStart[m];
+        for (label i = 0; i < K; ++i)
+            for (label j = 0; j < N; ++j) M(i, j) = src[size_t(i) * N + j];
+        wb->LSmatrix_.DB_[size_t(m)] = std::move(M);
+    }
+    for (label c = 0; c < d.nCells; ++c)
+    {
+        labelList dim(3);
+        for (int i = 0; i < 3; ++i) dim[i] = d.dim[i];
+        wb->dimList_[c] = dim;
+        const int64_t s0 = d.cellStencilStart[c], s1 = d.cellStencilStart[c + 1];
+        wb->stencilsID_[c].setSize(label(s1 - s0));
+        wb->cellToProcMap_[c].setSize(label(s1 - s0));
+        wb->LSmatrix_.LSmatrix_[c].setSize(label(s1 - s0));
+        for (int64_t s = s0; s < s1; ++s)
+        {
+            const int64_t e0 = d.stencilEntryStart[s], e1 = d.stencilEntryStart[s + 1];
+            labelList ids(label(e1 - e0)), map(label(e1 - e0));
+            for (int64_t e = e0; e < e1; ++e)
+            {
+                ids[label(e - e0)] = d.stencilsID[e];
+                map[label(e - e0)] = d.cellToProcMap ? d.cellToProcMap[e]
+                                   : (d.stencilsID[e] < 0 ? d.stencilsID[e] : int(Cell::local));
+            }
+            wb->stencilsID_[c][label(s - s0)] = std::move(ids);
+            wb->cellToProcMap_[c][label(s - s0)] = std::move(map);
+            const int32_t m = d.stencilMatrix[s];
+            wb->LSmatrix_.LSmatrix_[c][label(s - s0)] =
+                matrixDB::MatrixPtr(m >= 0 ? &wb->LSmatrix_.DB_[size_t(m)] : nullptr);
+        }
+        const size_t nK = size_t(K);
+        geometryWENO::DynamicMatrix Bc(nK, nK);
+        const double* src = d.B + size_t(c) * K * K;
+        for (label i = 0; i < K; ++i)
+            for (label j = 0; j < K; ++j) Bc(i, j) = src[i * K + j];
+        wb->B_[c] = std::move(Bc);
+    }
+    wb->intBasTrans_.setSize(d.nFaces);
+    wb->refFacAr_.setSize(d.nFaces);
+    const size_t cube = size_t(r1) * r1 * r1;
+    for (label f = 0; f < d.nFaces; ++f)
+    {
+        for (int side = 0; side < 2; ++side)
+        {
+            List3D<scalar> L(r1, r1, r1);
+            const double* src = d.intBasTrans + (size_t(f) * 2 + side) * cube;
+            for (label n = 0; n < r1; ++n)
+                for (label m = 0; m < r1; ++m)
+                    for (label l = 0; l < r1; ++l) L(n, m, l) = src[(size_t(n) * r1 + m) * r1 + l];
+            wb->intBasTrans_[f][side] = std::move(L);
+        }
+        wb->refFacAr_[f] = d.refFacAr[f];
+    }
+    const label nProcs = d.nProcs > 1 ? d.nProcs : 0;
+    wb->sendProcList_.setSize(nProcs);
+    wb->receiveProcList_.setSize(nProcs);
+    wb->receiveHaloSize_.setSize(nProcs);
+    wb->sendHaloCellIDList_.setSize(nProcs);
+    for (label p = 0; p < nProcs; ++p)
+    {
+        wb->sendProcList_[p] = d.sendProcList[p];
+        wb->receiveProcList_[p] = d.receiveProcList[p];
+        wb->receiveHaloSize_[p] = d.receiveHaloSize[p];
+        const int64_t a = d.sendHaloStart[p], b = d.sendHaloStart[p + 1];
+        labelList ids(label(b - a));
+        for (int64_t i = a; i < b; ++i) ids[label(i - a)] = d.sendHaloCellID[i];
+        wb->sendHaloCellIDList_[p] = std::move(ids);
+    }
+    std::lock_guard<std::mutex> g(bases().m);
+    WENOBase*& slot = bases().map[std::make_pair(&mesh, label(d.polOrder))];
+    delete slot;
+    slot = wb;
+    return *wb;
+}
+
+//- WENOCoeff reads WENODict only at its first construction per Type (static printWENODict_,
+//  WENOCoeff.C:68-98, a protected member); a derived class may clear the flag so that a test can change
+//  the dictionary between runs inside one process
+template<class Type>
+struct WENODictReread : public WENOCoeff<Type>
+{
+    static void arm() { WENOCoeff<Type>::printWENODict_ = false; }
+};
+}  // namespace Foam
+
+#include "ref_harness_run.inc"

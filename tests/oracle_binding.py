@@ -235,3 +235,96 @@ def correction_distributed(orc, case, scheme, bounded, vf, flux, p=4.0, dm=1000.
         recv[start - nI:start - nI + size] = t[:size]
         pnf[start - nI:start - nI + size] = t[size:]
     return orc.phaseB(case, scheme, bounded, vf, flux, cw, corr, pnf, recv, bugCompat)
+
+
+# ----------------------------------------------------------------------------------------------------
+# The reference's OWN hot-path code (oracle/_ref/libweno_ref_<isa>.so, built by oracle/Makefile from the
+# unmodified translation units under /root/reference against oracle/of_stub). Parity pin + CPU baseline.
+def _ref_so_path():
+    """AVX-512 build when the host has it (what the reference's -march=native gives), else AVX2."""
+    flags = ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    flags = line
+                    break
+    except OSError:
+        pass
+    need = ("avx512f", "avx512dq", "avx512cd", "avx512bw", "avx512vl")
+    isa = "v4" if all(x in flags.split() for x in need) else "v3"
+    if os.environ.get("WENO_REF_ISA"):
+        isa = os.environ["WENO_REF_ISA"]
+    return os.path.join(ROOT, "oracle", "_ref", f"libweno_ref_{isa}.so"), isa
+
+
+def reference_build_available():
+    return os.path.exists(_ref_so_path()[0])
+
+
+_TYPE_OF_NCOMP = {1: "scalar", 3: "vector", 6: "symmTensor", 9: "tensor"}
+
+
+class ReferenceBuild:
+    """Runs WENOUpwindFit<Type>::correction / WENOUpwindFit01<Type>::correction of the reference
+    itself on one case (serial) or a list of per-rank cases (one thread per MPI rank)."""
+
+    def __init__(self, cases):
+        path, self.isa = _ref_so_path()
+        self.L = C.CDLL(path)
+        self.L.weno_ref_create.restype = vp
+        self.L.weno_ref_create.argtypes = [C.c_int, vp]
+        self.L.weno_ref_destroy.argtypes = [vp]
+        self.L.weno_ref_last_error.restype = C.c_char_p
+        self.L.weno_ref_provenance.restype = C.c_char_p
+        self.L.weno_ref_set_dict.argtypes = [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int,
+                                             C.c_double]
+        self.L.weno_ref_correction.argtypes = [vp, C.c_char_p, C.c_char_p, vp, vp, vp, vp, C.c_int, vp]
+        self.cases = list(cases) if isinstance(cases, (list, tuple)) else [cases]
+        self.serial_input = not isinstance(cases, (list, tuple))
+        R = len(self.cases)
+        self._descs = (vp * R)(*[C.addressof(c.desc) for c in self.cases])
+        self.h = self.L.weno_ref_create(R, self._descs)
+        if not self.h:
+            raise RuntimeError(self.L.weno_ref_last_error().decode())
+        self.provenance = self.L.weno_ref_provenance().decode()
+        self.last_seconds = None
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.weno_ref_destroy(self.h)
+            self.h = None
+
+    def set_dict(self, p=None, dm=None, epsilon=None):
+        """system/WENODict (WENOCoeff.C:87-89); None keeps the reference's default."""
+        self.L.weno_ref_set_dict(self.h, p is not None, p or 0.0, dm is not None, dm or 0.0,
+                                 epsilon is not None, epsilon or 0.0)
+
+    def correction(self, scheme, order, bounded, vfs, fluxes, typeName=None, repeat=1,
+                   want_weights=False):
+        """scheme: 0 / 'WENOUpwindFit' or 1 / 'WENOUpwindFit01'. Returns corr per rank
+        ([nFaces] or [nFaces][nComp], like vf), or the single array for a serial case."""
+        name = {0: "WENOUpwindFit", 1: "WENOUpwindFit01"}.get(scheme, scheme)
+        spec = f"{name} {order}" + (f" {int(bounded)}" if name == "WENOUpwindFit" else "")
+        if self.serial_input:
+            vfs, fluxes = [vfs], [fluxes]
+        R = len(self.cases)
+        vfs = [_f64(v) for v in vfs]
+        flat = vfs[0].ndim == 1
+        vfs2 = [v.reshape(c.nCells, -1) for v, c in zip(vfs, self.cases)]
+        nComp = vfs2[0].shape[1]
+        typeName = typeName or _TYPE_OF_NCOMP[nComp]
+        fl = [_f64(f) for f in fluxes]
+        corr = [np.zeros((c.nFaces, nComp)) for c in self.cases]
+        wts = [np.zeros(c.nFaces) for c in self.cases] if want_weights else None
+        arr = lambda xs: (vp * R)(*[x.ctypes.data for x in xs])  # noqa: E731
+        secs = C.c_double(0.0)
+        rc = self.L.weno_ref_correction(self.h, spec.encode(), typeName.encode(), arr(vfs2), arr(fl),
+                                        arr(corr), arr(wts) if wts else None, repeat, C.byref(secs))
+        if rc != 0:
+            raise RuntimeError(self.L.weno_ref_last_error().decode())
+        self.last_seconds = secs.value
+        out = [c[:, 0] if flat else c for c in corr]
+        if want_weights:
+            return (out[0], wts[0]) if self.serial_input else (out, wts)
+        return out[0] if self.serial_input else out
