@@ -1,18 +1,22 @@
 """Generate the golden correction() vectors under tests/golden/.
 
-The reference itself cannot run in this container (every hot-path translation unit
-needs OpenFOAM) and its own tests pin no per-face value, so the
-golden outputs are produced by the strongest available stand-in: the oracle
-variant that performs the three matrix products with the reference's vendored
-Blaze 3.8 (oracle/weno_oracle_blaze.cpp -> oracle/_ref/), on the stencil data of
-the host setup restatement. Inputs follow SURVEY.md 8(c)/(d): the reference's
-analytic test field, a Zalesak-like indicator, polynomial / constant fields,
-seeded noise, and fluxes with mixed signs and exact zeros.
+PROVENANCE: the outputs are produced by the REFERENCE'S OWN CODE. oracle/Makefile compiles the
+unmodified translation units libWENOEXT/WENOUpwindFit/makeWENOUpwindFit.C and
+libWENOEXT/WENOUpwindFit01/makeWENOUpwindFit01.C (hence WENOUpwindFit.C, WENOUpwindFit01.C,
+WENOCoeff.C, List3D.H and the vendored Blaze 3.8) where they lie under /root/reference against the
+OpenFOAM stand-in oracle/of_stub/, and tests/oracle_binding.ReferenceBuild drives them through
+run-time selection ("WENOUpwindFit 2 1"), weights() and correction(vf) - one thread per MPI rank for
+the decomposed cases, so collectData and swapData run as written. The reference's own tests pin no
+per-face value, so these vectors are what pins the C oracle and the CUDA path.
+The stencil data (the WENOBase content) comes from the host setup stand-in, which is what all three
+(reference build, oracle, GPU plan) consume in the same flattened form.
 
-    python tests/golden/make_golden.py        (rewrites tests/golden/*.npz)
+    python tests/golden/make_golden.py        (rewrites tests/golden/*.npz; needs /root/reference)
 
-Each file holds, for one mesh case: cell values and face fluxes per input set,
-and the oracle's correction for every (scheme, bounded) pair.
+Inputs follow SURVEY.md 8(c)/(d): the reference's analytic test field, a Zalesak-like indicator,
+polynomial / constant fields, seeded noise, fluxes with mixed signs and exact zeros.
+Each file holds, for one mesh case: cell values and face fluxes per input set (per rank for the
+decomposed cases, keys "<set>/r<rank>/..."), and the correction for every (scheme, bounded) pair.
 """
 import os
 import sys
@@ -23,7 +27,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 import wenoext_b200 as wx  # noqa: E402
 from tests import helpers as H  # noqa: E402
-from tests.oracle_binding import Oracle  # noqa: E402
 
 FIT, FIT01 = 0, 1
 SCHEMES = [(FIT, 0), (FIT, 1), (FIT01, 1)]
@@ -36,6 +39,12 @@ CASES = {
     "cyclic2d12_o2": dict(n=(12, 12, 1), order=2, sides=(2, 2, 2, 2, 3, 3)),
     "hex6_o3": dict(n=(6, 6, 6), order=3),
 }
+# decomposed cases: `decomposePar simple` blocks, one MPI rank each
+PAR_CASES = {
+    "hex8x6x6_o2_np2": dict(n=(8, 6, 6), order=2, nProc=(2, 1, 1)),
+    "hex6_o2_np8": dict(n=(6, 6, 6), order=2, nProc=(2, 2, 2)),
+    "cyclicy10x6x6_o2_np2": dict(n=(10, 6, 6), order=2, nProc=(2, 1, 1), sides=(0, 0, 2, 2, 0, 0)),
+}
 
 
 def make_case(name):
@@ -44,14 +53,24 @@ def make_case(name):
     return wx.BoxCase(n, order, useClassCache=False, **kw)
 
 
-def unit_coords(case):
-    lo, hi = case.C.min(axis=0), case.C.max(axis=0)
+def make_par_cases(name):
+    kw = dict(PAR_CASES[name])
+    n, order, nProc = kw.pop("n"), kw.pop("order"), kw.pop("nProc")
+    R = int(np.prod(nProc))
+    cases = [wx.BoxCase(n, order, nProc=nProc, myProc=r, useClassCache=False, **kw) for r in range(R)]
+    wx.exchange_halo_lists(cases)
+    return cases
+
+
+def unit_coords(case, lo=None, hi=None):
+    lo = case.C.min(axis=0) if lo is None else lo
+    hi = case.C.max(axis=0) if hi is None else hi
     return (case.C - lo) / (hi - lo + 1e-300)
 
 
-def input_sets(case):
+def input_sets(case, X=None):
     """name -> (vf [nCells] or [nCells][3], flux [nFaces])"""
-    X = unit_coords(case)
+    X = unit_coords(case) if X is None else X
     sets = {}
     # (i) reference test field, U = (1,1,1)                (WENOUpwindFit-Test.C:87-94,:199,:220)
     sets["sine_u111"] = (H.sin_field(X), H.face_flux(case.Sf))
@@ -74,22 +93,50 @@ def input_sets(case):
     return sets
 
 
+def par_input_sets(cases):
+    """name -> ([vf per rank], [flux per rank]); the fields are functions of the global coordinates
+    (unit box) and the processor-patch fluxes of the two sides are equal and opposite by
+    construction (S_f . U with opposite S_f; the zero pattern is not used here because the two
+    sides would draw different random faces)."""
+    per_rank = [input_sets(c, X=c.C.copy()) for c in cases]
+    names = [k for k in per_rank[0] if k != "vector_zero_flux"]
+    return {k: ([s[k][0] for s in per_rank], [s[k][1] for s in per_rank]) for k in names}
+
+
 def main():
+    from tests.oracle_binding import ReferenceBuild
     out_dir = os.path.dirname(os.path.abspath(__file__))
-    orc = Oracle("blaze")
     for name in CASES:
         case = make_case(name)
+        order = CASES[name]["order"]
+        ref = ReferenceBuild(case)
         data = {"nCells": np.int64(case.nCells), "nFaces": np.int64(case.nFaces),
-                "nInternalFaces": np.int64(case.nInternalFaces)}
+                "nInternalFaces": np.int64(case.nInternalFaces),
+                "provenance": np.array(ref.provenance)}
         for sname, (vf, flux) in input_sets(case).items():
             data[f"{sname}/vf"] = vf
             data[f"{sname}/flux"] = flux
             for scheme, bounded in SCHEMES:
-                corr = orc.correction(case, scheme, bounded, vf, flux)
-                data[f"{sname}/corr_s{scheme}b{bounded}"] = corr
+                data[f"{sname}/corr_s{scheme}b{bounded}"] = ref.correction(scheme, order, bounded, vf, flux)
         path = os.path.join(out_dir, name + ".npz")
         np.savez_compressed(path, **data)
         print(name, case.nCells, "cells ->", os.path.getsize(path) // 1024, "KiB")
+    for name in PAR_CASES:
+        cases = make_par_cases(name)
+        order = PAR_CASES[name]["order"]
+        ref = ReferenceBuild(cases)
+        data = {"nRanks": np.int64(len(cases)), "provenance": np.array(ref.provenance)}
+        for sname, (vfs, fluxes) in par_input_sets(cases).items():
+            for r in range(len(cases)):
+                data[f"{sname}/r{r}/vf"] = vfs[r]
+                data[f"{sname}/r{r}/flux"] = fluxes[r]
+            for scheme, bounded in SCHEMES:
+                corr = ref.correction(scheme, order, bounded, vfs, fluxes)
+                for r in range(len(cases)):
+                    data[f"{sname}/r{r}/corr_s{scheme}b{bounded}"] = corr[r]
+        path = os.path.join(out_dir, name + ".npz")
+        np.savez_compressed(path, **data)
+        print(name, sum(c.nCells for c in cases), "cells ->", os.path.getsize(path) // 1024, "KiB")
 
 
 if __name__ == "__main__":
