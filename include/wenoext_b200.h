@@ -25,6 +25,7 @@ extern "C" {
 #define WENOEXT_ERR_CUDA 2      /* CUDA runtime error or no device */
 #define WENOEXT_ERR_NCCL 3      /* NCCL unavailable or failed */
 #define WENOEXT_ERR_SETUP 4     /* host setup (WENOBase stand-in) failed */
+#define WENOEXT_ERR_TIMEOUT 5   /* a peer's halo did not arrive within WENOEXT_HALO_TIMEOUT_S */
 
 /* WENOBase::Cell (WENOBase.H:62-67) */
 #define WENOEXT_CELL_LOCAL (-1)

@@ -286,3 +286,22 @@ def test_launch_geometries(monkeypatch, env, name):
         ref = Oracle("c").correction(case, scheme, bounded, vf, flux)
         assert H.normwise_err(got, ref) <= TOL, (env, name, scheme, bounded)
     plan.destroy()
+
+
+def test_plans_on_two_devices_in_one_process():
+    """The opt-in to >48 KB dynamic shared memory is per function AND per device: a second plan on
+    another GPU of the same process must launch as well (kernels.cu launchT)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    case = case_of("hex8")
+    vf = _fields(case, 3, seed=2)
+    flux = H.rotating_flux(case)
+    want = Oracle("c").correction(case, FIT, 1, vf, flux)
+    for dev in (0, 1, 0):
+        plan = wx.Plan(case.desc, device=dev)
+        try:
+            got = plan.correction(FIT, 1, vf, flux)
+            assert H.normwise_err(np.asarray(got).reshape(want.shape), want) < TOL
+        finally:
+            plan.destroy()

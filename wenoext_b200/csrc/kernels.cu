@@ -169,22 +169,39 @@ __device__ __forceinline__ uint64_t evictLastPolicy() {
 }
 // Cell values are re-read by every neighbouring stencil while 26 GB of records
 // stream through the L2 once: keep them resident (evict_last) against the stream.
+// `coh` (warp-uniform): the values may have been written by a peer GPU while this kernel runs
+// (halo region of `vals`, boundary tiles of a gated launch). The non-coherent path (.nc) is only
+// defined for data that is read-only for the kernel's lifetime, so those tiles use the coherent
+// path, which the ld.acquire.sys on the halo flag orders against the peers' writes.
 template <int CB>
-__device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB], uint64_t pol) {
+__device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB], uint64_t pol,
+                                         const bool coh = false) {
+    const uint32_t c = coh ? 1u : 0u;
     if constexpr (CB == 1) {
-        asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v[0]) : "l"(p), "l"(pol));
+        asm volatile(
+            "{\n.reg .pred q;\nsetp.ne.u32 q, %3, 0;\n"
+            "@q ld.global.L2::cache_hint.f64 %0, [%1], %2;\n"
+            "@!q ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;\n}\n"
+            : "=d"(v[0])
+            : "l"(p), "l"(pol), "r"(c));
     } else {
         if constexpr (CB == 3) {
             // a 3-vector sits in a 32-byte slot (VS = 4): one 256-bit load, the pad is dropped
             double pad;
-            asm volatile("ld.global.nc.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;"
-                         : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(pad)
-                         : "l"(p), "l"(pol));
+            asm volatile(
+                "{\n.reg .pred q;\nsetp.ne.u32 q, %6, 0;\n"
+                "@q ld.global.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;\n"
+                "@!q ld.global.nc.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;\n}\n"
+                : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(pad)
+                : "l"(p), "l"(pol), "r"(c));
             return;
         }
-        asm volatile("ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
-                     : "=d"(v[0]), "=d"(v[1])
-                     : "l"(p), "l"(pol));
+        asm volatile(
+            "{\n.reg .pred q;\nsetp.ne.u32 q, %4, 0;\n"
+            "@q ld.global.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;\n"
+            "@!q ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;\n}\n"
+            : "=d"(v[0]), "=d"(v[1])
+            : "l"(p), "l"(pol), "r"(c));
     }
 }
 
@@ -255,6 +272,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         if (lane == 0) t = ready ? nTilesA + atomicAdd(a.tileCounter + 1, 1) : nTiles;
         return __shfl_sync(0xffffffffu, t, 0);
     };
+    // a halo that never arrived (halo_wait_kernel timed out): leave the boundary cells alone
+    if (a.abortFlag && *reinterpret_cast<const volatile int32_t*>(a.abortFlag) != 0) return;
     int curTile = resolveTile(grabTile());
     if (curTile >= nTiles) return;
     int pendingTile = grabTile();  // becomes nextTile at pass PPT / 2 of the current tile
@@ -436,8 +455,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                              (uint32_t)cslot * (fastCur ? a.tmaBytes[0] : (uint32_t)a.headSlotBytes);
         const uint32_t tail = tailBuf + (uint32_t)cslot * (fastCur ? a.tmaBytes[1] : (uint32_t)a.tailSlotBytes);
         const int cell = valid ? workToCell(item) : 0;
+        // boundary tiles of a gated launch read halo values that peers push during this kernel
+        const bool coh = split && curTile >= nTilesA;
         double cen[CB];
-        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV);
+        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV, coh);
 
         // the other head slot and the tail slot were last read by the previous pass
         issueHead(infoNext, fNext, hb ^ 1);
@@ -488,7 +509,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #endif
             pfFlux = __ldg(a.flux + pfFace.x);
             if (fitBounded && (pfFace.z >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
-                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN, polV);
+                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN, polV, coh);
         }
 
         // gather of column j of this lane's stencil (WENOCoeff.C:138-156), branch-free:
@@ -509,7 +530,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                     id = 0;
                 }
 #endif
-                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d], polV);
+                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d], polV, coh);
             }
         };
         // two buffers: the columns of step ch are gathered GATHER_AHEAD = 2 steps earlier
@@ -776,7 +797,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                             for (int c = 0; c < CB; ++c) psiN[c] = pfPsiN[c];
                         } else {
-                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN, polV);
+                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN, polV, coh);
                         }
 #pragma unroll
                         for (int c = 0; c < CB; ++c) {
@@ -939,13 +960,17 @@ int cellKernelMaxWarps() { return MAX_THREADS / 32; }
 namespace {
 template <int K, int CB, int CELLS, int D>
 int launchT(const CellKernelArgs& a, int gridBlocks, size_t smemBytes, cudaStream_t st) {
-    static size_t configured = 0;  // per instantiation
-    if (smemBytes > configured) {
+    // the opt-in to large dynamic shared memory is per function AND per device
+    constexpr int MAX_DEVICES = 64;
+    static size_t configured[MAX_DEVICES] = {0};  // per instantiation
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+    if (dev < 0 || dev >= MAX_DEVICES || smemBytes > configured[dev]) {
         if (cudaFuncSetAttribute(weno_cell_kernel<K, CB, CELLS, D>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smemBytes) != cudaSuccess)
             return 1;
-        configured = smemBytes;
+        if (dev >= 0 && dev < MAX_DEVICES) configured[dev] = smemBytes;
     }
     const int threads = a.nWarps * 32;
     weno_cell_kernel<K, CB, CELLS, D><<<gridBlocks, threads, smemBytes, st>>>(a);
@@ -1063,7 +1088,11 @@ void launchHaloPush(const HaloPushArgs& a, cudaStream_t st) {
 // their own), so the wait cannot deadlock. A sender may legitimately be late (a rank writing
 // results, say), so the patience is long: timeoutNs (WENOEXT_HALO_TIMEOUT_S, default 600 s;
 // 0 = wait for ever, like a blocking receive) before the launch fails instead of hanging.
-__global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch, long long timeoutNs) {
+// On a timeout the kernel records 1 + (index of the late sender) in *status (host-mapped memory)
+// and returns: the follow-up cell launch sees it and does nothing, the host turns it into
+// WENOEXT_ERR_TIMEOUT. The CUDA context stays usable (no trap).
+__global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch, long long timeoutNs,
+                                 int32_t* status) {
     if ((int)threadIdx.x >= n) return;
     long long t0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -1071,15 +1100,18 @@ __global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch, lon
         __nanosleep(200);
         long long t1;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (timeoutNs > 0 && t1 - t0 > timeoutNs) __trap();
+        if (timeoutNs > 0 && t1 - t0 > timeoutNs) {
+            if (status) atomicCAS(status, 0, 1 + (int)threadIdx.x);
+            return;
+        }
     }
 }
-void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st) {
+void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st, int32_t* status) {
     static const long long timeoutNs = [] {
         const char* e = getenv("WENOEXT_HALO_TIMEOUT_S");
         return (long long)((e ? atof(e) : 600.0) * 1e9);
     }();
-    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch, timeoutNs);
+    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch, timeoutNs, status);
 }
 
 void launchPackHalo(const double* vals, int VS, const int32_t* sendIds, int64_t nSend,

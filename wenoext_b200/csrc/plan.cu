@@ -704,6 +704,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (!P) return 0;
     cudaSetDevice(P->device);
     if (P->h_fix) cudaFreeHost(P->h_fix);
+    if (P->haloStatusH) cudaFreeHost(P->haloStatusH);
     void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
                     P->tileCounter, P->haloFlags, P->pushDone, P->tmaMaps, P->records, P->recInfo, P->cellListInterior, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
@@ -821,6 +822,13 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
         allocOk = allocOk && cudaMalloc((void**)&P->valsIpc[i], std::max<size_t>(valsN, 1) * 8) == cudaSuccess;
     allocOk = allocOk && cudaMalloc((void**)&P->haloFlags, 32 * sizeof(int32_t)) == cudaSuccess;
     allocOk = allocOk && cudaMalloc((void**)&P->pushDone, sizeof(int32_t)) == cudaSuccess;
+    if (allocOk && !P->haloStatusH) {
+        allocOk = cudaHostAlloc((void**)&P->haloStatusH, sizeof(int32_t), cudaHostAllocMapped) == cudaSuccess;
+        if (allocOk) {
+            *P->haloStatusH = 0;
+            allocOk = cudaHostGetDevicePointer((void**)&P->haloStatusD, P->haloStatusH, 0) == cudaSuccess;
+        }
+    }
     P2PBlobHead head{};
     if (allocOk) {
         cudaMemset(P->haloFlags, 0, 32 * sizeof(int32_t));
@@ -1028,6 +1036,17 @@ extern "C" int wenoext_kernel_time(wenoext_plan* P, double* msSum, int* nLaunche
 //            [post exchange #2: coupled-patch values, swapData]
 //   phase 2  coupled patches: received values, cyclic copy, patch limiter
 // ---------------------------------------------------------------------------
+// a halo_wait_kernel of an earlier or of this call gave up (WENOEXT_HALO_TIMEOUT_S): sticky
+static int haloStatus(wenoext_plan* P) {
+    if (!P->haloStatusH) return 0;
+    const int32_t v = *reinterpret_cast<volatile int32_t*>(P->haloStatusH);
+    if (v == 0) return 0;
+    setError("halo exchange: the values of sender #" + std::to_string(v - 1) +
+             " of this rank's sender list did not arrive within WENOEXT_HALO_TIMEOUT_S; results of this and "
+             "later calls are invalid");
+    return WENOEXT_ERR_TIMEOUT;
+}
+
 static int ensureBuf(double** p, size_t* cap, size_t n) {
     if (*cap >= n && *p) return 0;
     if (*p) cudaFree(*p);
@@ -1067,6 +1086,7 @@ static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int work
         a.tmaElemOff[p] = P->tmaElemOff[p];
     }
     a.gateItem = gateItem;
+    a.abortFlag = P->haloStatusD;  // set only by a timed-out halo_wait_kernel
     if (gateItem >= 0 && !followUp) {
         a.gateFlags = P->haloFlags;
         a.nGate = P->nRecvPeers;
@@ -1265,7 +1285,7 @@ static int phase1(wenoext_plan* P) {
         if (int rc = launchCells(P, nullptr, P->nCells)) return rc;
     } else {
         if (P->p2p) {
-            launchHaloWait(P->haloFlags, P->nRecvPeers, P->haloEpoch, c.st);
+            launchHaloWait(P->haloFlags, P->nRecvPeers, P->haloEpoch, c.st, P->haloStatusD);
             if (P->nRecvPeers > 0) P->lastLaunches++;
         } else if (P->comm) {
             CUDA_TRY(cudaStreamWaitEvent(c.st, P->evB, 0));
@@ -1378,6 +1398,7 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
         setError("correction: NULL argument");
         return WENOEXT_ERR_INVALID;
     }
+    if (int rc = haloStatus(P)) return rc;
     if (nComp < 1 || (scheme != WENOEXT_SCHEME_UPWINDFIT && scheme != WENOEXT_SCHEME_UPWINDFIT01)) {
         setError("correction: bad scheme or nComp");
         return WENOEXT_ERR_INVALID;
@@ -1463,7 +1484,7 @@ static int finishCall(wenoext_plan* P, double* corr, double* fv, int memKind) {
     CUDA_TRY(cudaMemcpyAsync(corr, c.corr, (size_t)P->nFaces * c.nComp * 8, cudaMemcpyDeviceToHost, c.st));
     if (fv) CUDA_TRY(cudaMemcpyAsync(fv, c.fv, (size_t)P->nInt * c.nComp * 8, cudaMemcpyDeviceToHost, c.st));
     CUDA_TRY(cudaStreamSynchronize(c.st));
-    return 0;
+    return haloStatus(P);
 }
 
 // Host-buffer call on a serial plan, pipelined over slabs of cells: the H2D copy of
@@ -1714,7 +1735,8 @@ extern "C" int wenoext_interpolate(wenoext_plan* P, int scheme, int bounded, int
     if (memKind == WENOEXT_MEM_HOST && usePipeline(P, nComp, faceValue != nullptr)) {
         setBatch(P, 0);
         if (P->nProcs == 1) return pipelinedHostCall(P, vf, faceFlux, patchNbrField, corr, faceValue);
-        return pipelinedHostCallParallel(P, vf, faceFlux, patchNbrField, corr);
+        const int rc = pipelinedHostCallParallel(P, vf, faceFlux, patchNbrField, corr);
+        return rc ? rc : haloStatus(P);
     }
     for (int c0 = 0; c0 < nComp; c0 += cellKernelMaxCB(P->K)) {
         setBatch(P, c0);
@@ -1830,6 +1852,10 @@ extern "C" int wenoext_attach_local(wenoext_plan** plans, int nRanks) {
 extern "C" int wenoext_correction_begin(wenoext_plan* P, int scheme, int bounded, int nComp,
                                         const double* vf, const double* faceFlux,
                                         const double* patchNbrField, double* corr, void* stream) {
+    if (!P) {
+        setError("correction_begin: NULL plan");
+        return WENOEXT_ERR_INVALID;
+    }
     if (nComp > cellKernelMaxCB(P->K)) {
         setError("split-phase correction supports one component batch (nComp <= 3, 1 at order 4 in 3-D)");
         return WENOEXT_ERR_INVALID;

@@ -83,6 +83,9 @@ struct wenoext_plan {
     };
     std::vector<PushPeer> pushPeers;
     int32_t haloEpoch = 0;
+    // halo_wait_kernel's verdict, host-mapped: 0, or 1 + index of the sender that never delivered
+    int32_t* haloStatusH = nullptr;
+    int32_t* haloStatusD = nullptr;
     bool mergedLaunch = false;  // this call's boundary cells already went with the interior launch
     int cfgMerge = 1;           // WENOEXT_MERGE=0: separate interior / boundary launches
     int cfgP2P = 1;             // WENOEXT_P2P=0: NCCL send/recv for exchange #1
