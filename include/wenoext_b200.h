@@ -188,6 +188,22 @@ int wenoext_div(wenoext_plan* plan, int scheme, int bounded, int nComp, const do
                 const double* faceFlux, const double* patchNbrField, const double* bndValue,
                 const double* cellVolumes, double* div, int memKind, void* stream);
 
+/* No counterpart in the reference.
+ * correction() for callers that may not allocate device memory (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc): same result as wenoext_correction with device buffers, but
+ * this call performs no cudaMalloc / cudaFree / event creation. The cell kernel's scratch (the packed
+ * value buffer [nCells][VS] doubles, VS = 1, 2 or 4 for nComp = 1, 2, 3, and its tile counters) lives
+ * in a static __device__ array of WENOEXT_NOALLOC_MAX_VALUE_BYTES + 256 bytes that every GPU loading
+ * the library holds until exit. Limits: serial plans (no processor patches), device pointers only,
+ * nComp <= 3 (1 at order 4 in 3-D), nCells * VS * 8 <= WENOEXT_NOALLOC_MAX_VALUE_BYTES (64^3 cells of
+ * a vector field); anything beyond is rejected with WENOEXT_ERR_INVALID and a message. All calls on
+ * a device share the array, which keeps the last call's contents: calls that overlap on the GPU
+ * (different streams, plans or host threads) race - serialise them. Stream-ordered, returns at once.
+ *   vf [nCells][nComp], faceFlux [nFaces], corr [nFaces][nComp] out: DEVICE pointers. */
+#define WENOEXT_NOALLOC_MAX_VALUE_BYTES (8u << 20)
+int wenoext_correction_noalloc(wenoext_plan* plan, int scheme, int bounded, int nComp,
+                               const double* vf, const double* faceFlux, double* corr, void* stream);
+
 /* In-process ranks (several plans in one process, on one or more GPUs; used by
  * the single-GPU tests of the multi-rank path): plans[r] must have myProc == r.
  * Exchanges become device-to-device copies; drive them with the split-phase

@@ -84,6 +84,7 @@ SYMBOLS = {
     "wenoext_correction": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
     "wenoext_interpolate": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp]),
     "wenoext_div": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp]),
+    "wenoext_correction_noalloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]),
     "wenoext_attach_local": (C.c_int, [C.POINTER(vp), C.c_int]),
     "wenoext_correction_begin": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
     "wenoext_correction_exchange": (C.c_int, [vp]),

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "wenoext_b200", "csrc")
 LIB = os.path.join(ROOT, "wenoext_b200", "libwenoext_b200.so")
 
-CU_SOURCES = ["kernels.cu", "plan.cu", "pinv.cu"]
+CU_SOURCES = ["kernels.cu", "plan.cu", "pinv.cu", "noalloc.cu"]
 CPP_SOURCES = [
     "capi_setup.cpp",
     "setup/polymesh.cpp",

@@ -285,6 +285,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
         return WENOEXT_ERR_CUDA;
     }
     CUDA_TRY(cudaSetDevice(device));
+    noAllocResolve(device);  // address of the static scratch of wenoext_correction_noalloc (no allocation)
     wenoext_plan* P = new wenoext_plan();
     P->device = device;
     CUDA_TRY(cudaDeviceGetAttribute(&P->nSM, cudaDevAttrMultiProcessorCount, device));
@@ -1061,9 +1062,8 @@ static int ensureBuf(double** p, size_t* cap, size_t n) {
 // (device_plan.h); followUp: second launch of such a pair, counters kept, gate known open
 // `st`/`counterSlot`: launches of one call that may overlap (slabs on alternating streams) use
 // their own stream and their own pair of tile counters
-static int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase = 0,
-                       int gateItem = -1, bool followUp = false, cudaStream_t st = nullptr,
-                       int counterSlot = 0) {
+int wenoext::launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase, int gateItem,
+                         bool followUp, cudaStream_t st, int counterSlot) {
     if (nWork <= 0) return 0;
     wenoext_call c = P->call;
     if (st) c.st = st;
@@ -1337,7 +1337,7 @@ static int phase1(wenoext_plan* P) {
     return 0;
 }
 
-static int phase2(wenoext_plan* P) {
+int wenoext::phase2(wenoext_plan* P) {
     const wenoext_call& c = P->call;
     if (!P->hasCoupled) return 0;
     if (P->hasProcessor && !P->comm) {

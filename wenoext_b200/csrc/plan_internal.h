@@ -153,3 +153,13 @@ struct wenoext_plan {
     // launch geometry overrides (tuning): 0 = auto
     int cfgWarps = 0, cfgSlots = 0, cfgGrid = 0, cfgSmemKB = 0, cfgCells = 0;
 };
+
+namespace wenoext {
+// plan.cu: enqueue the fused cell kernel over work items [workBase, workBase + nWork) of `list`
+// (nullptr: cell = work item) with the call record P->call; coupled-patch epilogue
+int launchCells(wenoext_plan* P, const int32_t* list, int nWork, int workBase = 0, int gateItem = -1,
+                bool followUp = false, cudaStream_t st = nullptr, int counterSlot = 0);
+int phase2(wenoext_plan* P);
+// noalloc.cu: resolve the static scratch array's device address for `device` (current device)
+void noAllocResolve(int device);
+}  // namespace wenoext
