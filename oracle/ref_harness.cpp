@@ -12,7 +12,13 @@
  * Inputs: one wenoext_plan_desc per rank, i.e. the same flattened WENOBase content the GPU plan gets.
  */
 #include "of_stub/WENOBase.H"
+#ifdef WENO_HARNESS_SHIM
+// the same harness around the B200 shim classes (shim/Makefile): run-time selection then finds
+// shim/openfoam/makeWENOUpwindFitB200.C's entries instead of the reference's
+#include "wenoB200Registry.H"
+#else
 #include "WENOCoeff.H"
+#endif
 
 #include <atomic>
 #include <chrono>
@@ -196,6 +202,14 @@ WENOBase& WENOBase::fromDesc(const fvMesh& mesh, const wenoext_plan_desc& d)
     return *wb;
 }
 
+#ifdef WENO_HARNESS_SHIM
+//- the shim reads WENODict when it creates the plan of a mesh: dropping the plans re-arms the read
+template<class Type>
+struct WENODictReread
+{
+    static void arm() { wenoB200::clearRegistry(); }
+};
+#else
 //- WENOCoeff reads WENODict only at its first construction per Type (static printWENODict_,
 //  WENOCoeff.C:68-98, a protected member); a derived class may clear the flag so that a test can change
 //  the dictionary between runs inside one process
@@ -204,6 +218,7 @@ struct WENODictReread : public WENOCoeff<Type>
 {
     static void arm() { WENOCoeff<Type>::printWENODict_ = false; }
 };
+#endif
 }  // namespace Foam
 
 #include "ref_harness_run.inc"

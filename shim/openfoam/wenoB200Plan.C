@@ -1,10 +1,14 @@
 // OpenFOAM-side flattening of the WENOBase singleton into a wenoext_plan_desc.
-// SOURCE ONLY: needs OpenFOAM (v5-8 / v1912-v2012) and the WENOEXT headers to compile;
-// neither is available in the build image of this repository.
-// Add to libWENOEXT/ and link with -lwenoext_b200. See INTEGRATION.md.
-// libWENOEXT/B200/wenoB200Plan.C   (new file in the reference tree; needs OpenFOAM)
+// Compiles against OpenFOAM (v5-8 / v1912-v2012) and the WENOEXT headers: add to libWENOEXT/ and link
+// with -lwenoext_b200. In this repository it is compiled and run against the OpenFOAM
+// stand-in oracle/of_stub (`make -C shim check`, tests/test_shim.py).
+#include <map>
+#include <vector>
+
 #include "WENOBase.H"
+#include "wenoB200Registry.H"
 #include "wenoext_b200.h"
+#include "wenoext_setup.h"
 #include "processorFvPatch.H"
 #include "cyclicFvPatch.H"
 #include "emptyFvPatch.H"
@@ -27,7 +31,8 @@ wenoext_plan* planFromBase(const fvMesh& mesh, const WENOBase& wb, const label p
     Flat f;
     const label nCells = mesh.nCells(), nFaces = mesh.nFaces(), nInt = mesh.nInternalFaces();
     const label K = wb.degreesOfFreedom();                       // WENOBase.H:319-397 accessors
-    f.owner.assign(mesh.owner().begin(), mesh.owner().end());
+    // fvMesh::owner() is the internal-face slice; the ABI wants the owner of every face
+    f.owner.assign(mesh.faceOwner().begin(), mesh.faceOwner().end());
     f.neighbour.assign(mesh.neighbour().begin(), mesh.neighbour().end());
     f.cellFaceStart.push_back(0);
     forAll(mesh.cells(), c)
@@ -42,7 +47,14 @@ wenoext_plan* planFromBase(const fvMesh& mesh, const WENOBase& wb, const label p
         if (isA<processorFvPatch>(fp))
             { q.type = WENOEXT_PATCH_PROCESSOR; q.nbr = refCast<const processorFvPatch>(fp).neighbProcNo(); }
         else if (isA<cyclicFvPatch>(fp))
-            { q.type = WENOEXT_PATCH_CYCLIC; q.nbr = refCast<const cyclicFvPatch>(fp).neighbPatchID(); }
+        {
+            q.type = WENOEXT_PATCH_CYCLIC;
+            #ifdef FOAM_NEW_COUPLED_PATCHES
+            q.nbr = refCast<const cyclicFvPatch>(fp).nbrPatchID();
+            #else
+            q.nbr = refCast<const cyclicFvPatch>(fp).neighbPatchID();
+            #endif
+        }
         else if (isA<emptyFvPatch>(fp)) q.type = WENOEXT_PATCH_EMPTY;
         f.patches.push_back(q);
     }
@@ -157,7 +169,7 @@ wenoext_plan* planFromCache(const fvMesh& mesh, const label polOrder, const int 
     // labels are 32-bit here (WM_LABEL_SIZE=32); with 64-bit labels copy owner/neighbour to int32 first
     wenoext_mesh_desc m{};
     m.nCells = mesh.nCells(); m.nFaces = mesh.nFaces(); m.nInternalFaces = mesh.nInternalFaces();
-    m.owner = mesh.owner().cdata(); m.neighbour = mesh.neighbour().cdata();
+    m.owner = mesh.faceOwner().cdata(); m.neighbour = mesh.neighbour().cdata();
     m.nPatches = patches.size(); m.patches = patches.data();
 
     const fileName dir = mesh.time().path()/"constant"/("WENOBase" + Foam::name(polOrder));

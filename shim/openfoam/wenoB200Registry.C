@@ -1,4 +1,4 @@
-// See wenoB200Registry.H. SOURCE ONLY (needs OpenFOAM).
+// See wenoB200Registry.H.
 #include "wenoB200Registry.H"
 #include "IOdictionary.H"
 #include "Pstream.H"
@@ -18,10 +18,10 @@ namespace
 {
     struct Registry
     {
-        std::map<std::pair<const fvMesh*, label>, wenoext_plan*> plans;
+        std::map<std::pair<const fvMesh*, label>, PlanEntry> plans;
         ~Registry()
         {
-            for (auto& kv : plans) wenoext_plan_destroy(kv.second);
+            for (auto& kv : plans) kv.second.release();
         }
     };
     Registry& theRegistry()
@@ -29,6 +29,44 @@ namespace
         static Registry r;
         return r;
     }
+}
+
+
+double* PlanEntry::reserve(double*& buf, size_t& cap, const size_t n)
+{
+    if (cap < n || !buf)
+    {
+        if (buf) wenoext_host_free(buf);
+        buf = nullptr;
+        cap = 0;
+        void* p = nullptr;
+        if (wenoext_host_alloc((n ? n : 1)*sizeof(double), &p) != WENOEXT_OK)
+        {
+            FatalErrorInFunction << "wenoext_b200: " << wenoext_last_error() << exit(FatalError);
+        }
+        buf = static_cast<double*>(p);
+        cap = n;
+    }
+    return buf;
+}
+
+
+void PlanEntry::release()
+{
+    if (plan) wenoext_plan_destroy(plan);
+    if (flux) wenoext_host_free(flux);
+    if (pnf) wenoext_host_free(pnf);
+    if (corr) wenoext_host_free(corr);
+    plan = nullptr;
+    flux = pnf = corr = nullptr;
+    fluxCap = pnfCap = corrCap = 0;
+}
+
+
+void clearRegistry()
+{
+    for (auto& kv : theRegistry().plans) kv.second.release();
+    theRegistry().plans.clear();
 }
 
 
@@ -49,7 +87,7 @@ int deviceOfThisRank()
 }
 
 
-wenoext_plan* registry(const fvMesh& mesh, const WENOBase& base, const label polOrder)
+PlanEntry& registry(const fvMesh& mesh, const WENOBase& base, const label polOrder)
 {
     auto& plans = theRegistry().plans;
     const auto key = std::make_pair(&mesh, polOrder);
@@ -57,9 +95,17 @@ wenoext_plan* registry(const fvMesh& mesh, const WENOBase& base, const label pol
     if (it != plans.end()) return it->second;
 
     // system/WENODict: the reference's keys with the reference's defaults (WENOCoeff.C:41-48, :87-89)
+    // opened exactly as the reference does (WENOCoeff.C:70-80)
     IOdictionary WENODict
     (
-        IOobject("WENODict", mesh.time().path()/"system", mesh, IOobject::READ_IF_PRESENT, IOobject::NO_WRITE)
+        IOobject
+        (
+            "WENODict",
+            mesh.time().caseSystem(),
+            mesh,
+            IOobject::READ_IF_PRESENT,
+            IOobject::NO_WRITE
+        )
     );
     const scalar p   = WENODict.lookupOrDefault<scalar>("p", 4.0);
     const scalar dm  = WENODict.lookupOrDefault<scalar>("dm", 1000.0);
@@ -93,8 +139,9 @@ wenoext_plan* registry(const fvMesh& mesh, const WENOBase& base, const label pol
         }
     }
 
-    plans[key] = plan;
-    return plan;
+    PlanEntry& e = plans[key];
+    e.plan = plan;
+    return e;
 }
 
 }

@@ -17,5 +17,7 @@ def _built():
     """Build the in-tree libraries once (no-op when up to date)."""
     from wenoext_b200 import build
     build.build_product()
+    build.build_setup()
     build.build_oracle()
     build.build_test_hooks()
+    build.build_shim_check()

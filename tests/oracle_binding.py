@@ -188,11 +188,12 @@ def _send_list(case, to):
 
 
 def correction_distributed(orc, case, scheme, bounded, vf, flux, p=4.0, dm=1000.0, eps=1e-40,
-                           bugCompat=1):
+                           bugCompat=1, group=None):
     """One process per rank (torch.distributed, any backend with send/recv): the same
     two exchange steps as the reference's MPI run - collectData (WENOCoeff.C:224-296)
     and swapData (WENOUpwindFit.C:326-385) - around the per-rank oracle calls.
-    `case` already had exchange_halo_lists_distributed()."""
+    `case` already had exchange_halo_lists_distributed(). `group`: a process group whose backend
+    moves CPU tensors (gloo) when the default group is NCCL."""
     import torch
     import torch.distributed as dist
 
@@ -205,11 +206,11 @@ def correction_distributed(orc, case, scheme, bounded, vf, flux, p=4.0, dm=1000.
         n = case.desc.receiveHaloSize[q]
         if q != me and n:
             recv_bufs[q] = torch.empty((n, nComp), dtype=torch.float64)
-            reqs.append(dist.irecv(recv_bufs[q], src=q))
+            reqs.append(dist.irecv(recv_bufs[q], src=q, group=group))
     for q in range(R):
         ids = _send_list(case, q)
         if q != me and len(ids):
-            reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(vf[ids])), dst=q))
+            reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(vf[ids])), dst=q, group=group))
     for r in reqs:
         r.wait()
     segs = [recv_bufs[q].numpy() for q in range(R) if q in recv_bufs]
@@ -226,8 +227,8 @@ def correction_distributed(orc, case, scheme, bounded, vf, flux, p=4.0, dm=1000.
         mine = np.concatenate([ud[start - nI:start - nI + size], vf[case.owner[start:start + size]]])
         theirs = torch.empty(mine.shape, dtype=torch.float64)
         bufs.append((start, size, theirs))
-        reqs.append(dist.irecv(theirs, src=nbr))
-        reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(mine)), dst=nbr))
+        reqs.append(dist.irecv(theirs, src=nbr, group=group))
+        reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(mine)), dst=nbr, group=group))
     for r in reqs:
         r.wait()
     for start, size, theirs in bufs:
@@ -269,8 +270,10 @@ class ReferenceBuild:
     """Runs WENOUpwindFit<Type>::correction / WENOUpwindFit01<Type>::correction of the reference
     itself on one case (serial) or a list of per-rank cases (one thread per MPI rank)."""
 
-    def __init__(self, cases):
+    def __init__(self, cases, lib_path=None):
         path, self.isa = _ref_so_path()
+        if lib_path:
+            path, self.isa = lib_path, "shim"
         self.L = C.CDLL(path)
         self.L.weno_ref_create.restype = vp
         self.L.weno_ref_create.argtypes = [C.c_int, vp]
@@ -328,3 +331,55 @@ class ReferenceBuild:
         if want_weights:
             return (out[0], wts[0]) if self.serial_input else (out, wts)
         return out[0] if self.serial_input else out
+
+
+class ExpandedCase:
+    """The same case with one private copy of the pseudo-inverse per (cell, stencil) instead of the
+    matrixDB-style de-duplicated pool: the CPU then streams the same matrix bytes as the GPU's
+    per-cell records ("expanded per-cell matrices"). Only the matrix pool of the
+    descriptor changes; everything else is shared with `case` (which must stay alive)."""
+
+    def __init__(self, case):
+        from wenoext_b200 import _capi
+        d = case.desc
+        nS = int(d.nStencils)
+        sm = np.ctypeslib.as_array(d.stencilMatrix, shape=(nS,))
+        nU = int(d.nUniqueMatrices)
+        ms = np.ctypeslib.as_array(d.matrixStart, shape=(nU + 1,))
+        mc = np.ctypeslib.as_array(d.matrixCols, shape=(nU,))
+        md = np.ctypeslib.as_array(d.matrixData, shape=(int(ms[-1]),))
+        live = np.where(sm >= 0)[0]
+        sizes = (ms[1:] - ms[:-1])[sm[live]]
+        self._start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        self._cols = np.ascontiguousarray(mc[sm[live]], dtype=np.int32)
+        # gather: element k of copy i comes from ms[sm[live[i]]] + k
+        src0 = np.repeat(ms[sm[live]], sizes)
+        within = np.arange(int(self._start[-1]), dtype=np.int64) - np.repeat(self._start[:-1], sizes)
+        self._data = np.ascontiguousarray(md[src0 + within])
+        self._sm = np.full(nS, -1, dtype=np.int32)
+        self._sm[live] = np.arange(len(live), dtype=np.int32)
+        self.desc = _capi.PlanDesc()
+        C.memmove(C.addressof(self.desc), C.addressof(d), C.sizeof(_capi.PlanDesc))
+        self.desc.stencilMatrix = self._sm.ctypes.data_as(_capi.i32p)
+        self.desc.nUniqueMatrices = len(live)
+        self.desc.matrixStart = self._start.ctypes.data_as(_capi.i64p)
+        self.desc.matrixCols = self._cols.ctypes.data_as(_capi.i32p)
+        self.desc.matrixData = self._data.ctypes.data_as(_capi.f64p)
+        self._base = case
+        for k in ("nCells", "nFaces", "nInternalFaces", "nDvt", "owner", "neighbour", "patches", "C", "Sf",
+                  "myProc", "nProcs"):
+            if hasattr(case, k):
+                setattr(self, k, getattr(case, k))
+        self.matrix_bytes = int(self._data.nbytes)
+
+
+SHIM_SO = os.path.join(ROOT, "shim", "_build", "libweno_shim_check.so")
+
+
+class ShimBuild(ReferenceBuild):
+    """The same harness around the B200 shim classes (shim/openfoam/*.C compiled against oracle/of_stub
+    by `make -C shim check`): WENOUpwindFit<Type> / WENOUpwindFit01<Type> selected at run time, with
+    correction() going through libwenoext_b200.so to the GPU. Serial cases."""
+
+    def __init__(self, case):
+        super().__init__(case, lib_path=SHIM_SO)

@@ -14,27 +14,48 @@ from wenoext_b200 import _capi
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def declared_functions():
-    txt = open(os.path.join(ROOT, "include", "wenoext_b200.h")).read()
+def declared_functions(header="wenoext_b200.h"):
+    txt = open(os.path.join(ROOT, "include", header)).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     return sorted(set(re.findall(r"^(?:int|const char\*)\s+(wenoext_\w+)\s*\(", txt, flags=re.M)))
 
 
 def test_every_declared_symbol_is_exported_and_bound():
-    names = declared_functions()
-    assert len(names) >= 29
-    raw = C.CDLL(_capi.LIB_PATH)
-    for nm in names:
-        assert hasattr(raw, nm), f"{nm} declared in the header but not exported"
-    assert sorted(_capi.SYMBOLS) == names
-    wx.lib()  # sets restype/argtypes for all of them, raises on a missing one
+    for header, path, table in (("wenoext_b200.h", _capi.LIB_PATH, _capi.SYMBOLS),
+                                ("wenoext_setup.h", _capi.SETUP_LIB_PATH, _capi.SETUP_SYMBOLS)):
+        names = declared_functions(header)
+        assert len(names) >= 10
+        raw = C.CDLL(path)
+        for nm in names:
+            assert hasattr(raw, nm), f"{nm} declared in {header} but not exported by {path}"
+        assert sorted(table) == names
+    wx.lib().product()  # sets restype/argtypes for all of them, raises on a missing one
+    wx.lib().setup()
+
+
+def test_setup_library_has_no_cuda_and_cpu_users_do_not_map_the_product_library():
+    """The descriptor producers live in libwenoext_setup.so (plain C++): building a case and running the
+    CPU checkers must not load the GPU library (the reference arm mapped the product .so)."""
+    import subprocess
+    import sys
+    code = (
+        "import wenoext_b200 as wx, numpy as np\n"
+        "from wenoext_b200 import _capi\n"
+        "from tests.oracle_binding import Oracle\n"
+        "c = wx.BoxCase((5, 5, 5), 2)\n"
+        "Oracle('c').correction(c, 0, 1, np.zeros(c.nCells), np.zeros(c.nFaces))\n"
+        "maps = open('/proc/self/maps').read()\n"
+        "assert 'libwenoext_setup.so' in maps\n"
+        "assert 'libwenoext_b200.so' not in maps and not _capi.product_loaded()\n"
+        "assert 'libcudart' not in maps\n")
+    subprocess.run([sys.executable, "-c", code], check=True, cwd=ROOT)
 
 
 def test_struct_layouts_match_the_header(tmp_path):
     """sizeof of every public struct as gcc lays it out from the header == the ctypes mirror"""
     import subprocess
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include "wenoext_b200.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
+    src.write_text('#include <stdio.h>\n#include "wenoext_setup.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
                    'sizeof(wenoext_patch),sizeof(wenoext_plan_desc),sizeof(wenoext_plan_info),sizeof(wenoext_box_spec),'
                    'sizeof(wenoext_setup_params),sizeof(wenoext_mesh_desc),sizeof(int));return 0;}\n')
     exe = tmp_path / "sz"

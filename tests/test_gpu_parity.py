@@ -305,3 +305,48 @@ def test_plans_on_two_devices_in_one_process():
             assert H.normwise_err(np.asarray(got).reshape(want.shape), want) < TOL
         finally:
             plan.destroy()
+
+
+@pytest.mark.parametrize("host", [True, False], ids=["host", "device"])
+def test_set_face_flux_once_per_time_step(host):
+    """faceFlux_ is the same field for every correction() of a time step (WENOUpwindFit.H:75): uploaded
+    once with wenoext_set_face_flux, later calls pass faceFlux = NULL and give the same bits."""
+    import torch
+    case = wx.BoxCase((40, 40, 36), 2)  # large enough for the slab-pipelined host path
+    plan = wx.Plan(case.desc)
+    try:
+        flux = H.face_flux(case.Sf, U=(1.0, -1.0, 0.5), zero_frac=0.02)
+        fields = [_fields(case, 3, seed=3), np.ascontiguousarray(_fields(case, 1, seed=4)).reshape(-1)]
+        conv = (lambda x: x) if host else (lambda x: torch.from_numpy(x).cuda())
+        back = (lambda x: np.asarray(x)) if host else (lambda x: x.cpu().numpy())
+        want = [back(plan.correction(FIT, 1, conv(v), conv(flux))) for v in fields]
+        with pytest.raises(wx.WenoextError):
+            plan.correction(FIT, 1, conv(fields[0]), None)
+        plan.set_face_flux(conv(flux))
+        for v, w in zip(fields, want):
+            got = back(plan.correction(FIT, 1, conv(v), None))
+            np.testing.assert_array_equal(got, w)
+        plan.set_face_flux(None)
+        with pytest.raises(wx.WenoextError):
+            plan.correction(FIT, 1, conv(fields[0]), None)
+    finally:
+        plan.destroy()
+
+
+def test_pinned_host_buffers_from_the_library():
+    """wenoext_host_alloc memory through the host-buffer call: same result as pageable numpy arrays."""
+    case = wx.BoxCase((40, 40, 36), 2)
+    plan = wx.Plan(case.desc)
+    try:
+        vf = _fields(case, 3, seed=6)
+        flux = H.rotating_flux(case)
+        want = np.asarray(plan.correction(FIT, 1, vf, flux))
+        pv, pf = wx.pinned_empty(vf.shape), wx.pinned_empty(flux.shape)
+        po = wx.pinned_empty((case.nFaces, 3))
+        pv[...] = vf
+        pf[...] = flux
+        po[...] = np.nan
+        plan.correction(FIT, 1, pv, pf, out=po)
+        np.testing.assert_array_equal(np.asarray(po), want)
+    finally:
+        plan.destroy()

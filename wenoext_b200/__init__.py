@@ -26,9 +26,9 @@ import numpy as np
 from . import _capi
 from ._capi import (MEM_DEVICE, MEM_HOST, PATCH_CYCLIC, PATCH_EMPTY, PATCH_GENERIC,
                     PATCH_PROCESSOR, SCHEME_UPWINDFIT, SCHEME_UPWINDFIT01, WenoextError, check,
-                    lib)
+                    check_setup, lib)
 
-__all__ = ["BoxCase", "CachedCase", "WENOBase", "Plan", "WENOUpwindFit", "WENOUpwindFit01", "WenoextError",
+__all__ = ["pinned_empty", "BoxCase", "CachedCase", "WENOBase", "Plan", "WENOUpwindFit", "WENOUpwindFit01", "WenoextError",
            "exchange_halo_lists", "exchange_halo_lists_distributed", "attach_local",
            "correction_local", "nccl_unique_id", "SCHEME_UPWINDFIT", "SCHEME_UPWINDFIT01",
            "PATCH_GENERIC", "PATCH_PROCESSOR", "PATCH_CYCLIC", "PATCH_EMPTY"]
@@ -66,7 +66,7 @@ class BoxCase:
         prm = _capi.SetupParams(order, extendRatio, int(bestConditioned), maxCondition,
                                 int(checkCondition), nThreads, int(useClassCache), int(gpuPinv), device)
         h = C.c_void_p()
-        check(L.wenoext_setup_box(C.byref(box), C.byref(prm), myProc, C.byref(h)))
+        check_setup(L.wenoext_setup_box(C.byref(box), C.byref(prm), myProc, C.byref(h)))
         self._h = h
         self.order = order
         self.nProcs = int(np.prod(nProc))
@@ -80,7 +80,7 @@ class BoxCase:
     def _refresh(self):
         L = lib()
         self.desc = _capi.PlanDesc()
-        check(L.wenoext_setup_desc(self._h, C.byref(self.desc)))
+        check_setup(L.wenoext_setup_desc(self._h, C.byref(self.desc)))
         d = self.desc
         self.nCells, self.nFaces, self.nInternalFaces = d.nCells, d.nFaces, d.nInternalFaces
         self.nDvt = d.nDvt
@@ -95,29 +95,29 @@ class BoxCase:
         # Cell::empty cells get zero correction (WENOCoeff.C:333)
         self.emptyCells = self.stencilsID[ses[css[:-1]]] == _capi.CELL_EMPTY
         cc, sf = _capi.f64p(), _capi.f64p()
-        check(L.wenoext_setup_geometry(self._h, C.byref(cc), C.byref(sf)))
+        check_setup(L.wenoext_setup_geometry(self._h, C.byref(cc), C.byref(sf)))
         self.C = _np_view(cc, (d.nCells, 3), np.float64)       # mesh.C()
         self.Sf = _np_view(sf, (d.nFaces, 3), np.float64)      # mesh.Sf()
 
     def write_cache(self, directory, labelBytes=4, simdDoubles=8):
         """WENOBase::writeList (WENOBase.C:1265-1312): the eleven files of
         constant/WENOBase<order>/ in the reference's binary format."""
-        check(lib().wenoext_cache_write(self._h, str(directory).encode(), labelBytes, simdDoubles))
+        check_setup(lib().wenoext_cache_write(self._h, str(directory).encode(), labelBytes, simdDoubles))
 
     def mesh_desc(self):
         """Mesh addressing (owner, neighbour, cells, patches) as a wenoext_mesh_desc."""
         m = _capi.MeshDesc()
-        check(lib().wenoext_setup_mesh(self._h, C.byref(m)))
+        check_setup(lib().wenoext_setup_mesh(self._h, C.byref(m)))
         return m
 
     def halo_request(self, proc):
         ids, n = _capi.i32p(), C.c_int64()
-        check(lib().wenoext_setup_halo_request(self._h, proc, C.byref(ids), C.byref(n)))
+        check_setup(lib().wenoext_setup_halo_request(self._h, proc, C.byref(ids), C.byref(n)))
         return _np_view(ids, (n.value,), np.int32).copy()
 
     def set_send_halo(self, proc, ids):
         ids = np.ascontiguousarray(ids, dtype=np.int32)
-        check(lib().wenoext_setup_set_send_halo(self._h, proc, ids.ctypes.data_as(_capi.i32p),
+        check_setup(lib().wenoext_setup_set_send_halo(self._h, proc, ids.ctypes.data_as(_capi.i32p),
                                                 ids.size))
         self._refresh()
 
@@ -143,7 +143,7 @@ class CachedCase(BoxCase):
             # `directory` is an OpenFOAM case (or processor<N>) directory: the cache from
             # constant/WENOBase<order>/, the addressing from constant/polyMesh/
             h = C.c_void_p()
-            check(lib().wenoext_case_read(str(directory).encode(), caseOrder, myProc, labelBytes,
+            check_setup(lib().wenoext_case_read(str(directory).encode(), caseOrder, myProc, labelBytes,
                                           C.byref(h)))
             self._finish(h, myProc, WENODict, geometry)
             return
@@ -163,7 +163,7 @@ class CachedCase(BoxCase):
                 keep.append(pn)
             keep += [owner, neighbour, parr]
         h = C.c_void_p()
-        check(lib().wenoext_cache_read(str(directory).encode(), C.byref(mesh), myProc, labelBytes,
+        check_setup(lib().wenoext_cache_read(str(directory).encode(), C.byref(mesh), myProc, labelBytes,
                                        C.byref(h)))
         self._finish(h, myProc, WENODict, geometry)
 
@@ -212,6 +212,35 @@ def exchange_halo_lists_distributed(case):
             case.set_send_halo(p, np.asarray(allreq[p][case.myProc], dtype=np.int32))
 
 
+class _PinnedArray(np.ndarray):
+    """ndarray over wenoext_host_alloc memory; `_owner` frees it when the last view is gone"""
+    _owner = None
+
+
+class _PinnedOwner:
+    def __init__(self, addr):
+        self.addr = addr
+
+    def __del__(self):
+        try:
+            lib().wenoext_host_free(self.addr)
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array in page-locked host memory from wenoext_host_alloc (freed with the array): what a
+    host-side caller stages its fields through so that the library can overlap copies and kernels."""
+    count = int(np.prod(shape))
+    n = count * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    check(lib().wenoext_host_alloc(n, C.byref(p)))
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=count).reshape(shape).view(_PinnedArray)
+    arr._owner = _PinnedOwner(p.value)
+    return arr
+
+
 class Plan:
     """Device plan (wenoext_plan): owns all device memory of one (mesh, order)."""
 
@@ -232,6 +261,21 @@ class Plan:
 
     def attach_nccl(self, uid, rank, nRanks):
         check(lib().wenoext_attach_nccl(self._h, uid, rank, nRanks))
+
+    def set_face_flux(self, faceFlux, stream=None):
+        """wenoext_set_face_flux: upload the flux field once per time step; later calls may pass
+        faceFlux=None (WENOUpwindFit.H:75: faceFlux_ is the same field for every correction() of a step)."""
+        if faceFlux is None:
+            check(lib().wenoext_set_face_flux(self._h, None, MEM_HOST, None))
+            self._step_flux = None
+            return
+        pf, kind, keep = self._ptr(faceFlux)
+        st = 0
+        if kind == MEM_DEVICE:
+            import torch
+            st = (stream if stream is not None else torch.cuda.current_stream(faceFlux.device)).cuda_stream
+        check(lib().wenoext_set_face_flux(self._h, pf, kind, st))
+        self._step_flux = keep if kind == MEM_DEVICE else None  # a device pointer is kept by the library
 
     def alg_bytes(self, nComp):
         return int(self.info.algBytesFixed + nComp * self.info.algBytesPerComp)
@@ -271,9 +315,9 @@ class Plan:
         tensors are used in place on `stream` (default: torch's current stream)."""
         nComp = 1 if vf.ndim == 1 else int(vf.shape[1])
         pv, kind, kv = self._ptr(vf)
-        pf, kindf, kf = self._ptr(faceFlux)
+        pf, kindf, kf = self._ptr(faceFlux)  # None: the field given to set_face_flux
         pn, _, kn = self._ptr(patchNbrField)
-        if kind != kindf:
+        if faceFlux is not None and kind != kindf:
             raise WenoextError("vf and faceFlux must live in the same memory space")
         shape = (self.nFaces,) if vf.ndim == 1 else (self.nFaces, nComp)
         if out is None:

@@ -1,8 +1,10 @@
-"""ctypes binding of include/wenoext_b200.h (the C-ABI drop-in boundary).
+"""ctypes binding of include/wenoext_b200.h (the C-ABI drop-in boundary, libwenoext_b200.so) and of
+include/wenoext_setup.h (host-side descriptor producers, libwenoext_setup.so).
 
-No torch types cross this boundary: plain pointers and sizes only. The library
-must exist in-tree (built by `python -m wenoext_b200.build`); there is no
-fallback of any kind when it is missing.
+No torch types cross this boundary: plain pointers and sizes only. The libraries must exist in-tree
+(built by `python -m wenoext_b200.build`); there is no fallback of any kind when one is missing.
+Each library is loaded on first use of one of its symbols, so CPU-only users of a descriptor (the
+oracle, the reference build) never map the GPU library.
 """
 import ctypes as C
 import os
@@ -10,6 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # WENOEXT_LIB: developer aid, an alternative build of the same library (kernel variants)
 LIB_PATH = os.environ.get("WENOEXT_LIB") or os.path.join(_HERE, "libwenoext_b200.so")
+SETUP_LIB_PATH = os.path.join(_HERE, "libwenoext_setup.so")
 
 # constants of include/wenoext_b200.h
 CELL_LOCAL, CELL_DELETED, CELL_EMPTY = -1, -4, -10
@@ -84,6 +87,9 @@ SYMBOLS = {
     "wenoext_correction": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
     "wenoext_interpolate": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp]),
     "wenoext_div": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp]),
+    "wenoext_host_alloc": (C.c_int, [C.c_uint64, C.POINTER(vp)]),
+    "wenoext_host_free": (C.c_int, [vp]),
+    "wenoext_set_face_flux": (C.c_int, [vp, vp, C.c_int, vp]),
     "wenoext_correction_noalloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]),
     "wenoext_attach_local": (C.c_int, [C.POINTER(vp), C.c_int]),
     "wenoext_correction_begin": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
@@ -92,44 +98,80 @@ SYMBOLS = {
     "wenoext_last_launch_count": (C.c_int, [vp]),
     "wenoext_enable_kernel_timing": (C.c_int, [vp, C.c_int]),
     "wenoext_kernel_time": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_int]),
+    "wenoext_pinv_batched": (C.c_int, [C.c_int32, C.c_int32, i32p, i64p, f64p, C.c_double, f64p, i32p, f64p,
+                                        i32p, C.c_int]),
+}
+
+# every symbol include/wenoext_setup.h declares
+SETUP_SYMBOLS = {
+    "wenoext_setup_last_error": (C.c_char_p, []),
     "wenoext_setup_box": (C.c_int, [C.POINTER(BoxSpec), C.POINTER(SetupParams), C.c_int32, C.POINTER(vp)]),
     "wenoext_setup_destroy": (C.c_int, [vp]),
     "wenoext_setup_desc": (C.c_int, [vp, C.POINTER(PlanDesc)]),
     "wenoext_setup_halo_request": (C.c_int, [vp, C.c_int32, C.POINTER(i32p), C.POINTER(C.c_int64)]),
     "wenoext_setup_set_send_halo": (C.c_int, [vp, C.c_int32, i32p, C.c_int64]),
     "wenoext_setup_geometry": (C.c_int, [vp, C.POINTER(f64p), C.POINTER(f64p)]),
-    "wenoext_pinv_batched": (C.c_int, [C.c_int32, C.c_int32, i32p, i64p, f64p, C.c_double, f64p, i32p, f64p,
-                                        i32p, C.c_int]),
     "wenoext_cache_write": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
     "wenoext_cache_read": (C.c_int, [C.c_char_p, C.POINTER(MeshDesc), C.c_int32, C.c_int, C.POINTER(vp)]),
     "wenoext_case_read": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int, C.POINTER(vp)]),
     "wenoext_setup_mesh": (C.c_int, [vp, C.POINTER(MeshDesc)]),
 }
 
-_lib = None
-
-
 class WenoextError(RuntimeError):
     pass
 
 
+class _Libs:
+    """Attribute access resolves a symbol in the library that exports it (loaded on first use)."""
+
+    def __init__(self):
+        self._handles = {}
+
+    def _load(self, path, table):
+        if path not in self._handles:
+            if not os.path.exists(path):
+                raise WenoextError(
+                    f"{path} is missing: build it with `python -m wenoext_b200.build` "
+                    "(wenoext_b200 has no CPU or eager fallback)")
+            L = C.CDLL(path)
+            for name, (res, args) in table.items():
+                fn = getattr(L, name)
+                fn.restype = res
+                fn.argtypes = args
+            self._handles[path] = L
+        return self._handles[path]
+
+    def product(self):
+        return self._load(LIB_PATH, SYMBOLS)
+
+    def setup(self):
+        return self._load(SETUP_LIB_PATH, SETUP_SYMBOLS)
+
+    def __getattr__(self, name):
+        if name in SETUP_SYMBOLS:
+            return getattr(self.setup(), name)
+        if name in SYMBOLS:
+            return getattr(self.product(), name)
+        raise AttributeError(name)
+
+
+_libs = _Libs()
+
+
 def lib():
-    """Load libwenoext_b200.so; raise if it has not been built (no fallback)."""
-    global _lib
-    if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise WenoextError(
-                f"{LIB_PATH} is missing: build it with `python -m wenoext_b200.build` "
-                "(wenoext_b200 has no CPU or eager fallback)")
-        L = C.CDLL(LIB_PATH)
-        for name, (res, args) in SYMBOLS.items():
-            fn = getattr(L, name)
-            fn.restype = res
-            fn.argtypes = args
-        _lib = L
-    return _lib
+    """The C ABI; raises when a library has not been built (no fallback)."""
+    return _libs
+
+
+def product_loaded():
+    return LIB_PATH in _libs._handles
 
 
 def check(rc):
     if rc != 0:
-        raise WenoextError(f"wenoext error {rc}: {lib().wenoext_last_error().decode()}")
+        raise WenoextError(f"wenoext error {rc}: {_libs.wenoext_last_error().decode()}")
+
+
+def check_setup(rc):
+    if rc != 0:
+        raise WenoextError(f"wenoext setup error {rc}: {_libs.wenoext_setup_last_error().decode()}")

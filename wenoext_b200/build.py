@@ -1,6 +1,9 @@
 """Build the in-tree native libraries.
 
-  libwenoext_b200.so   product: host setup (C++), device plan + kernels (CUDA, sm_100a), C ABI
+  libwenoext_b200.so   product: device plan + kernels (CUDA, sm_100a), C ABI (include/wenoext_b200.h)
+  libwenoext_setup.so  host-side producers of plan descriptors (plain C++, no CUDA): box stand-in of the
+                       WENOBase constructor, reader/writer of constant/WENOBase<order>/, polyMesh reader
+                       (include/wenoext_setup.h)
   oracle/libweno_oracle.so, oracle/_ref/libweno_oracle_blaze.so   checker (tests only)
 
 nvcc cross-compiles sm_100a without a GPU. Run as `python -m wenoext_b200.build`.
@@ -12,6 +15,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "wenoext_b200", "csrc")
 LIB = os.path.join(ROOT, "wenoext_b200", "libwenoext_b200.so")
+SETUP_LIB = os.path.join(ROOT, "wenoext_b200", "libwenoext_setup.so")
 
 CU_SOURCES = ["kernels.cu", "plan.cu", "pinv.cu", "noalloc.cu"]
 CPP_SOURCES = [
@@ -62,7 +66,7 @@ def build_product(force=False, verbose=False):
     if kdebug != os.path.exists(stamp):
         force = True
         (open(stamp, "w").close() if kdebug else os.remove(stamp))
-    for src in CU_SOURCES + CPP_SOURCES:
+    for src in CU_SOURCES:
         path = os.path.join(CSRC, src)
         obj = os.path.join(objdir, src.replace("/", "_") + ".o")
         hs = _headers()
@@ -82,11 +86,38 @@ def build_product(force=False, verbose=False):
     return LIB
 
 
+def build_setup(force=False):
+    """libwenoext_setup.so with the host compiler (no CUDA headers, no CUDA runtime)."""
+    objdir = os.path.join(ROOT, "build", "obj_setup")
+    os.makedirs(objdir, exist_ok=True)
+    hs = [h for h in _headers() if os.sep + "setup" + os.sep in h or h.endswith("wenoext_b200.h")]
+    hs.append(os.path.join(ROOT, "include", "wenoext_setup.h"))
+    objs, rebuilt = [], False
+    for src in CPP_SOURCES:
+        path = os.path.join(CSRC, src)
+        obj = os.path.join(objdir, src.replace("/", "_") + ".o")
+        if force or _newer(obj, [path] + hs):
+            subprocess.run(["g++", "-O3", "-std=c++17", "-fPIC", "-I", os.path.join(ROOT, "include"),
+                            "-I", CSRC, "-c", path, "-o", obj], check=True)
+            rebuilt = True
+        objs.append(obj)
+    if rebuilt or not os.path.exists(SETUP_LIB):
+        subprocess.run(["g++", "-shared", "-o", SETUP_LIB] + objs + ["-lpthread", "-ldl"], check=True)
+    return SETUP_LIB
+
+
 def build_oracle(force=False):
     odir = os.path.join(ROOT, "oracle")
     subprocess.run(["make", "-C", odir] + (["-B"] if force else []), check=True,
                    stdout=subprocess.DEVNULL)
     return os.path.join(odir, "libweno_oracle.so")
+
+
+def build_shim_check():
+    """shim/_build/libweno_shim_check.so: the OpenFOAM-side shim compiled against the OpenFOAM stand-in
+    (needs /root/reference for List3D.H / Blaze; elsewhere the prebuilt file is kept)."""
+    subprocess.run(["make", "-C", os.path.join(ROOT, "shim"), "check"], check=True, stdout=subprocess.DEVNULL)
+    return os.path.join(ROOT, "shim", "_build", "libweno_shim_check.so")
 
 
 def build_test_hooks(force=False):
@@ -105,5 +136,7 @@ def build_test_hooks(force=False):
 if __name__ == "__main__":
     force = "--force" in sys.argv
     print(build_product(force=force, verbose="-v" in sys.argv))
+    print(build_setup(force=force))
     print(build_oracle(force=force))
     print(build_test_hooks(force=force))
+    print(build_shim_check())

@@ -1,17 +1,62 @@
-// extern "C" wrappers of the host setup stand-in (see include/wenoext_b200.h).
+// extern "C" wrappers of the host-side descriptor producers (include/wenoext_setup.h):
+// libwenoext_setup.so, plain C++ without CUDA. Kept apart from the product library so that the
+// CPU-only users of a descriptor (the reference build, the oracle) never map the GPU library.
 #include <cstring>
 #include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
 
-#include "../../include/wenoext_b200.h"
-#include "plan_internal.h"
+#include <dlfcn.h>
+
+#include "../../include/wenoext_setup.h"
+#include "setup/pinv_device.h"
 #include "setup/box_fast.h"
 #include "setup/weno_setup.h"
 #include "setup/wenobase_cache.h"
 
 using namespace wenoext;
+
+namespace {
+thread_local std::string g_setupError;
+void setError(const std::string& s) { g_setupError = s; }
+}  // namespace
+
+extern "C" const char* wenoext_setup_last_error(void) { return g_setupError.c_str(); }
+
+// The optional device batch of the pseudo-inverses (wenoext_setup_params::gpuPinv) lives in the product
+// library; it is looked up at run time in libwenoext_b200.so next to this library, so that nothing here
+// links against CUDA.
+int wenoext::pinvBatchedDevice(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
+                               const double* A, double minCondition, double* Ainv, int32_t* nZeros,
+                               double* condition, int32_t* converged, std::string& err) {
+    typedef int (*Fn)(int32_t, int32_t, const int32_t*, const int64_t*, const double*, double, double*, int32_t*,
+                      double*, int32_t*, int);
+    typedef const char* (*ErrFn)(void);
+    static void* handle = nullptr;
+    if (!handle) {
+        Dl_info info{};
+        std::string dir = ".";
+        if (dladdr((const void*)&wenoext_setup_last_error, &info) && info.dli_fname) {
+            const std::string self(info.dli_fname);
+            const size_t slash = self.rfind('/');
+            if (slash != std::string::npos) dir = self.substr(0, slash);
+        }
+        handle = dlopen((dir + "/libwenoext_b200.so").c_str(), RTLD_NOW | RTLD_LOCAL);
+        if (!handle) handle = dlopen("libwenoext_b200.so", RTLD_NOW | RTLD_LOCAL);
+    }
+    Fn fn = handle ? (Fn)dlsym(handle, "wenoext_pinv_batched") : nullptr;
+    if (!fn) {
+        err = "gpuPinv: libwenoext_b200.so (wenoext_pinv_batched) not found next to libwenoext_setup.so";
+        return WENOEXT_ERR_SETUP;
+    }
+    const int rc = fn(nMat, n, rows, start, A, minCondition, Ainv, nZeros, condition, converged, device);
+    if (rc) {
+        ErrFn ef = (ErrFn)dlsym(handle, "wenoext_last_error");
+        err = ef ? ef() : "wenoext_pinv_batched failed";
+    }
+    return rc;
+}
 
 struct wenoext_setup {
     HostPlan hp;

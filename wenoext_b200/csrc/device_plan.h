@@ -216,6 +216,9 @@ void launchDivKernel(const DivKernelArgs& a, cudaStream_t st);
 void launchGatherRows(const double* src, const int32_t* rows, int64_t n, int nComp, double* dst,
                       cudaStream_t st);
 
+void launchScatterRows(const double* src, const int32_t* rows, int64_t n, int nComp, double* dst,
+                       cudaStream_t st);
+
 int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t smemBytes,
                      cudaStream_t st);
 size_t cellKernelSmemBytes(const CellKernelArgs& a);

@@ -1033,6 +1033,23 @@ void launchGatherRows(const double* src, const int32_t* rows, int64_t n, int nCo
     gather_rows_kernel<<<(unsigned)((n * nComp + 255) / 256), 256, 0, st>>>(src, rows, n, nComp, dst);
 }
 
+// dst[rows[i]][:] = src[rows[i]][:] — dst may be page-locked HOST memory (zero-copy stores over the
+// host link): puts the few faces that boundary cells finalise late straight into the caller's result
+// buffer, behind the bulk copies of the ranges that contain them
+__global__ void scatter_rows_kernel(const double* __restrict__ src, const int32_t* __restrict__ rows, int64_t n,
+                                    int nComp, double* __restrict__ dst) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * nComp) return;
+    const int64_t r = i / nComp;
+    const size_t at = (size_t)rows[r] * nComp + (size_t)(i - r * nComp);
+    dst[at] = src[at];
+}
+void launchScatterRows(const double* src, const int32_t* rows, int64_t n, int nComp, double* dst,
+                       cudaStream_t st) {
+    if (n <= 0) return;
+    scatter_rows_kernel<<<(unsigned)((n * nComp + 255) / 256), 256, 0, st>>>(src, rows, n, nComp, dst);
+}
+
 void launchDivKernel(const DivKernelArgs& a, cudaStream_t st) {
     const int64_t n = (int64_t)a.nCells * a.nComp;
     if (n <= 0) return;

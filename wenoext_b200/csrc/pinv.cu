@@ -15,7 +15,6 @@
 
 #include "../../include/wenoext_b200.h"
 #include "plan_internal.h"
-#include "setup/pinv_device.h"
 
 namespace {
 
@@ -143,7 +142,7 @@ struct DevBuf {
 
 namespace wenoext {
 
-int pinvBatchedDevice(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
+int pinvBatchedImpl(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
                       const double* A, double minCondition, double* Ainv, int32_t* nZeros, double* condition,
                       int32_t* converged, std::string& err) {
     if (nMat <= 0) return 0;
@@ -222,7 +221,7 @@ extern "C" int wenoext_pinv_batched(int32_t nMat, int32_t n, const int32_t* rows
             return WENOEXT_ERR_INVALID;
         }
     std::string err;
-    const int rc = wenoext::pinvBatchedDevice(device, nMat, n, rows, start, A, minCondition, Ainv, nZeros,
+    const int rc = wenoext::pinvBatchedImpl(device, nMat, n, rows, start, A, minCondition, Ainv, nZeros,
                                               condition, converged, err);
     if (rc) wenoext::setError(err);
     return rc;

@@ -706,6 +706,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     cudaSetDevice(P->device);
     if (P->h_fix) cudaFreeHost(P->h_fix);
     if (P->haloStatusH) cudaFreeHost(P->haloStatusH);
+    if (P->stepFluxOwned) cudaFree(P->stepFluxOwned);
     void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
                     P->tileCounter, P->haloFlags, P->pushDone, P->tmaMaps, P->records, P->recInfo, P->cellListInterior, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
@@ -1394,8 +1395,12 @@ static bool usePipeline(const wenoext_plan* P, int nComp, bool wantFaceValue) {
 static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
                        const double* flux, const double* pnf, double* corr, double* fv,
                        int memKind, void* stream) {
-    if (!P || !vf || !flux || !corr) {
+    if (!P || !vf || !corr) {
         setError("correction: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (!flux && !P->stepFlux) {
+        setError("correction: faceFlux is NULL and no field was given to wenoext_set_face_flux");
         return WENOEXT_ERR_INVALID;
     }
     if (int rc = haloStatus(P)) return rc;
@@ -1423,16 +1428,17 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
     const size_t nB = (size_t)P->nBnd * nComp, nO = nF * nComp, nFV = (size_t)P->nInt * nComp;
     if (memKind == WENOEXT_MEM_HOST) {
         if (int rc = ensureBuf(&P->s_vf, &P->s_vfCap, nV)) return rc;
-        if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
+        if (flux)
+            if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
         if (int rc = ensureBuf(&P->s_corr, &P->s_corrCap, nO)) return rc;
         // (the pipelined path copies slab by slab, see pipelinedHostCall)
         const bool pipelined = usePipeline(P, nComp, fv != nullptr);
         if (!pipelined) {
             CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
-            CUDA_TRY(cudaMemcpyAsync(P->s_flux, flux, nF * 8, cudaMemcpyHostToDevice, st));
+            if (flux) CUDA_TRY(cudaMemcpyAsync(P->s_flux, flux, nF * 8, cudaMemcpyHostToDevice, st));
         }
         c.vf = P->s_vf;
-        c.flux = P->s_flux;
+        c.flux = flux ? P->s_flux : P->stepFlux;
         c.corr = P->s_corr;
         if (pnf && nB) {
             if (int rc = ensureBuf(&P->s_pnf, &P->s_pnfCap, nB)) return rc;
@@ -1445,7 +1451,7 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
         }
     } else {
         c.vf = vf;
-        c.flux = flux;
+        c.flux = flux ? flux : P->stepFlux;
         c.pnf = pnf;
         c.corr = corr;
         c.fv = fv;
@@ -1522,7 +1528,7 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         if (nv > haveVf)
             CUDA_TRY(cudaMemcpyAsync(dvf + (size_t)haveVf * nComp, vf + (size_t)haveVf * nComp,
                                      (size_t)(nv - haveVf) * nComp * 8, cudaMemcpyHostToDevice, P->sIn));
-        if (nf > haveFlux)
+        if (flux && nf > haveFlux)
             CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
                                      cudaMemcpyHostToDevice, P->sIn));
         // the pack follows its copy on the input stream, so that a slab's kernel depends on
@@ -1570,6 +1576,46 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
                                  (size_t)(P->nInt - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
     CUDA_TRY(cudaStreamSynchronize(P->sOut));
     CUDA_TRY(cudaStreamSynchronize(c.st));
+    return 0;
+}
+
+// Tail of a pipelined host-buffer call on a parallel plan: the faces [sent, nFaces) follow in one
+// copy; the internal faces below `sent` that boundary cells finalised after their range had been
+// copied (fixFaces) are put in place last. If the caller's buffer is page-locked the device writes
+// them straight into it (zero-copy stores ordered behind the bulk copies on the output stream);
+// otherwise they travel compactly and the host scatters them.
+static int finishParallelHostCall(wenoext_plan* P, double* corr, int sent, cudaEvent_t evEnd) {
+    const wenoext_call& c = P->call;
+    const int nComp = c.nComp;
+    const size_t nFix = P->fixFacesH.size();
+    double* mapped = nullptr;
+    if (nFix && !getenv("WENOEXT_HOST_SCATTER")) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, corr) == cudaSuccess && at.type == cudaMemoryTypeHost)
+            mapped = static_cast<double*>(at.devicePointer);
+        cudaGetLastError();
+    }
+    if (nFix && !mapped) {
+        launchGatherRows(c.corr, P->fixFacesD, (int64_t)nFix, nComp, P->d_fix, c.st);
+        P->lastLaunches++;
+    }
+    CUDA_TRY(cudaEventRecord(evEnd, c.st));
+    CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
+    if (nFix && !mapped)
+        CUDA_TRY(cudaMemcpyAsync(P->h_fix, P->d_fix, nFix * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                             (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    if (mapped) {
+        launchScatterRows(c.corr, P->fixFacesD, (int64_t)nFix, nComp, mapped, P->sOut);
+        P->lastLaunches++;
+    }
+    CUDA_TRY(cudaStreamSynchronize(P->sOut));
+    CUDA_TRY(cudaStreamSynchronize(c.st));
+    if (nFix && !mapped)
+        for (size_t i = 0; i < nFix; ++i) {
+            const size_t f = (size_t)P->fixFacesH[i];
+            for (int k = 0; k < nComp; ++k) corr[f * nComp + k] = P->h_fix[i * nComp + k];
+        }
     return 0;
 }
 
@@ -1638,7 +1684,7 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
                 pushHalo(P, P->sIn);
                 pushed = true;
             }
-            if (nf > haveFlux)
+            if (flux && nf > haveFlux)
                 CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
                                          cudaMemcpyHostToDevice, P->sIn));
             haveFlux = nf;
@@ -1663,26 +1709,13 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
         }
         if (int rc = phase1(P)) return rc;  // halo wait, boundary cells, exchange #2
         if (int rc = phase2(P)) return rc;  // coupled patches
-        launchGatherRows(c.corr, P->fixFacesD, (int64_t)nFix, nComp, P->d_fix, c.st);
-        if (nFix) P->lastLaunches++;
-        CUDA_TRY(cudaEventRecord(evEnd, c.st));
-        CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
-        if (nFix)
-            CUDA_TRY(cudaMemcpyAsync(P->h_fix, P->d_fix, nFix * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
-        CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
-                                 (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
-        CUDA_TRY(cudaStreamSynchronize(P->sOut));
-        CUDA_TRY(cudaStreamSynchronize(c.st));
-        for (size_t i = 0; i < nFix; ++i) {
-            const size_t f = (size_t)P->fixFacesH[i];
-            for (int k = 0; k < nComp; ++k) corr[f * nComp + k] = P->h_fix[i * nComp + k];
-        }
-        return 0;
+        return finishParallelHostCall(P, corr, sent, evEnd);
     }
     CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.vf), vf, (size_t)P->nCells * nComp * 8,
                              cudaMemcpyHostToDevice, P->sIn));
-    CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.flux), flux, (size_t)P->nFaces * 8,
-                             cudaMemcpyHostToDevice, P->sIn));
+    if (flux)
+        CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.flux), flux, (size_t)P->nFaces * 8,
+                                 cudaMemcpyHostToDevice, P->sIn));
     if (pnf && P->nBnd)
         CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.pnf), pnf, (size_t)P->nBnd * nComp * 8,
                                  cudaMemcpyHostToDevice, P->sIn));
@@ -1704,19 +1737,42 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
     }
     if (int rc = phase1(P)) return rc;  // boundary cells, exchange #2
     if (int rc = phase2(P)) return rc;  // coupled patches
-    launchGatherRows(c.corr, P->fixFacesD, (int64_t)nFix, nComp, P->d_fix, c.st);
-    if (nFix) P->lastLaunches++;
-    CUDA_TRY(cudaEventRecord(evEnd, c.st));
-    CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
-    if (nFix)
-        CUDA_TRY(cudaMemcpyAsync(P->h_fix, P->d_fix, nFix * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
-    CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
-                             (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
-    CUDA_TRY(cudaStreamSynchronize(P->sOut));
-    CUDA_TRY(cudaStreamSynchronize(c.st));
-    for (size_t i = 0; i < nFix; ++i) {
-        const size_t f = (size_t)P->fixFacesH[i];
-        for (int k = 0; k < nComp; ++k) corr[f * nComp + k] = P->h_fix[i * nComp + k];
+    return finishParallelHostCall(P, corr, sent, evEnd);
+}
+
+extern "C" int wenoext_host_alloc(uint64_t bytes, void** out) {
+    if (!out) {
+        setError("host_alloc: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    *out = nullptr;
+    CUDA_TRY(cudaHostAlloc(out, std::max<uint64_t>(bytes, 1), cudaHostAllocPortable));
+    return 0;
+}
+extern "C" int wenoext_host_free(void* p) {
+    if (p) CUDA_TRY(cudaFreeHost(p));
+    return 0;
+}
+
+extern "C" int wenoext_set_face_flux(wenoext_plan* P, const double* faceFlux, int memKind, void* stream) {
+    if (!P) {
+        setError("set_face_flux: NULL plan");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (!faceFlux) {  // forget the field: later calls must pass faceFlux again
+        P->stepFlux = nullptr;
+        return 0;
+    }
+    CUDA_TRY(cudaSetDevice(P->device));
+    if (memKind == WENOEXT_MEM_HOST) {
+        if (int rc = ensureBuf(&P->stepFluxOwned, &P->stepFluxCap, (size_t)P->nFaces)) return rc;
+        CUDA_TRY(cudaMemcpyAsync(P->stepFluxOwned, faceFlux, (size_t)P->nFaces * 8, cudaMemcpyHostToDevice,
+                                 (cudaStream_t)stream));
+        // host buffer: the caller may reuse it as soon as this returns
+        CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+        P->stepFlux = P->stepFluxOwned;
+    } else {
+        P->stepFlux = faceFlux;
     }
     return 0;
 }
@@ -1758,8 +1814,12 @@ extern "C" int wenoext_correction(wenoext_plan* P, int scheme, int bounded, int 
 extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
                            const double* faceFlux, const double* patchNbrField, const double* bndValue,
                            const double* cellVolumes, double* div, int memKind, void* stream) {
-    if (!P || !vf || !faceFlux || !cellVolumes || !div || (P->nBnd > 0 && !bndValue)) {
+    if (!P || !vf || !cellVolumes || !div || (P->nBnd > 0 && !bndValue)) {
         setError("div: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (!faceFlux && !P->stepFlux) {
+        setError("div: faceFlux is NULL and no field was given to wenoext_set_face_flux");
         return WENOEXT_ERR_INVALID;
     }
     if (P->nProcs > 1 && !P->comm) {
@@ -1775,19 +1835,21 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
     const size_t nV = (size_t)P->nCells * nComp, nF = (size_t)P->nFaces, nB = (size_t)P->nBnd * nComp;
     if (int rc = ensureBuf(&P->d_corr, &P->d_corrCap, nF * nComp)) return rc;
     if (int rc = ensureBuf(&P->d_fv, &P->d_fvCap, (size_t)P->nInt * nComp)) return rc;
-    const double *dvf = vf, *dflux = faceFlux, *dpnf = patchNbrField, *dbnd = bndValue, *dvol = cellVolumes;
+    const double *dvf = vf, *dflux = faceFlux ? faceFlux : P->stepFlux, *dpnf = patchNbrField, *dbnd = bndValue,
+                 *dvol = cellVolumes;
     double* ddiv = div;
     if (memKind == WENOEXT_MEM_HOST) {
         // stage everything once; the reconstruction below then runs on device pointers
         if (int rc = ensureBuf(&P->s_vf, &P->s_vfCap, nV)) return rc;
-        if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
+        if (faceFlux)
+            if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
         if (int rc = ensureBuf(&P->d_vol, &P->d_volCap, (size_t)P->nCells)) return rc;
         if (int rc = ensureBuf(&P->d_div, &P->d_divCap, nV)) return rc;
         CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(P->s_flux, faceFlux, nF * 8, cudaMemcpyHostToDevice, st));
+        if (faceFlux) CUDA_TRY(cudaMemcpyAsync(P->s_flux, faceFlux, nF * 8, cudaMemcpyHostToDevice, st));
         CUDA_TRY(cudaMemcpyAsync(P->d_vol, cellVolumes, (size_t)P->nCells * 8, cudaMemcpyHostToDevice, st));
         dvf = P->s_vf;
-        dflux = P->s_flux;
+        dflux = faceFlux ? P->s_flux : P->stepFlux;
         dvol = P->d_vol;
         ddiv = P->d_div;
         if (nB) {

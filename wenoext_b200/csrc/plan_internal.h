@@ -115,6 +115,10 @@ struct wenoext_plan {
     int32_t* cellFacesSortedD = nullptr;
     double *d_corr = nullptr, *d_fv = nullptr, *d_bnd = nullptr, *d_vol = nullptr, *d_div = nullptr;
     size_t d_corrCap = 0, d_fvCap = 0, d_bndCap = 0, d_volCap = 0, d_divCap = 0;
+    // wenoext_set_face_flux: the flux field of this time step (device); stepFluxOwned if uploaded here
+    const double* stepFlux = nullptr;
+    double* stepFluxOwned = nullptr;
+    size_t stepFluxCap = 0;
     // staging for host-pointer calls
     double *s_vf = nullptr, *s_flux = nullptr, *s_pnf = nullptr, *s_corr = nullptr,
            *s_fv = nullptr;
