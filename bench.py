@@ -3,20 +3,22 @@
 
   python bench.py --gpus N --steps K --warmup W              (our arm, N=1)
   python -m torch.distributed.run ... bench.py --gpus N ...  (our arm, N>1)
-  python bench.py --impl reference ...                       (CPU arm: the oracle
-        port of the reference loop on all host threads; the reference library
-        itself needs OpenFOAM and cannot be built)
+  python bench.py --impl reference ...                       (CPU arm: the reference's OWN hot-path code,
+        oracle/_ref/libweno_ref_*.so = its unmodified translation units compiled against the OpenFOAM
+        stand-in oracle/of_stub, one thread per emulated MPI rank on all host cores; the oracle port is
+        the fallback when that build is absent)
+  python bench.py --config c2|c3|c4|c4tets|c5                (BASELINE.json configs as one command each)
 
-Workload (BASELINE.json configs[2], the one the metric is quoted on): 128^3 hex
-box per GPU, `WENOUpwindFit 2 1` (order 2, bounded), vector field (3 components
-share every LSmatrix read). N>1: weak scaling, the global box is decomposed
-`simple`-style into N blocks of 128^3 (2x1x1, 2x2x1, 2x2x2), halo exchange of
-stencil cell values and processor-patch faces over NCCL.
+Workload (BASELINE.json configs[2], the one the metric is quoted on): 128^3 hex box per GPU,
+`WENOUpwindFit 2 1` (order 2, bounded), vector field (3 components share every LSmatrix read). N>1: weak
+scaling, the global box is decomposed `simple`-style into N blocks of 128^3 (2x1x1, 2x2x1, 2x2x2), halo
+exchange of stencil cell values and processor-patch faces between the GPUs.
 
 One JSON line on stdout (rank 0). A "step" = one correction() call.
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -29,7 +31,16 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-NPROC = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+NPROC = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2), 16: (4, 2, 2), 32: (4, 4, 2)}
+
+# BASELINE.json configs as presets (c1, the 20x20x1 cavity, is a parity-test case: tests/test_golden.py)
+CONFIGS = {
+    "c2": dict(n=64, order=2, bounded=1, ncomp=1),
+    "c3": dict(n=128, order=2, bounded=1, ncomp=3),
+    "c4": dict(n=96, order=3, bounded=0, ncomp=3),
+    "c4tets": dict(n=32, order=2, bounded=1, ncomp=3, tets=6, best_conditioned=True),
+    "c5": dict(n=128, order=2, bounded=1, ncomp=3),  # = c3 per GPU; run with --gpus 8 under torchrun
+}
 
 
 def log(*a):
@@ -42,6 +53,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default=None, choices=sorted(CONFIGS), help="BASELINE.json config preset")
     ap.add_argument("--n", type=int, default=128, help="cells per direction per GPU")
     ap.add_argument("--order", type=int, default=2)
     ap.add_argument("--ncomp", type=int, default=3)
@@ -51,7 +63,16 @@ def parse():
     ap.add_argument("--best-conditioned", action="store_true", help="WENODict bestConditioned true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the bench fields")
+    ap.add_argument("--sustained-s", type=float, default=2.0,
+                    help="seconds of back-to-back steps for the `sustained` sub-record (0: skip)")
+    ap.add_argument("--cpu-sample-n", type=int, default=64,
+                    help="cells per direction of the block the cpu_baseline sub-records are timed on")
+    a = ap.parse_args()
+    if a.config:
+        for k, v in CONFIGS[a.config].items():
+            setattr(a, k, v)
+    return a
 
 
 def workload_name(a, N):
@@ -74,9 +95,8 @@ def case_kwargs(a):
 
 def make_fields(case, ncomp, rank=0):
     """synthetic fields of SURVEY.md 8(d): psi = sum sin(pi x_i) family + 1e-3 noise,
-    flux of a rotating velocity (mixed signs) with a few exact zeros"""
+    flux of a constant velocity (mixed signs over the face orientations) with a few exact zeros"""
     from tests import helpers as H
-    lo, hi = case.C.min(axis=0), case.C.max(axis=0)
     v = H.vector_field(case.C, seed=1 + rank)
     if ncomp <= 3:
         vf = np.ascontiguousarray(v[:, :ncomp])
@@ -86,11 +106,13 @@ def make_fields(case, ncomp, rank=0):
     return vf, phi
 
 
+
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks/throttle reasons DURING a timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
@@ -111,20 +133,18 @@ class ClockSampler:
             self.lines.append(ln.strip())
 
     def mark(self):
-        """start of the timed region: earlier samples are dropped (unless nothing follows)"""
+        """start of a timed region; returns the index of its first sample"""
         t0 = time.time()
         while self.proc and not self.lines and time.time() - t0 < 5.0:
             time.sleep(0.01)  # nvidia-smi still starting
-        self.first = len(self.lines)
+        return len(self.lines)
 
-    def stop(self):
+    def window(self, first, last=None):
+        """median clock, max clock, power and throttle reasons of the samples [first, last)"""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        self.t.join(timeout=2)
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        timed = self.lines[getattr(self, "first", 0):]
+        timed = self.lines[first:last]
+        sm, mx, pw, reasons = [], [], [], set()
         for ln in (timed if timed else self.lines[-3:]):
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
@@ -132,14 +152,40 @@ class ClockSampler:
             try:
                 sm.append(float(f[0]))
                 mx.append(float(f[1]))
+                pw.append(float(f[2]))
             except ValueError:
                 continue
-            for nm, val in zip(names, f[3:7]):
+            for nm, val in zip(self.NAMES, f[3:7]):
                 if val.lower().startswith("active"):
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None,
                 "sm_max_mhz": float(max(mx)) if mx else None,
+                "power_w": float(np.median(pw)) if pw else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+
+def reduce_clocks(clocks, N, dev):
+    """rank 0 reports the slowest GPU's median clock and the union of the throttle reasons"""
+    if N == 1:
+        return clocks
+    import torch
+    import torch.distributed as dist
+    names = ClockSampler.NAMES
+    cm = torch.tensor([clocks["sm_mhz"] or 0.0] + [float(nm in clocks["reasons"]) for nm in names],
+                      dtype=torch.float64, device=dev)
+    lo, hi = cm.clone(), cm.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    clocks = dict(clocks)
+    clocks["sm_mhz"] = lo[0].item() or None
+    clocks["reasons"] = [nm for i, nm in enumerate(names) if hi[1 + i].item() > 0]
+    clocks["ranks"] = N
+    return clocks
 
 
 def host_threads():
@@ -159,52 +205,128 @@ def cpu_model():
     return "unknown"
 
 
-def oracle_for_cpu():
-    """the checker used as the timed CPU leg: Blaze-backed variant (the reference's
-    own arithmetic library) when oracle/_ref was built, else the plain-C port"""
-    from tests.oracle_binding import BLAZE_SO, Oracle
-    if os.path.exists(BLAZE_SO):
-        return Oracle("blaze"), "oracle/_ref Blaze-backed restatement of WENOCoeff.C/WENOUpwindFit.C"
-    return Oracle("c"), "oracle/ plain-C restatement of WENOCoeff.C/WENOUpwindFit.C"
+def cpu_ranks(limit=None):
+    """ranks of the emulated `mpirun -np <cores>`: the largest power of two the host threads allow"""
+    T = host_threads() if limit is None else min(limit, host_threads())
+    return max(k for k in NPROC if k <= max(T, 1))
+
+
+def global_internal_faces(n, tets):
+    """internal faces of the n^3 box as ONE mesh (what a decomposed run reconstructs in total)"""
+    if not tets:
+        return 3 * n * n * (n - 1)
+    return None  # counted from the serial case where needed
+
+
+def build_cpu_cases(a, n, R):
+    """the n^3 box decomposed `simple`-style over R emulated MPI ranks, halo lists exchanged"""
+    import wenoext_b200 as wx
+    if R == 1:
+        return [wx.BoxCase((n,) * 3, a.order, **case_kwargs(a))]
+    cases = [wx.BoxCase((n,) * 3, a.order, nProc=NPROC[R], myProc=r, **case_kwargs(a)) for r in range(R)]
+    wx.exchange_halo_lists(cases)
+    return cases
+
+
+def time_reference(a, cases, warmup, steps, expanded=False):
+    """seconds per correction() of the reference's own code on `cases` (one thread per rank, released
+    together, max over ranks inside the harness; methodology of the reference's performance test,
+    tests/Cases/performanceTest/src/main.C:157-164: N repeated calls, wall clock / N).
+    Returns (seconds, kind, description) — kind "reference" with oracle/_ref/libweno_ref_*.so, else the
+    oracle port ("port")."""
+    from tests.oracle_binding import (ExpandedCase, Oracle, ReferenceBuild, correction_multirank,
+                                      correction_threaded, reference_build_available)
+    fields = [make_fields(c, a.ncomp, r) for r, c in enumerate(cases)]
+    vfs, phis = [f[0] for f in fields], [f[1] for f in fields]
+    use = [ExpandedCase(c) for c in cases] if expanded else cases
+    serial = len(cases) == 1
+    if reference_build_available():
+        ref = ReferenceBuild(use[0] if serial else use)
+        call = lambda k: ref.correction("WENOUpwindFit", a.order, a.bounded, vfs[0] if serial else vfs,  # noqa: E731
+                                        phis[0] if serial else phis, repeat=k)
+        if warmup:
+            call(warmup)
+        call(steps)
+        what = (f"the reference's own WENOUpwindFit<Type>::correction (unmodified WENOUpwindFit.C / WENOCoeff.C "
+                f"/ Blaze 3.8 compiled against oracle/of_stub, {ref.isa}), {len(cases)} rank(s) as threads")
+        return ref.last_seconds, "reference", what
+    orc = Oracle("c")
+    if serial:
+        run = lambda: correction_threaded(orc, use[0], a.bounded, vfs[0], phis[0], 1)  # noqa: E731
+    else:
+        run = lambda: correction_multirank(orc, use, 0, a.bounded, vfs, phis)  # noqa: E731
+    for _ in range(warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run()
+    return (time.perf_counter() - t0) / steps, "port", "oracle/ plain-C restatement (reference build absent)"
 
 
 def run_reference(a):
-    """--impl reference: the CPU implementation of the path on all host threads.
-    libWENOEXT itself cannot be compiled without OpenFOAM, so this is
-    the oracle port, cell and face loops split over the host threads the way
-    `mpirun -np <cores>` splits the reference."""
+    """--impl reference: the reference's CPU implementation of the path on all host cores, the way
+    `mpirun -np <cores>` runs it: the per-GPU block of the workload decomposed over <cores> ranks
+    (threads here: no MPI on the box), collectData and swapData between them as the reference wrote them."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import wenoext_b200 as wx
-    from tests.oracle_binding import correction_threaded
+    R = cpu_ranks()
     t0 = time.time()
-    case = wx.BoxCase((a.n,) * 3, a.order, **case_kwargs(a))
-    log(f"[reference] setup {time.time() - t0:.1f}s, {case.nCells} cells")
-    vf, phi = make_fields(case, a.ncomp)
-    orc, what = oracle_for_cpu()
-    T = host_threads()
-    for _ in range(max(a.warmup, 1)):
-        correction_threaded(orc, case, a.bounded, vf, phi, T)
-    t0 = time.perf_counter()
-    for _ in range(a.steps):
-        correction_threaded(orc, case, a.bounded, vf, phi, T)
-    dt = (time.perf_counter() - t0) / a.steps
-    val = case.nInternalFaces / dt
+    cases = build_cpu_cases(a, a.n, R)
+    log(f"[reference] setup {time.time() - t0:.1f}s, {sum(c.nCells for c in cases)} cells on {R} ranks")
+    dt, kind, what = time_reference(a, cases, max(a.warmup, 1), a.steps)
+    faces = global_internal_faces(a.n, a.tets)
+    if faces is None:
+        faces = sum(c.nInternalFaces for c in cases) + sum(
+            size for c in cases for (pt, st, size, nb) in c.patches if pt == 1) // 2
+    val = faces / dt
     out = {
         "impl": "reference", "metric": "WENO-reconstructed faces/sec", "value": val,
         "unit": "faces/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a, a.gpus), "sample_cells": case.nCells,
-                   "sample_faces": case.nInternalFaces},
-        "cpu_baseline": {"value": val, "unit": "faces/s", "cores": T, "kind": "port",
-                         "cpu": cpu_model(),
-                         "sample": f"one full {a.n}^3 block (the per-GPU share of the workload) per step, {what}, "
-                                   f"de-duplicated matrices ({case.desc.nUniqueMatrices} unique)"},
+        "config": {"workload": workload_name(a, a.gpus), "sample_cells": int(sum(c.nCells for c in cases)),
+                   "sample_faces": int(faces)},
+        "cpu_baseline": {"value": val, "unit": "faces/s", "cores": R, "host_threads": host_threads(),
+                         "kind": kind, "cpu": cpu_model(),
+                         "sample": f"one full {a.n}^3 block (the per-GPU share of the workload) per step, decomposed "
+                                   f"over {R} ranks {NPROC[R]} with halo and patch exchange; {what}; de-duplicated "
+                                   f"matrices as the reference's matrixDB keeps them; at --gpus N > 1 the same block "
+                                   f"is timed (CPU throughput does not grow with the mesh)"},
         "e2e": {"value": val, "unit": "faces/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(out), flush=True)
+
+
+def cpu_baseline_record(a):
+    """cpu_baseline of our main line (N = 1, rank 0): the reference's own code on a bounded sample of
+    the workload (a --cpu-sample-n ^3 block with the workload's scheme and field type): serial (the
+    headline `value`, one core, like the reference's serial run), all cores, and serial with expanded
+    per-cell matrices (the same matrix bytes the GPU streams)."""
+    n = min(a.cpu_sample_n, a.n)
+    faces1 = global_internal_faces(n, a.tets)
+    serial = build_cpu_cases(a, n, 1)
+    if faces1 is None:
+        faces1 = serial[0].nInternalFaces
+    dt1, kind, what = time_reference(a, serial, 1, 3)
+    rec = {"value": faces1 / dt1, "unit": "faces/s", "cores": 1, "kind": kind, "cpu": cpu_model(),
+           "sample": f"{n}^3 block of the workload ({faces1} faces), 3 timed calls after 1 warm-up (handles built "
+                     f"before timing), serial; {what}; de-duplicated matrices ({serial[0].desc.nUniqueMatrices} unique)"}
+    try:
+        dtx, _, _ = time_reference(a, serial, 1, 3, expanded=True)
+        rec["expanded_matrices"] = {"value": faces1 / dtx, "unit": "faces/s", "cores": 1,
+                                    "sample": "same block, one private matrix copy per (cell, stencil): the matrix "
+                                              "bytes the GPU streams"}
+    except MemoryError:
+        rec["expanded_matrices"] = None
+    R = cpu_ranks()
+    if R > 1:
+        par = build_cpu_cases(a, n, R)
+        dtp, _, _ = time_reference(a, par, 1, 5)
+        rec["all_cores"] = {"value": faces1 / dtp, "unit": "faces/s", "cores": R, "host_threads": host_threads(),
+                            "sample": f"same block decomposed over {R} ranks {NPROC[R]} (threads), halo and patch "
+                                      f"exchange included"}
+    return rec
 
 
 def run_ours(a):
@@ -218,17 +340,16 @@ def run_ours(a):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != N:
-        if N == 1 and world == 1:
-            pass
-        else:
-            raise SystemExit(f"--gpus {N} needs torchrun with {N} ranks (WORLD_SIZE={world})")
+    if world != N and not (N == 1 and world == 1):
+        raise SystemExit(f"--gpus {N} needs torchrun with {N} ranks (WORLD_SIZE={world})")
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; wenoext_b200 has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    gloo = None
     if N > 1:
         dist.init_process_group("nccl", device_id=dev)
+        gloo = dist.new_group(backend="gloo")  # host-side exchanges of the oracle's distributed run
     px, py, pz = NPROC[N]
     t0 = time.time()
     case = wx.BoxCase((a.n * px, a.n * py, a.n * pz), a.order, nProc=(px, py, pz), myProc=rank,
@@ -236,12 +357,17 @@ def run_ours(a):
     if N > 1:
         wx.exchange_halo_lists_distributed(case)
     t_setup = time.time() - t0
+
+    def make_plan():
+        p = wx.Plan(case.desc, device=local)
+        if N > 1:
+            uid = [wx.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            p.attach_nccl(uid[0], rank, N)
+        return p
+
     t0 = time.time()
-    plan = wx.Plan(case.desc, device=local)
-    if N > 1:
-        uid = [wx.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        plan.attach_nccl(uid[0], rank, N)
+    plan = make_plan()
     t_plan = time.time() - t0
     info = plan.info
     log(f"[rank {rank}] setup {t_setup:.1f}s plan {t_plan:.1f}s cells {info.nCells} "
@@ -261,46 +387,96 @@ def run_ours(a):
     def step():
         plan.correction(FIT, a.bounded, vf, phi, out=out)
 
+    def timed(steps):
+        """K steps between barrier + synchronize, CUDA events on the launching stream, per-launch event
+        pairs of the cell kernel inside the library; returns (ms per step, kernel ms per step, launches),
+        both times the max over ranks"""
+        plan.enable_kernel_timing(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        launches = 0
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            step()
+            launches += plan.last_launch_count()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        k_ms, _ = plan.kernel_time()
+        plan.enable_kernel_timing(False)
+        t = torch.tensor([ms / steps, k_ms / steps], dtype=torch.float64, device=dev)
+        if N > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t[0].item(), t[1].item(), launches
+
     # every rank samples its own GPU; rank 0 reports the slowest. nvidia-smi needs a while to
     # start (longer with 8 of them), so it is started before the warm-up and only the samples
-    # taken during the timed region are used.
+    # taken during a timed region are used.
     sampler = ClockSampler(local)
     sampler.start()
     for _ in range(a.warmup):
         step()
-    # ---- timed region: device-resident inputs, K steps, CUDA events ----
-    plan.enable_kernel_timing(True)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches = 0
-    sampler.mark()
-    barrier()
-    e0.record()
-    for _ in range(a.steps):
-        step()
-        launches += plan.last_launch_count()
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    clocks = sampler.stop()
-    if N > 1:
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        cm = torch.tensor([clocks["sm_mhz"] or 0.0] + [float(nm in clocks["reasons"]) for nm in names],
-                          dtype=torch.float64, device=dev)
-        lo, hi = cm.clone(), cm.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        clocks["sm_mhz"] = lo[0].item() or None  # median under load of the slowest GPU
-        clocks["reasons"] = [nm for i, nm in enumerate(names) if hi[1 + i].item() > 0]
-        clocks["ranks"] = N
-    k_ms, k_n = plan.kernel_time()
-    plan.enable_kernel_timing(False)
-    t = torch.tensor([ms, k_ms / max(a.steps, 1)], dtype=torch.float64, device=dev)
+    # ---- timed region (the headline): device-resident inputs, EXACTLY K steps ----
+    first = sampler.mark()
+    ms_step, k_ms_launch, launches = timed(a.steps)
+    clocks = reduce_clocks(sampler.window(first, sampler.mark()), N, dev)
     tot = torch.tensor([faces, alg_bytes], dtype=torch.float64, device=dev)
     if N > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    ms_step = t[0].item() / a.steps
     value = tot[0].item() / (ms_step * 1e-3)
+
+    # ---- sustained: the same steps back to back for --sustained-s seconds, i.e. at the clocks a solver
+    # sees once the power cap has settled (the K-step region above is over before that happens) ----
+    sustained = None
+    if a.sustained_s > 0:
+        ks = max(a.steps, int(math.ceil(a.sustained_s * 1e3 / ms_step)))
+        timed(max(1, ks // 4))  # settle
+        first = sampler.mark()
+        s_ms, s_kms, _ = timed(ks)
+        s_clocks = reduce_clocks(sampler.window(first, sampler.mark()), N, dev)
+        sustained = {"steps": ks, "ms_per_step": s_ms, "value": tot[0].item() / (s_ms * 1e-3), "kernel_ms": s_kms,
+                     "clocks": s_clocks}
+    sampler.stop()
+
+    # ---- parity of exactly what was timed: this rank's result against the CPU oracle on the bench
+    # fields (N = 1: serial oracle over all host threads; N > 1: the oracle's distributed run, its two
+    # exchange steps over a gloo side group). The oracle is pinned to the reference's own code by
+    # tests/test_reference_build.py and the goldens. ----
+    parity = None
+    parity_fallback = None
+    if not a.no_parity:
+        from tests import helpers as H
+        from tests.oracle_binding import Oracle, correction_distributed, correction_threaded
+        step()
+        torch.cuda.synchronize()
+        got = out.cpu().numpy()
+        orc = Oracle("c")
+        if N == 1:
+            want = correction_threaded(orc, case, a.bounded, vf_h, phi_h, host_threads())
+        else:
+            want = correction_distributed(orc, case, FIT, a.bounded, vf_h, phi_h, group=gloo)
+        err = torch.tensor([H.normwise_err(got, np.asarray(want).reshape(got.shape))], dtype=torch.float64,
+                           device=dev)
+        if N > 1:
+            dist.all_reduce(err, op=dist.ReduceOp.MAX)
+        parity = err.item()
+        if N > 1:
+            # the NCCL send/recv transport of exchange #1 (WENOEXT_P2P=0) on a second plan, same fields
+            os.environ["WENOEXT_P2P"] = "0"
+            try:
+                p2 = make_plan()
+                out2 = torch.empty_like(out)
+                p2.correction(FIT, a.bounded, vf, phi, out=out2)
+                torch.cuda.synchronize()
+                e2 = torch.tensor([H.normwise_err(out2.cpu().numpy(), np.asarray(want).reshape(got.shape))],
+                                  dtype=torch.float64, device=dev)
+                dist.all_reduce(e2, op=dist.ReduceOp.MAX)
+                parity_fallback = e2.item()
+                dist.barrier()
+                p2.destroy()
+                del out2
+            finally:
+                del os.environ["WENOEXT_P2P"]
 
     # ---- e2e: the same call through the C ABI with HOST (pinned) buffers ----
     e2e = None
@@ -323,6 +499,11 @@ def run_ours(a):
                "ms_per_step": w.item() * 1e3,
                "h2d_bytes_per_step": int(vf_p.nbytes + phi_p.nbytes),
                "d2h_bytes_per_step": int(out_p.nbytes)}
+        if parity is not None:
+            ee = torch.tensor([float(np.abs(out_p - got).max())], dtype=torch.float64, device=dev)
+            if N > 1:
+                dist.all_reduce(ee, op=dist.ReduceOp.MAX)
+            e2e["max_abs_diff_vs_device_path"] = ee.item()
 
     if rank != 0:
         if N > 1:
@@ -335,15 +516,16 @@ def run_ours(a):
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    # DRAM traffic of the dominant kernel: taken from the committed ncu capture of this
-    # workload (profiles/traffic.json), null for workloads that were not captured
-    traffic = None
+    # DRAM traffic of the dominant kernel is not measured by this run: it comes from the committed ncu
+    # capture of the same workload (profiles/traffic.json), null for workloads that were not captured
+    traffic, traffic_src = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tj.get(workload_name(a, 1), {}).get("traffic_bytes_per_launch")
+        ent = tj.get(workload_name(a, 1), {})
+        traffic = ent.get("traffic_bytes_per_launch")
+        traffic_src = ent.get("source")
     except OSError:
         pass
-    k_ms_launch = t[1].item()  # fused cell kernel(s) per step, max over ranks
     achieved = alg_bytes / (k_ms_launch * 1e-3) / 1e9 if k_ms_launch > 0 else 0.0
     res = {
         "metric": "WENO-reconstructed faces/sec", "value": value, "unit": "faces/s",
@@ -359,26 +541,25 @@ def run_ours(a):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
+                     "traffic_source": (traffic_src or "committed ncu capture, not this run") if traffic else None,
                      "kernel": "weno_cell_kernel", "kernel_ms": k_ms_launch,
                      "alg_bytes_per_launch": alg_bytes,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks
                      else "fallback 6650 GB/s (of fallback)"},
     }
+    if sustained:
+        s_ach = alg_bytes / (sustained["kernel_ms"] * 1e-3) / 1e9 if sustained["kernel_ms"] > 0 else 0.0
+        sustained["roofline_frac"] = s_ach / peak
+        sustained["achieved_gbs"] = s_ach
+        res["sustained"] = sustained
     if e2e:
         res["e2e"] = e2e
+    if parity is not None:
+        res["parity_vs_oracle"] = parity
+        if parity_fallback is not None:
+            res["parity_vs_oracle_nccl_fallback"] = parity_fallback
     if N == 1 and not a.no_cpu_baseline:
-        from tests.oracle_binding import correction_threaded
-        orc, what = oracle_for_cpu()
-        t0 = time.perf_counter()
-        ref = correction_threaded(orc, case, a.bounded, vf_h, phi_h, 1)
-        dt = time.perf_counter() - t0
-        from tests import helpers as H
-        err = H.normwise_err(out.cpu().numpy(), ref)
-        res["cpu_baseline"] = {"value": case.nInternalFaces / dt, "unit": "faces/s", "cores": 1,
-                               "kind": "port", "cpu": cpu_model(),
-                               "sample": f"one full correction() of the same {a.n}^3 workload, "
-                                         f"serial, {what}"}
-        res["parity_vs_oracle"] = err
+        res["cpu_baseline"] = cpu_baseline_record(a)
     print(json.dumps(res), flush=True)
     if N > 1:
         dist.barrier()
