@@ -99,3 +99,87 @@ def test_nccl_ranks_match_oracle(world, mesh):
         assert p.exitcode == 0
     for r in range(world):
         assert max(got[r]) <= 1e-12, (r, got[r])
+
+
+def _timeout_worker(rank, world, port, q):
+    """rank 1 arrives 3 s late; rank 0 waits 0.5 s for its halo (WENOEXT_HALO_TIMEOUT_S)"""
+    import time
+
+    import torch
+    import torch.distributed as dist
+
+    import wenoext_b200 as wx
+    from tests import helpers as H
+    from tests.oracle_binding import Oracle
+
+    os.environ["WENOEXT_HALO_TIMEOUT_S"] = "0.5" if rank == 0 else "60"
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        cases = [wx.BoxCase((24, 16, 16), 2, nProc=NPROC[world], myProc=r) for r in range(world)]
+        wx.exchange_halo_lists(cases)
+        mine = cases[rank]
+        plan = wx.Plan(mine.desc, device=rank)
+        uid = [wx.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        plan.attach_nccl(uid[0], rank, world)
+        vf = H.vector_field(mine.C, seed=4)
+        fl = H.face_flux(mine.Sf, U=(1.0, -1.0, 0.5))
+        dist.barrier()
+        torch.cuda.synchronize()
+        res = {"rank": rank}
+        if rank == 1:
+            time.sleep(3.0)
+            plan.correction(0, 1, vf, fl)
+        else:
+            try:
+                plan.correction(0, 1, vf, fl)
+                res["first"] = "no error"
+            except wx.WenoextError as e:
+                res["first"] = str(e)
+            try:  # sticky: the plan's results can no longer be trusted
+                plan.correction(0, 1, vf, fl)
+                res["second"] = "no error"
+            except wx.WenoextError as e:
+                res["second"] = str(e)
+            # the CUDA context is alive: a fresh serial plan on the same device still works
+            serial = wx.BoxCase((8, 8, 8), 2, useClassCache=False)
+            p2 = wx.Plan(serial.desc, device=rank)
+            svf, sfl = H.vector_field(serial.C, seed=1), H.rotating_flux(serial)
+            got = p2.correction(0, 1, svf, sfl)
+            res["serial_err"] = H.normwise_err(np.asarray(got), Oracle("c").correction(serial, 0, 1, svf, sfl))
+            p2.destroy()
+        q.put(res)
+        q.close()
+        q.join_thread()  # flush before the hard exit below
+    finally:
+        os._exit(0)  # skip the destructors: the two ranks are not at the same point of the exchange
+
+
+def test_halo_timeout_is_an_error_code_not_a_trap():
+    """A halo that does not arrive within WENOEXT_HALO_TIMEOUT_S makes the call return
+    WENOEXT_ERR_TIMEOUT (sticky for the plan); the CUDA context stays usable."""
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_timeout_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in procs:
+        r = q.get(timeout=120)
+        got[r["rank"]] = r
+    for p in procs:
+        p.join(timeout=60)
+    r0 = got[0]
+    assert "wenoext error 5" in r0["first"] and "did not arrive" in r0["first"], r0
+    assert "wenoext error 5" in r0["second"], r0
+    assert r0["serial_err"] <= 1e-12

@@ -146,7 +146,7 @@ struct CellKernelArgs {
     uint32_t tmaBytes[18], tmaElemOff[18];
     const int32_t* gateFlags;
     int32_t nGate, gateEpoch, gateItem;
-    const int32_t* abortFlag;  // nullable: non-zero = the halo of this step never arrived, do nothing
+    const int32_t* abortFlag;  // nullable, DEVICE memory: non-zero = the halo of this step never arrived, do nothing
     int32_t K;
     int32_t nComp;             // stride of corr / faceValue / thetaPatch
     int32_t c0;                // first component of this batch
@@ -241,6 +241,7 @@ struct HaloPushArgs {
     int32_t* done;             // block counter, zero between launches
 };
 void launchHaloPush(const HaloPushArgs& a, cudaStream_t st);
-void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st, int32_t* status);
+void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st, int32_t* status,
+                    int32_t* statusDev);
 
 }  // namespace wenoext

@@ -273,7 +273,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         return __shfl_sync(0xffffffffu, t, 0);
     };
     // a halo that never arrived (halo_wait_kernel timed out): leave the boundary cells alone
+#ifndef WENOEXT_NO_ABORT  // developer A/B switch
     if (a.abortFlag && *reinterpret_cast<const volatile int32_t*>(a.abortFlag) != 0) return;
+#endif
     int curTile = resolveTile(grabTile());
     if (curTile >= nTiles) return;
     int pendingTile = grabTile();  // becomes nextTile at pass PPT / 2 of the current tile
@@ -456,7 +458,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const uint32_t tail = tailBuf + (uint32_t)cslot * (fastCur ? a.tmaBytes[1] : (uint32_t)a.tailSlotBytes);
         const int cell = valid ? workToCell(item) : 0;
         // boundary tiles of a gated launch read halo values that peers push during this kernel
+#ifdef WENOEXT_NO_COH  // developer A/B switch
+        const bool coh = false;
+#else
         const bool coh = split && curTile >= nTilesA;
+#endif
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV, coh);
 
@@ -1105,11 +1111,11 @@ void launchHaloPush(const HaloPushArgs& a, cudaStream_t st) {
 // their own), so the wait cannot deadlock. A sender may legitimately be late (a rank writing
 // results, say), so the patience is long: timeoutNs (WENOEXT_HALO_TIMEOUT_S, default 600 s;
 // 0 = wait for ever, like a blocking receive) before the launch fails instead of hanging.
-// On a timeout the kernel records 1 + (index of the late sender) in *status (host-mapped memory)
-// and returns: the follow-up cell launch sees it and does nothing, the host turns it into
+// On a timeout the kernel records 1 + (index of the late sender) in *statusDev (device memory) and
+// *status (host-mapped memory) and returns: the follow-up cell launch sees it and does nothing, the host turns it into
 // WENOEXT_ERR_TIMEOUT. The CUDA context stays usable (no trap).
 __global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch, long long timeoutNs,
-                                 int32_t* status) {
+                                 int32_t* status, int32_t* statusDev) {
     if ((int)threadIdx.x >= n) return;
     long long t0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -1118,17 +1124,21 @@ __global__ void halo_wait_kernel(const int32_t* flags, int n, int32_t epoch, lon
         long long t1;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         if (timeoutNs > 0 && t1 - t0 > timeoutNs) {
+            // device copy: read by the cell kernels that follow (a host-mapped word is far too slow to
+            // be read by every thread of a launch); host-mapped copy: read by the host after the call
+            if (statusDev) atomicCAS(statusDev, 0, 1 + (int)threadIdx.x);
             if (status) atomicCAS(status, 0, 1 + (int)threadIdx.x);
             return;
         }
     }
 }
-void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st, int32_t* status) {
+void launchHaloWait(const int32_t* flags, int n, int32_t epoch, cudaStream_t st, int32_t* status,
+                    int32_t* statusDev) {
     static const long long timeoutNs = [] {
         const char* e = getenv("WENOEXT_HALO_TIMEOUT_S");
         return (long long)((e ? atof(e) : 600.0) * 1e9);
     }();
-    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch, timeoutNs, status);
+    if (n > 0) halo_wait_kernel<<<1, 32, 0, st>>>(flags, n, epoch, timeoutNs, status, statusDev);
 }
 
 void launchPackHalo(const double* vals, int VS, const int32_t* sendIds, int64_t nSend,

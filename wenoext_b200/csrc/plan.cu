@@ -706,6 +706,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     cudaSetDevice(P->device);
     if (P->h_fix) cudaFreeHost(P->h_fix);
     if (P->haloStatusH) cudaFreeHost(P->haloStatusH);
+    if (P->haloStatusDev) cudaFree(P->haloStatusDev);
     if (P->stepFluxOwned) cudaFree(P->stepFluxOwned);
     void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
                     P->tileCounter, P->haloFlags, P->pushDone, P->tmaMaps, P->records, P->recInfo, P->cellListInterior, P->owner,
@@ -824,6 +825,10 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
         allocOk = allocOk && cudaMalloc((void**)&P->valsIpc[i], std::max<size_t>(valsN, 1) * 8) == cudaSuccess;
     allocOk = allocOk && cudaMalloc((void**)&P->haloFlags, 32 * sizeof(int32_t)) == cudaSuccess;
     allocOk = allocOk && cudaMalloc((void**)&P->pushDone, sizeof(int32_t)) == cudaSuccess;
+    if (allocOk && !P->haloStatusDev) {
+        allocOk = cudaMalloc((void**)&P->haloStatusDev, sizeof(int32_t)) == cudaSuccess &&
+                  cudaMemset(P->haloStatusDev, 0, sizeof(int32_t)) == cudaSuccess;
+    }
     if (allocOk && !P->haloStatusH) {
         allocOk = cudaHostAlloc((void**)&P->haloStatusH, sizeof(int32_t), cudaHostAllocMapped) == cudaSuccess;
         if (allocOk) {
@@ -1087,7 +1092,7 @@ int wenoext::launchCells(wenoext_plan* P, const int32_t* list, int nWork, int wo
         a.tmaElemOff[p] = P->tmaElemOff[p];
     }
     a.gateItem = gateItem;
-    a.abortFlag = P->haloStatusD;  // set only by a timed-out halo_wait_kernel
+    a.abortFlag = P->haloStatusDev;  // set only by a timed-out halo_wait_kernel
     if (gateItem >= 0 && !followUp) {
         a.gateFlags = P->haloFlags;
         a.nGate = P->nRecvPeers;
@@ -1286,7 +1291,7 @@ static int phase1(wenoext_plan* P) {
         if (int rc = launchCells(P, nullptr, P->nCells)) return rc;
     } else {
         if (P->p2p) {
-            launchHaloWait(P->haloFlags, P->nRecvPeers, P->haloEpoch, c.st, P->haloStatusD);
+            launchHaloWait(P->haloFlags, P->nRecvPeers, P->haloEpoch, c.st, P->haloStatusD, P->haloStatusDev);
             if (P->nRecvPeers > 0) P->lastLaunches++;
         } else if (P->comm) {
             CUDA_TRY(cudaStreamWaitEvent(c.st, P->evB, 0));

@@ -86,6 +86,7 @@ struct wenoext_plan {
     // halo_wait_kernel's verdict, host-mapped: 0, or 1 + index of the sender that never delivered
     int32_t* haloStatusH = nullptr;
     int32_t* haloStatusD = nullptr;
+    int32_t* haloStatusDev = nullptr;  // the same verdict in device memory, read by the cell kernels
     bool mergedLaunch = false;  // this call's boundary cells already went with the interior launch
     int cfgMerge = 1;           // WENOEXT_MERGE=0: separate interior / boundary launches
     int cfgP2P = 1;             // WENOEXT_P2P=0: NCCL send/recv for exchange #1
