@@ -232,8 +232,8 @@ void launchPackHalo(const double* vals, int VS, const int32_t* sendIds, int64_t 
                     double* sendBuf, cudaStream_t st);
 struct HaloPushArgs {
     int32_t nPeers, VS, epoch;
-    const double* vals;        // this rank's packed values
-    const int32_t* sendIds;    // sendHaloCellIDList flattened, peer after peer
+    const double* vals;        // this rank's packed values (exchange #2: corr, VS = nComp)
+    const int32_t* sendIds;    // sendHaloCellIDList flattened, peer after peer; nullptr: rows src0[p] + j
     int64_t off[33];           // [nPeers+1] running count of cells pushed to peers 0..i-1
     int64_t src0[32];          // first entry of peer i in sendIds
     double* dst[32];           // receiver's value buffer at nCells + haloOffset(this rank)

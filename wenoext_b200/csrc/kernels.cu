@@ -36,7 +36,10 @@ namespace wenoext {
 
 namespace {
 
-constexpr int MAX_THREADS = 256;  // 8 warps per CTA (up to 255 registers per thread)
+#ifndef WENOEXT_MAX_THREADS
+#define WENOEXT_MAX_THREADS 256
+#endif
+constexpr int MAX_THREADS = WENOEXT_MAX_THREADS;  // 8 warps per CTA (up to 255 registers per thread)
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -211,7 +214,11 @@ __device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&
 // it has consumed it, so program order (plus __syncwarp) is the only "empty"
 // signal needed: no producer warp, no cross-warp synchronisation.
 template <int K, int CB, int CELLS, int D>
+#ifdef WENOEXT_MAXNREG  // developer A/B switch: explicit register cap instead of ptxas' own choice
+__global__ void __maxnreg__(WENOEXT_MAXNREG)
+#else
 __global__ void __launch_bounds__(MAX_THREADS, 1)
+#endif
     weno_cell_kernel(const __grid_constant__ CellKernelArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int SS = 32 / CELLS;  // stencil lanes per cell (8, 6 with two idle lanes, or 32)
@@ -1090,7 +1097,9 @@ __global__ void halo_push_kernel(const __grid_constant__ HaloPushArgs a) {
         int p = 0;
         while (k >= a.off[p + 1]) ++p;
         const int64_t j = k - a.off[p];
-        a.dst[p][j * a.VS + c] = a.vals[(size_t)a.sendIds[a.src0[p] + j] * a.VS + c];
+        // sendIds == nullptr: contiguous rows starting at src0[p] (exchange #2: a processor patch of corr)
+        const int64_t row = a.sendIds ? (int64_t)a.sendIds[a.src0[p] + j] : a.src0[p] + j;
+        a.dst[p][j * a.VS + c] = a.vals[(size_t)row * a.VS + c];
     }
     __threadfence_system();
     __syncthreads();

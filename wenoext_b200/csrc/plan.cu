@@ -307,6 +307,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     if (const char* e = getenv("WENOEXT_SMEM_KB")) P->cfgSmemKB = atoi(e);
     if (const char* e = getenv("WENOEXT_MERGE")) P->cfgMerge = atoi(e);
     if (const char* e = getenv("WENOEXT_P2P")) P->cfgP2P = atoi(e);
+    if (const char* e = getenv("WENOEXT_PATCH_PUSH")) P->cfgPatchPush = atoi(e);
 
     // coefficient enumeration: n-outer, m, l-inner (WENOUpwindFit.C:304-319)
     const int s1 = d->polOrder + 1;
@@ -718,6 +719,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
         for (double* v : pp.vals)
             if (v) cudaIpcCloseMemHandle(v);
         if (pp.flags) cudaIpcCloseMemHandle(pp.flags);
+        if (pp.recvPatch) cudaIpcCloseMemHandle(pp.recvPatch);
     }
     for (double* v : P->valsIpc)
         if (v) cudaFree(v);
@@ -799,8 +801,9 @@ extern "C" int wenoext_nccl_unique_id(char id[128]) {
 // the same decision: if any rank cannot take part, everybody stays with NCCL send/recv.
 namespace {
 struct P2PBlobHead {
-    cudaIpcMemHandle_t hVals[2], hFlags;
+    cudaIpcMemHandle_t hVals[2], hFlags, hRecvPatch;
     int32_t ok, nCells;
+    int32_t patchOk;  // exchange #2 can be pushed too: at most one processor patch per neighbour
 };
 }  // namespace
 
@@ -823,8 +826,29 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
     bool allocOk = true;
     for (int i = 0; i < 2; ++i)
         allocOk = allocOk && cudaMalloc((void**)&P->valsIpc[i], std::max<size_t>(valsN, 1) * 8) == cudaSuccess;
-    allocOk = allocOk && cudaMalloc((void**)&P->haloFlags, 32 * sizeof(int32_t)) == cudaSuccess;
-    allocOk = allocOk && cudaMalloc((void**)&P->pushDone, sizeof(int32_t)) == cudaSuccess;
+    // flags: [0, 32) one per halo sender, [32, 64) one per processor-patch sender
+    allocOk = allocOk && cudaMalloc((void**)&P->haloFlags, 64 * sizeof(int32_t)) == cudaSuccess;
+    allocOk = allocOk && cudaMalloc((void**)&P->pushDone, 2 * sizeof(int32_t)) == cudaSuccess;
+    // exchange #2: the receive buffer of the processor-patch values must be mappable by the peers, so
+    // it is allocated here for the widest field type instead of lazily per call
+    std::vector<int32_t> patchSlotOf(R, -1), patchStartOf(R, -1), patchSizeOf(R, 0);
+    int32_t patchOk = P->cfgPatchPush ? 1 : 0, nPatchSend = 0;
+    for (const auto& pt : P->patches) {
+        if (pt.type != WENOEXT_PATCH_PROCESSOR || pt.size == 0) continue;
+        if (pt.nbr < 0 || pt.nbr >= R || pt.nbr == me || patchSlotOf[pt.nbr] >= 0) {
+            patchOk = 0;  // two patches towards one neighbour: keep the NCCL exchange
+            continue;
+        }
+        patchSlotOf[pt.nbr] = nPatchSend++;
+        patchStartOf[pt.nbr] = pt.start;
+        patchSizeOf[pt.nbr] = pt.size;
+    }
+    if (nPatchSend > 32) patchOk = 0;
+    const size_t patchN = (size_t)std::max(P->nBnd, 1) * wenoext_plan::kPatchMaxComp;
+    double* recvPatchIpc = nullptr;
+    if (allocOk && P->hasProcessor)
+        allocOk = cudaMalloc((void**)&recvPatchIpc, patchN * 8) == cudaSuccess &&
+                  cudaMemset(recvPatchIpc, 0, patchN * 8) == cudaSuccess;
     if (allocOk && !P->haloStatusDev) {
         allocOk = cudaMalloc((void**)&P->haloStatusDev, sizeof(int32_t)) == cudaSuccess &&
                   cudaMemset(P->haloStatusDev, 0, sizeof(int32_t)) == cudaSuccess;
@@ -838,11 +862,13 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
     }
     P2PBlobHead head{};
     if (allocOk) {
-        cudaMemset(P->haloFlags, 0, 32 * sizeof(int32_t));
-        cudaMemset(P->pushDone, 0, sizeof(int32_t));
+        cudaMemset(P->haloFlags, 0, 64 * sizeof(int32_t));
+        cudaMemset(P->pushDone, 0, 2 * sizeof(int32_t));
         allocOk = cudaIpcGetMemHandle(&head.hVals[0], P->valsIpc[0]) == cudaSuccess &&
                   cudaIpcGetMemHandle(&head.hVals[1], P->valsIpc[1]) == cudaSuccess &&
                   cudaIpcGetMemHandle(&head.hFlags, P->haloFlags) == cudaSuccess;
+        if (allocOk && recvPatchIpc)
+            allocOk = cudaIpcGetMemHandle(&head.hRecvPatch, recvPatchIpc) == cudaSuccess;
     }
     if (!allocOk) {
         cudaGetLastError();
@@ -850,8 +876,11 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
     }
     head.ok = ok;
     head.nCells = P->nCells;
+    head.patchOk = patchOk;
     // blob: head | haloBase[R] (int64: where sender q's values start in my buffer) | slot[R]
-    const size_t blob = sizeof(P2PBlobHead) + (size_t)R * 8 + (size_t)R * 4;
+    //       | patchOff[R] (int32: boundary-face index where sender q's patch values go, -1 none)
+    //       | patchSize[R] | patchSlot[R]
+    const size_t blob = sizeof(P2PBlobHead) + (size_t)R * 8 + (size_t)R * 4 * 4;
     const size_t blobPad = (blob + 15) / 16 * 16;
     std::vector<unsigned char> mine(blobPad, 0), all(blobPad * R, 0);
     memcpy(mine.data(), &head, sizeof(head));
@@ -859,6 +888,10 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
         const int64_t base = (int64_t)P->nCells + P->haloOff[q];
         memcpy(mine.data() + sizeof(head) + (size_t)q * 8, &base, 8);
         memcpy(mine.data() + sizeof(head) + (size_t)R * 8 + (size_t)q * 4, &slotOf[q], 4);
+        const int32_t poff = patchStartOf[q] >= 0 ? patchStartOf[q] - P->nInt : -1;
+        memcpy(mine.data() + sizeof(head) + (size_t)R * 12 + (size_t)q * 4, &poff, 4);
+        memcpy(mine.data() + sizeof(head) + (size_t)R * 16 + (size_t)q * 4, &patchSizeOf[q], 4);
+        memcpy(mine.data() + sizeof(head) + (size_t)R * 20 + (size_t)q * 4, &patchSlotOf[q], 4);
     }
     unsigned char *dMine = nullptr, *dAll = nullptr;
     CUDA_TRY(cudaMalloc((void**)&dMine, blobPad));
@@ -878,6 +911,17 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
         return h;
     };
     for (int p = 0; use && p < R; ++p) use = headOf(p).ok != 0;
+    // exchange #2 by push only if every rank can, and the two sides of every patch agree on its size
+    bool usePatch = use;
+    for (int p = 0; usePatch && p < R; ++p) usePatch = headOf(p).patchOk != 0;
+    for (int p = 0; usePatch && p < R; ++p) {
+        if (patchSlotOf[p] < 0) continue;
+        const unsigned char* tab = all.data() + (size_t)p * blobPad + sizeof(P2PBlobHead);
+        int32_t theirOff, theirSize;
+        memcpy(&theirOff, tab + (size_t)R * 12 + (size_t)me * 4, 4);
+        memcpy(&theirSize, tab + (size_t)R * 16 + (size_t)me * 4, 4);
+        if (theirOff < 0 || theirSize != patchSizeOf[p]) usePatch = false;
+    }
     // map the receivers' buffers
     int32_t opened = use ? 1 : 0;
     if (use) {
@@ -893,6 +937,17 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
             for (int i = 0; i < 2 && o; ++i)
                 o = cudaIpcOpenMemHandle((void**)&pp.vals[i], h.hVals[i], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
             o = o && cudaIpcOpenMemHandle((void**)&pp.flags, h.hFlags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            if (o && usePatch && patchSlotOf[p] >= 0) {
+                int32_t poff, pslot;
+                memcpy(&poff, tab + (size_t)R * 12 + (size_t)me * 4, 4);
+                memcpy(&pslot, tab + (size_t)R * 20 + (size_t)me * 4, 4);
+                pp.patchOff = poff;
+                pp.patchSlot = pslot;
+                pp.patchStart = patchStartOf[p];
+                pp.patchSize = patchSizeOf[p];
+                o = cudaIpcOpenMemHandle((void**)&pp.recvPatch, h.hRecvPatch, cudaIpcMemLazyEnablePeerAccess) ==
+                    cudaSuccess;
+            }
             P->pushPeers.push_back(pp);  // (closed in plan_destroy, also when partly opened)
             if (!o) {
                 cudaGetLastError();
@@ -914,21 +969,44 @@ static int setupHaloPush(wenoext_plan* P, NcclApi* n) {
             for (double*& v : pp.vals)
                 if (v) cudaIpcCloseMemHandle(v), v = nullptr;
             if (pp.flags) cudaIpcCloseMemHandle(pp.flags), pp.flags = nullptr;
+            if (pp.recvPatch) cudaIpcCloseMemHandle(pp.recvPatch), pp.recvPatch = nullptr;
         }
         P->pushPeers.clear();
+        if (recvPatchIpc) cudaFree(recvPatchIpc);
         for (double*& v : P->valsIpc)
             if (v) cudaFree(v), v = nullptr;
         if (getenv("WENOEXT_VERBOSE")) fprintf(stderr, "[wenoext rank %d] halo push unavailable, using NCCL send/recv\n", me);
         return 0;
     }
+    // every processor neighbour must also be a halo peer (it always is: face neighbours are in the
+    // central stencil), otherwise its patch would have nobody to push to
+    if (usePatch) {
+        int mapped = 0;
+        for (const auto& pp : P->pushPeers) mapped += pp.recvPatch != nullptr;
+        if (mapped != nPatchSend) usePatch = false;
+    }
+    if (recvPatchIpc) {
+        // the plan's patch buffers, sized once for the widest field type (prepareCall keeps them)
+        if (P->recvPatch) cudaFree(P->recvPatch);
+        if (P->thetaPatch) cudaFree(P->thetaPatch);
+        if (P->sendPatch) cudaFree(P->sendPatch);
+        P->recvPatch = recvPatchIpc;
+        P->thetaPatch = P->sendPatch = nullptr;
+        CUDA_TRY(cudaMalloc((void**)&P->thetaPatch, patchN * 8));
+        CUDA_TRY(cudaMalloc((void**)&P->sendPatch, patchN * 8));
+        CUDA_TRY(cudaMemset(P->thetaPatch, 0, patchN * 8));
+        P->patchCap = patchN;
+    }
+    P->patchPush = usePatch && P->hasProcessor;
+    P->nPatchSenders = P->patchPush ? nPatchSend : 0;
     P->nRecvPeers = nRecv;
     if (P->vals && P->vals != P->valsIpc[0] && P->vals != P->valsIpc[1]) cudaFree(P->vals);
     P->vals = P->valsIpc[0];
     P->valsCap = valsN;
     P->p2p = true;
     if (getenv("WENOEXT_VERBOSE"))
-        fprintf(stderr, "[wenoext rank %d] halo push over peer memory: %d senders, %zu receivers\n", me, nRecv,
-                P->pushPeers.size());
+        fprintf(stderr, "[wenoext rank %d] halo push over peer memory: %d senders, %zu receivers; patch values %s\n",
+                me, nRecv, P->pushPeers.size(), P->patchPush ? "pushed too" : "by ncclSend/ncclRecv");
     return 0;
 }
 
@@ -1232,6 +1310,33 @@ static void pushHalo(wenoext_plan* P, cudaStream_t st) {
     P->lastLaunches++;
 }
 
+// exchange #2 (swapData, WENOUpwindFit.C:326-385) as a one-sided push: this rank's processor-patch
+// values of `corr` (btsfUD: written by the owner cells where flux > 0, zero elsewhere) go straight into
+// the neighbours' receive buffers over peer memory; the last block raises their patch flags. No
+// rendezvous and no communication kernel on the compute stream.
+static void pushPatches(wenoext_plan* P, cudaStream_t st) {
+    const wenoext_call& c = P->call;
+    HaloPushArgs a{};
+    a.VS = c.nComp;
+    a.epoch = P->haloEpoch;
+    a.vals = c.corr;
+    a.sendIds = nullptr;
+    a.done = P->pushDone + 1;
+    int n = 0;
+    for (const auto& pp : P->pushPeers) {
+        if (!pp.recvPatch || pp.patchSize == 0) continue;
+        a.src0[n] = pp.patchStart;
+        a.off[n + 1] = a.off[n] + pp.patchSize;
+        a.dst[n] = pp.recvPatch + (size_t)pp.patchOff * c.nComp;
+        a.flag[n] = pp.flags + 32 + pp.patchSlot;
+        ++n;
+    }
+    a.nPeers = n;
+    if (n == 0) return;
+    launchHaloPush(a, st);
+    P->lastLaunches++;
+}
+
 static int phase0(wenoext_plan* P, bool launchInterior = true) {
     const wenoext_call& c = P->call;
     const bool parallel = P->nProcs > 1;
@@ -1318,7 +1423,9 @@ static int phase1(wenoext_plan* P) {
         }
         P->mergedLaunch = false;
     }
-    if (P->hasProcessor) {
+    if (P->hasProcessor && P->patchPush) {
+        pushPatches(P, c.st);
+    } else if (P->hasProcessor) {
         CUDA_TRY(cudaEventRecord(P->evC, c.st));
         if (P->comm) {
             // swapData (WENOUpwindFit.C:326-385): whole patch arrays, both directions
@@ -1362,6 +1469,11 @@ int wenoext::phase2(wenoext_plan* P) {
                                      Q->sendPatch + (size_t)(qp->start - Q->nInt) * c.nComp,
                                      (size_t)pt.size * c.nComp * 8, cudaMemcpyDeviceToDevice, c.st));
         }
+    }
+    if (P->patchPush && P->nPatchSenders > 0) {
+        // the neighbours' patch values of this step (they push on their own: cannot deadlock)
+        launchHaloWait(P->haloFlags + 32, P->nPatchSenders, P->haloEpoch, c.st, P->haloStatusD, P->haloStatusDev);
+        P->lastLaunches++;
     }
     PatchKernelArgs a{};
     a.nBnd = P->nBnd;
@@ -1415,6 +1527,10 @@ static int prepareCall(wenoext_plan* P, int scheme, int bounded, int nComp, cons
     }
     if (P->nProcs > 1 && !P->comm && P->localPeers.empty()) {
         setError("correction: parallel plan without a communicator (wenoext_attach_nccl)");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (P->patchPush && nComp > wenoext_plan::kPatchMaxComp) {
+        setError("correction: more than 9 components on a plan that pushes its patch values over peer memory");
         return WENOEXT_ERR_INVALID;
     }
     if (scheme == WENOEXT_SCHEME_UPWINDFIT && bounded && P->hasProcessor && !pnf && !P->hasNbrCell) {

@@ -73,13 +73,21 @@ struct wenoext_plan {
     double* valsIpc[2] = {nullptr, nullptr};  // double-buffered value buffers the peers write into
     int32_t* haloFlags = nullptr;             // [nRecvPeers]: epoch of the last halo each sender delivered
     int32_t nRecvPeers = 0;
-    int32_t* pushDone = nullptr;              // block counter of halo_push_kernel
+    int32_t* pushDone = nullptr;              // block counters of halo_push_kernel: [0] exchange #1, [1] exchange #2
+    bool patchPush = false;                   // exchange #2 over peer memory too (else grouped ncclSend/ncclRecv)
+    int32_t nPatchSenders = 0;                // flags [32, 32 + nPatchSenders) of haloFlags
+    static constexpr int kPatchMaxComp = 9;   // the IPC receive buffer holds [nBnd][9] doubles (tensor)
     struct PushPeer {
         int32_t proc = 0;
         double* vals[2] = {nullptr, nullptr};  // peer's valsIpc, mapped here
         int32_t* flags = nullptr;              // peer's haloFlags, mapped here
         int64_t haloBase = 0;                  // peer's nCells + its haloOff[this rank]
         int32_t slot = 0;                      // this rank's index among the peer's senders
+        // exchange #2 (processor-patch face values) pushed the same way: the peer's receive buffer,
+        // where this rank's patch starts in it (boundary-face index), this rank's patch, flag slot
+        double* recvPatch = nullptr;
+        int64_t patchOff = -1;
+        int32_t patchStart = 0, patchSize = 0, patchSlot = -1;
     };
     std::vector<PushPeer> pushPeers;
     int32_t haloEpoch = 0;
@@ -90,6 +98,7 @@ struct wenoext_plan {
     bool mergedLaunch = false;  // this call's boundary cells already went with the interior launch
     int cfgMerge = 1;           // WENOEXT_MERGE=0: separate interior / boundary launches
     int cfgP2P = 1;             // WENOEXT_P2P=0: NCCL send/recv for exchange #1
+    int cfgPatchPush = 1;       // WENOEXT_PATCH_PUSH=0: grouped ncclSend/ncclRecv for exchange #2
     // faces / patches
     int32_t* owner = nullptr;
     int32_t* bfPatchType = nullptr;
