@@ -285,9 +285,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #endif
     int curTile = resolveTile(grabTile());
     if (curTile >= nTiles) return;
-    int pendingTile = grabTile();  // becomes nextTile at pass PPT / 2 of the current tile
+    int pendingTile = grabTile();  // becomes nextTile at pass 1 of the current tile
     int nextTile = nTiles;
-    static_assert(PPT >= 4, "the next tile is broadcast at pass PPT / 2, at least 2 passes before its first use");
+    static_assert(PPT >= 4, "the next tile is broadcast at pass 1 and first needed by the look-ahead of pass 1 (3 ahead)");
     int tp = 0;  // pass of the current tile being consumed
     // work item of cell c of the pass k passes after the one being consumed (k <= 2);
     // -1 beyond the end of the work
@@ -312,14 +312,19 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     // so the slots of such a pass are tmaBytes[part] apart instead of the padded slot strides.
     // fastOf: cell 0 of the pass, or -1 (per-lane 1-D copies, the general path).
     const bool tma2d = CELLS == 4 && a.tmaMaps != nullptr;
-    auto fetchInfo = [&](int k, int& fastOf) {
+    // two halves, so that the load can be issued a whole pass before its result is looked at
+    // (looking at it right away cost one full memory latency per pass: 4 % of the stall samples)
+    auto loadInfo = [&](int k, int& cellIdx) {
         int4 v = make_int4(0, 0, 0, -1);
         const int w = issuer ? workItem(k, lane) : -1;
-        int cellIdx = -1;
+        cellIdx = -1;
         if (w >= 0) {
             cellIdx = workToCell(w);
             v = __ldg(reinterpret_cast<const int4*>(a.recInfo + cellIdx));
         }
+        return v;
+    };
+    auto finishInfo = [&](const int4& v, int cellIdx, int& fastOf) {
         fastOf = -1;
         if (tma2d) {
             const int c0 = __shfl_sync(0xffffffffu, cellIdx, 0);
@@ -327,6 +332,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             if (__all_sync(0xffffffffu, ok) && c0 >= 0) fastOf = c0;
         }
         return v;
+    };
+    auto fetchInfo = [&](int k, int& fastOf) {
+        int cellIdx;
+        const int4 v = loadInfo(k, cellIdx);
+        return finishInfo(v, cellIdx, fastOf);
     };
     auto issue2D = [&](uint32_t dst, int part, int cell0, uint32_t bar) {
         if (issuer) mbarArriveExpectTx(bar, a.tmaBytes[part]);
@@ -472,6 +482,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #endif
         double cen[CB];
         loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV, coh);
+        // RecInfo of the pass three ahead: with the state of this pass it is workItem(3, .), which is
+        // what fetchInfo(2, .) gives once tp has moved on at the bottom of the pass (the next tile is
+        // resolved at tp == 1, before any pass needs it here)
+        int cellN3;
+        const int4 rawN3 = loadInfo(3, cellN3);
 
         // the other head slot and the tail slot were last read by the previous pass
         issueHead(infoNext, fNext, hb ^ 1);
@@ -835,14 +850,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             curTile = nextTile;
             if (curTile >= nTiles) break;
             pendingTile = grabTile();
-        } else if (tp == PPT / 2) {
+        } else if (tp == 1) {
             nextTile = resolveTile(pendingTile);
         }
         infoCur = infoNext;
         infoNext = infoNN;
         fCur = fNext;
         fNext = fNN;
-        infoNN = fetchInfo(2, fNN);
+        infoNN = finishInfo(rawN3, cellN3, fNN);
     }
 }
 }  // namespace
