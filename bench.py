@@ -195,6 +195,23 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def bind_to_gpu_cpus(index):
+    """Pin this rank (and the pinned buffers it allocates afterwards: first touch) to the CPUs next to
+    its GPU (NVML's ideal CPU affinity, i.e. the GPU's NUMA node / PCIe root). Returns the CPU count."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, x in enumerate(words) for b in range(64) if (x >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return len(os.sched_getaffinity(0))
+    except Exception:  # NVML missing or affinity not permitted: keep the inherited mask
+        return len(os.sched_getaffinity(0))
+
+
 def cpu_model():
     try:
         for ln in open("/proc/cpuinfo"):
@@ -346,6 +363,7 @@ def run_ours(a):
         raise SystemExit("bench.py: no CUDA device; wenoext_b200 has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    n_cpus = bind_to_gpu_cpus(local)
     gloo = None
     if N > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -499,6 +517,30 @@ def run_ours(a):
                "ms_per_step": w.item() * 1e3,
                "h2d_bytes_per_step": int(vf_p.nbytes + phi_p.nbytes),
                "d2h_bytes_per_step": int(out_p.nbytes)}
+        # e2e_div: what a solver times (tests/Cases/performanceTest/src/main.C:160, fvc::div(phi, psi)): the
+        # same reconstruction, surface-integrated on the device, so only [nCells][nComp] returns. The cell
+        # volumes are mesh data (uploaded by the warm-up call, not a per-step input).
+        nB = plan.nFaces - int(info.nInternalFaces)
+        bnd_p = torch.zeros((nB, a.ncomp), dtype=torch.float64).pin_memory().numpy()
+        vol_p = torch.full((int(info.nCells),), 1.0 / a.n ** 3, dtype=torch.float64).pin_memory().numpy()
+        div_p = torch.empty((int(info.nCells), a.ncomp), dtype=torch.float64).pin_memory().numpy()
+        try:
+            plan.div(FIT, a.bounded, vf_p, phi_p, bnd_p, vol_p, out=div_p)
+            plan.div(FIT, a.bounded, vf_p, phi_p, bnd_p, None, out=div_p)
+            barrier()
+            w0 = time.perf_counter()
+            for _ in range(ke):
+                plan.div(FIT, a.bounded, vf_p, phi_p, bnd_p, None, out=div_p)
+            torch.cuda.synchronize()
+            wd = torch.tensor([(time.perf_counter() - w0) / ke], dtype=torch.float64, device=dev)
+            if N > 1:
+                dist.all_reduce(wd, op=dist.ReduceOp.MAX)
+            e2e["div"] = {"value": tot[0].item() / wd.item(), "unit": "faces/s", "ms_per_step": wd.item() * 1e3,
+                          "h2d_bytes_per_step": int(vf_p.nbytes + phi_p.nbytes + bnd_p.nbytes),
+                          "d2h_bytes_per_step": int(div_p.nbytes),
+                          "what": "wenoext_div with host buffers: fvc::div(phi, vf) formed on the device"}
+        except wx.WenoextError as ex:  # e.g. a plan whose coupled patches carry no neighbour-cell map
+            e2e["div"] = {"unavailable": str(ex)}
         if parity is not None:
             ee = torch.tensor([float(np.abs(out_p - got).max())], dtype=torch.float64, device=dev)
             if N > 1:
@@ -536,7 +578,7 @@ def run_ours(a):
                    "faces_per_step": int(tot[0].item()),
                    "l2": "inputs (per-cell records, %.1f GB) are far larger than the 126 MB L2; "
                          "no flush needed" % (info.recordBytes / 1e9),
-                   "setup_s": round(t_setup, 1)},
+                   "setup_s": round(t_setup, 1), "host_cpus_per_rank": n_cpus},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -192,10 +192,13 @@ int wenoext_interpolate(wenoext_plan* plan, int scheme, int bounded, int nComp,
  *   div[cell]  = (sum over the cell's faces, ascending face index as OpenFOAM's face loops:
  *                 +flux*value where the cell owns the face, -flux*value where it is the
  *                 neighbour) / cellVolumes[cell]
- * Only [nCells][nComp] returns to the host instead of [nFaces][nComp].
+ * Only [nCells][nComp] returns to the host instead of [nFaces][nComp]; with host buffers
+ * the reconstruction runs slab-pipelined like wenoext_correction (copies of the next slab under the kernel
+ * of the current one), on serial and on parallel plans. faceFlux may be NULL after wenoext_set_face_flux.
  *   bndValue    [nFaces-nInternalFaces][nComp]  vf.boundaryField() on the patch faces (read on
  *               non-coupled patches only)
- *   cellVolumes [nCells]                        mesh.V()
+ *   cellVolumes [nCells]                        mesh.V(); host-buffer calls: NULL reuses the volumes the
+ *               previous host-buffer call uploaded (the mesh does not change between time steps)
  *   div         [nCells][nComp] out
  * Coupled patches need the value across the face: patchNbrField, or desc.patchNbrCell. */
 int wenoext_div(wenoext_plan* plan, int scheme, int bounded, int nComp, const double* vf,

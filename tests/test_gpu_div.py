@@ -77,3 +77,35 @@ def test_div_is_conservative_at_full_size():
     scale = np.abs(flux[nI:, None] * bnd).sum(axis=0)
     assert np.all(np.abs(total - want) <= 1e-9 * scale)
     plan.destroy()
+
+
+@pytest.mark.parametrize("sides", [(0,) * 6, (2, 2, 0, 0, 0, 0)], ids=["walls", "cyclic_x"])
+def test_div_host_buffers_pipelined_equals_device_buffers(sides):
+    """Host buffers: the reconstruction runs slab-pipelined and the face field stays on the device; only
+    [nCells][nComp] comes back. Same bits as the device-buffer call; the volumes and the flux of an
+    earlier call can be reused (cellVolumes = NULL, faceFlux = NULL after wenoext_set_face_flux)."""
+    import torch
+    case = wx.BoxCase((48, 48, 40), 2, sides=sides)
+    plan = wx.Plan(case.desc)
+    try:
+        rng = np.random.default_rng(4)
+        vf = H.vector_field(case.C, seed=9)
+        flux = H.face_flux(case.Sf, U=(1.0, -1.0, 0.5), zero_frac=0.02)
+        bnd = rng.uniform(-1, 1, (case.nFaces - case.nInternalFaces, 3))
+        vol = rng.uniform(0.5, 1.5, case.nCells) * 1e-3
+        t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).cuda()  # noqa: E731
+        want = plan.div(FIT, 1, t(vf), t(flux), t(bnd), t(vol)).cpu().numpy()
+        got = np.asarray(plan.div(FIT, 1, vf, flux, bnd, vol))
+        np.testing.assert_array_equal(got, want)
+        # second "time step": new field, same mesh volumes, flux uploaded once
+        vf2 = H.vector_field(case.C, seed=10)
+        want2 = plan.div(FIT, 1, t(vf2), t(flux), t(bnd), t(vol)).cpu().numpy()
+        plan.set_face_flux(flux)
+        got2 = np.asarray(plan.div(FIT, 1, vf2, None, bnd, None))
+        np.testing.assert_array_equal(got2, want2)
+        # and the face field of an ordinary call is unaffected by the skipped copies before it
+        corr = np.asarray(plan.correction(FIT, 1, vf2, None))
+        corr_d = plan.correction(FIT, 1, t(vf2), t(flux)).cpu().numpy()
+        np.testing.assert_array_equal(corr, corr_d)
+    finally:
+        plan.destroy()

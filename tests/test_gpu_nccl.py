@@ -64,6 +64,15 @@ def _worker(rank, world, port, q, mesh):
             out = torch.empty((mine.nFaces, 3), dtype=torch.float64, device="cuda")
             plan.correction(scheme, bounded, dvf, dfl, out=out)
             errs.append(H.normwise_err(out.cpu().numpy().reshape(ref.shape), ref))
+        # wenoext_div on a parallel plan: host buffers (pipelined, face field stays on the device) against
+        # device buffers, same bits
+        rng = np.random.default_rng(11 + rank)
+        bnd = rng.uniform(-1, 1, (mine.nFaces - mine.nInternalFaces, 3))
+        vol = rng.uniform(0.5, 1.5, mine.nCells) * 1e-3
+        tt = lambda x: torch.from_numpy(np.ascontiguousarray(x)).cuda()  # noqa: E731
+        dd = plan.div(0, 1, tt(vfs[rank]), tt(fls[rank]), tt(bnd), tt(vol)).cpu().numpy()
+        dh = np.asarray(plan.div(0, 1, vfs[rank], fls[rank], bnd, vol))
+        errs.append(0.0 if np.array_equal(dd, dh) else 1.0)
         # scalar field (value stride 1: four cells per 32-byte sector at the halo boundary)
         svfs = [np.ascontiguousarray(v[:, 0]) for v in vfs]
         ref = correction_multirank(Oracle("c"), cases, 0, 1, svfs, fls)[rank]

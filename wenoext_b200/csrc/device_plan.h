@@ -199,13 +199,13 @@ struct DivKernelArgs {
     const int32_t* cellFaceStart;  // [nCells+1]
     const int32_t* cellFaces;      // faces of a cell in ascending face index
     const int32_t* owner;          // [nFaces]
+    const int32_t* neighbour;      // [nInternalFaces]
     const int32_t* bfPatchType;    // [nBnd] FACE_* or -1 (not coupled)
     const int32_t* bfNbrCell;      // [nBnd] flat value index across a coupled face, or null
     const double* vf;              // [nCells][nComp]
     const double* vals;            // packed values incl. halo (stride VS) of the LAST component batch
     int32_t VS, c0, CB;
     const double* flux;            // [nFaces]
-    const double* faceValue;       // [nInternalFaces][nComp] upwind value + correction
     const double* corr;            // [nFaces][nComp]
     const double* patchNbrField;   // nullable [nBnd][nComp]
     const double* bndValue;        // [nBnd][nComp]

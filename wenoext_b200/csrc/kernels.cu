@@ -946,8 +946,11 @@ __global__ void surface_integrate_kernel(const DivKernelArgs a) {
         const int f = a.cellFaces[k];
         const double fl = a.flux[f];
         if (f < a.nInternalFaces) {
-            const double v = fl * a.faceValue[(size_t)f * a.nComp + c];
-            sum += a.owner[f] == cell ? v : -v;
+            // interpolate(): weights()*vf_P + (1 - weights())*vf_N + correction(), weights() = pos(flux)
+            const int P_ = a.owner[f], N_ = a.neighbour[f];
+            const double up = a.vf[(size_t)(fl >= 0 ? P_ : N_) * a.nComp + c];
+            const double v = fl * (up + a.corr[(size_t)f * a.nComp + c]);
+            sum += P_ == cell ? v : -v;
         } else {
             const int bf = f - a.nInternalFaces;
             double val;

@@ -506,6 +506,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
             std::sort(sorted.begin() + d->cellFaceStart[c], sorted.begin() + d->cellFaceStart[c + 1]);
         rc = rc ? rc : upload(&P->cellFaceStartD, d->cellFaceStart, (size_t)nC + 1);
         rc = rc ? rc : upload(&P->cellFacesSortedD, sorted.data(), sorted.size());
+        if (d->nInternalFaces) rc = rc ? rc : upload(&P->neighbourD, d->neighbour, (size_t)d->nInternalFaces);
     }
     rc = rc ? rc : upload(&P->bfPatchType, bfType.data(), bfType.size());
     rc = rc ? rc : upload(&P->bfPartner, bfPartner.data(), bfPartner.size());
@@ -709,7 +710,7 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (P->haloStatusH) cudaFreeHost(P->haloStatusH);
     if (P->haloStatusDev) cudaFree(P->haloStatusDev);
     if (P->stepFluxOwned) cudaFree(P->stepFluxOwned);
-    void* ptrs[] = {P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_fv, P->d_bnd, P->d_vol, P->d_div,
+    void* ptrs[] = {P->neighbourD, P->fixFacesD, P->d_fix, P->cellFaceStartD, P->cellFacesSortedD, P->d_corr, P->d_bnd, P->d_vol, P->d_div,
                     P->tileCounter, P->haloFlags, P->pushDone, P->tmaMaps, P->records, P->recInfo, P->cellListInterior, P->owner,
                     P->bfPatchType, P->bfPartner, P->bfNbrCell, P->sendIds, P->vals, P->sendBuf,
                     P->recvPatch, P->thetaPatch, P->sendPatch, P->s_vf, P->s_flux, P->s_pnf, P->s_corr, P->s_fv};
@@ -1606,7 +1607,7 @@ static void setBatch(wenoext_plan* P, int c0) {
 }
 
 static int finishCall(wenoext_plan* P, double* corr, double* fv, int memKind) {
-    if (memKind != WENOEXT_MEM_HOST) return 0;
+    if (memKind != WENOEXT_MEM_HOST || P->skipD2H) return 0;
     const wenoext_call& c = P->call;
     CUDA_TRY(cudaMemcpyAsync(corr, c.corr, (size_t)P->nFaces * c.nComp * 8, cudaMemcpyDeviceToHost, c.st));
     if (fv) CUDA_TRY(cudaMemcpyAsync(fv, c.fv, (size_t)P->nInt * c.nComp * 8, cudaMemcpyDeviceToHost, c.st));
@@ -1677,7 +1678,7 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
             CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * (k - 1) + 1], 0));
         }
         const int done = k == S - 1 ? sent : P->doneFaces[k];  // the rest follows the patch kernel
-        if (done > sent) {
+        if (done > sent && !P->skipD2H) {
             CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
                                      (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
             if (fv)
@@ -1688,6 +1689,10 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         }
     }
     if (int rc = phase2(P)) return rc;  // cyclic patches
+    if (P->skipD2H) {  // wenoext_div: the face field stays on the device
+        CUDA_TRY(cudaStreamSynchronize(P->sIn));
+        return 0;
+    }
     CUDA_TRY(cudaEventRecord(evEnd, c.st));
     CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
     CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
@@ -1707,6 +1712,10 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
 // otherwise they travel compactly and the host scatters them.
 static int finishParallelHostCall(wenoext_plan* P, double* corr, int sent, cudaEvent_t evEnd) {
     const wenoext_call& c = P->call;
+    if (P->skipD2H) {  // wenoext_div: the face field stays on the device
+        CUDA_TRY(cudaStreamSynchronize(P->sIn));
+        return 0;
+    }
     const int nComp = c.nComp;
     const size_t nFix = P->fixFacesH.size();
     double* mapped = nullptr;
@@ -1822,7 +1831,7 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
                 if (S > 1) CUDA_TRY(cudaStreamWaitEvent(c.st, P->evSlab[2 * (k - 1) + 1], 0));
             }
             const int done = P->doneFaces[k];
-            if (k < S - 1 && done > sent) {
+            if (k < S - 1 && done > sent && !P->skipD2H) {
                 CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
                                          (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
                 sent = done;
@@ -1849,7 +1858,7 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
         item0 = P->slabEnd[k];
         CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], c.st));
         const int done = P->doneFaces[k];
-        if (k < S - 1 && done > sent) {
+        if (k < S - 1 && done > sent && !P->skipD2H) {
             CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
             CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
                                      (size_t)(done - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
@@ -1935,8 +1944,12 @@ extern "C" int wenoext_correction(wenoext_plan* P, int scheme, int bounded, int 
 extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, const double* vf,
                            const double* faceFlux, const double* patchNbrField, const double* bndValue,
                            const double* cellVolumes, double* div, int memKind, void* stream) {
-    if (!P || !vf || !cellVolumes || !div || (P->nBnd > 0 && !bndValue)) {
+    if (!P || !vf || !div || (P->nBnd > 0 && !bndValue)) {
         setError("div: NULL argument");
+        return WENOEXT_ERR_INVALID;
+    }
+    if (!cellVolumes && !(memKind == WENOEXT_MEM_HOST && P->volValid)) {
+        setError("div: cellVolumes is NULL and no earlier host-buffer call left the volumes on the device");
         return WENOEXT_ERR_INVALID;
     }
     if (!faceFlux && !P->stepFlux) {
@@ -1954,39 +1967,42 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
     CUDA_TRY(cudaSetDevice(P->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t nV = (size_t)P->nCells * nComp, nF = (size_t)P->nFaces, nB = (size_t)P->nBnd * nComp;
-    if (int rc = ensureBuf(&P->d_corr, &P->d_corrCap, nF * nComp)) return rc;
-    if (int rc = ensureBuf(&P->d_fv, &P->d_fvCap, (size_t)P->nInt * nComp)) return rc;
     const double *dvf = vf, *dflux = faceFlux ? faceFlux : P->stepFlux, *dpnf = patchNbrField, *dbnd = bndValue,
-                 *dvol = cellVolumes;
+                 *dvol = cellVolumes, *dcorr = nullptr;
     double* ddiv = div;
     if (memKind == WENOEXT_MEM_HOST) {
-        // stage everything once; the reconstruction below then runs on device pointers
-        if (int rc = ensureBuf(&P->s_vf, &P->s_vfCap, nV)) return rc;
-        if (faceFlux)
-            if (int rc = ensureBuf(&P->s_flux, &P->s_fluxCap, nF)) return rc;
+        // The reconstruction is the ordinary host-buffer correction() (slab-pipelined where the plan
+        // allows it: H2D of the next slab under the kernel of the current one) whose face field stays on
+        // the device; only [nCells][nComp] comes back.
         if (int rc = ensureBuf(&P->d_vol, &P->d_volCap, (size_t)P->nCells)) return rc;
         if (int rc = ensureBuf(&P->d_div, &P->d_divCap, nV)) return rc;
-        CUDA_TRY(cudaMemcpyAsync(P->s_vf, vf, nV * 8, cudaMemcpyHostToDevice, st));
-        if (faceFlux) CUDA_TRY(cudaMemcpyAsync(P->s_flux, faceFlux, nF * 8, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(P->d_vol, cellVolumes, (size_t)P->nCells * 8, cudaMemcpyHostToDevice, st));
-        dvf = P->s_vf;
-        dflux = faceFlux ? P->s_flux : P->stepFlux;
-        dvol = P->d_vol;
-        ddiv = P->d_div;
+        if (cellVolumes) {  // mesh.V() is constant: NULL on later calls reuses this copy
+            CUDA_TRY(cudaMemcpyAsync(P->d_vol, cellVolumes, (size_t)P->nCells * 8, cudaMemcpyHostToDevice, st));
+            P->volValid = true;
+        }
         if (nB) {
             if (int rc = ensureBuf(&P->d_bnd, &P->d_bndCap, nB)) return rc;
             CUDA_TRY(cudaMemcpyAsync(P->d_bnd, bndValue, nB * 8, cudaMemcpyHostToDevice, st));
             dbnd = P->d_bnd;
-            if (patchNbrField) {
-                if (int rc = ensureBuf(&P->s_pnf, &P->s_pnfCap, nB)) return rc;
-                CUDA_TRY(cudaMemcpyAsync(P->s_pnf, patchNbrField, nB * 8, cudaMemcpyHostToDevice, st));
-                dpnf = P->s_pnf;
-            }
         }
+        P->skipD2H = true;
+        const int rc = wenoext_interpolate(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, div /*unused*/,
+                                           nullptr, WENOEXT_MEM_HOST, stream);
+        P->skipD2H = false;
+        if (rc) return rc;
+        dvf = P->s_vf;
+        dflux = faceFlux ? P->s_flux : P->stepFlux;
+        dpnf = patchNbrField ? P->s_pnf : nullptr;
+        dvol = P->d_vol;
+        ddiv = P->d_div;
+        dcorr = P->s_corr;
+    } else {
+        if (int rc = ensureBuf(&P->d_corr, &P->d_corrCap, nF * nComp)) return rc;
+        if (int rc = wenoext_interpolate(P, scheme, bounded, nComp, dvf, dflux, dpnf, P->d_corr, nullptr,
+                                         WENOEXT_MEM_DEVICE, stream))
+            return rc;
+        dcorr = P->d_corr;
     }
-    if (int rc = wenoext_interpolate(P, scheme, bounded, nComp, dvf, dflux, dpnf, P->d_corr, P->d_fv,
-                                     WENOEXT_MEM_DEVICE, stream))
-        return rc;
     DivKernelArgs a{};
     a.nCells = P->nCells;
     a.nInternalFaces = P->nInt;
@@ -1994,6 +2010,7 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
     a.cellFaceStart = P->cellFaceStartD;
     a.cellFaces = P->cellFacesSortedD;
     a.owner = P->owner;
+    a.neighbour = P->neighbourD;
     a.bfPatchType = P->bfPatchType;
     a.bfNbrCell = P->bfNbrCell;
     a.vf = dvf;
@@ -2002,8 +2019,7 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
     a.c0 = P->call.c0;
     a.CB = P->call.CB;
     a.flux = dflux;
-    a.faceValue = P->d_fv;
-    a.corr = P->d_corr;
+    a.corr = dcorr;
     a.patchNbrField = dpnf;
     a.bndValue = dbnd;
     a.cellVolumes = dvol;
@@ -2014,6 +2030,7 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
     if (memKind == WENOEXT_MEM_HOST) {
         CUDA_TRY(cudaMemcpyAsync(div, ddiv, nV * 8, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
+        return haloStatus(P);
     }
     return 0;
 }

@@ -123,8 +123,11 @@ struct wenoext_plan {
     // wenoext_div: faces of a cell in ascending face index, device scratch
     int32_t* cellFaceStartD = nullptr;
     int32_t* cellFacesSortedD = nullptr;
-    double *d_corr = nullptr, *d_fv = nullptr, *d_bnd = nullptr, *d_vol = nullptr, *d_div = nullptr;
-    size_t d_corrCap = 0, d_fvCap = 0, d_bndCap = 0, d_volCap = 0, d_divCap = 0;
+    int32_t* neighbourD = nullptr;  // mesh.neighbour() [nInternalFaces]: upwind cell of a face in wenoext_div
+    bool skipD2H = false;           // host-buffer reconstruction whose face field stays on the device (wenoext_div)
+    bool volValid = false;          // d_vol holds the cell volumes of an earlier wenoext_div call
+    double *d_corr = nullptr, *d_bnd = nullptr, *d_vol = nullptr, *d_div = nullptr;
+    size_t d_corrCap = 0, d_bndCap = 0, d_volCap = 0, d_divCap = 0;
     // wenoext_set_face_flux: the flux field of this time step (device); stepFluxOwned if uploaded here
     const double* stepFlux = nullptr;
     double* stepFluxOwned = nullptr;
