@@ -539,6 +539,25 @@ def run_ours(a):
                           "h2d_bytes_per_step": int(vf_p.nbytes + phi_p.nbytes + bnd_p.nbytes),
                           "d2h_bytes_per_step": int(div_p.nbytes),
                           "what": "wenoext_div with host buffers: fvc::div(phi, vf) formed on the device"}
+            # the same with the flux uploaded once (wenoext_set_face_flux): the reference's own performance
+            # test repeats fvc::div(phi, psi) with ONE phi (performanceTest/src/main.C:150-164), and a solver
+            # reuses phi for every field of a time step; per step only vf goes up and div comes back
+            plan.set_face_flux(phi_p)
+            plan.div(FIT, a.bounded, vf_p, None, bnd_p, None, out=div_p)
+            barrier()
+            w0 = time.perf_counter()
+            for _ in range(ke):
+                plan.div(FIT, a.bounded, vf_p, None, bnd_p, None, out=div_p)
+            torch.cuda.synchronize()
+            wf = torch.tensor([(time.perf_counter() - w0) / ke], dtype=torch.float64, device=dev)
+            plan.set_face_flux(None)
+            if N > 1:
+                dist.all_reduce(wf, op=dist.ReduceOp.MAX)
+            e2e["div_flux_once"] = {"value": tot[0].item() / wf.item(), "unit": "faces/s",
+                                    "ms_per_step": wf.item() * 1e3,
+                                    "h2d_bytes_per_step": int(vf_p.nbytes + bnd_p.nbytes),
+                                    "d2h_bytes_per_step": int(div_p.nbytes),
+                                    "what": "as div, faceFlux uploaded once before the timed steps"}
         except wx.WenoextError as ex:  # e.g. a plan whose coupled patches carry no neighbour-cell map
             e2e["div"] = {"unavailable": str(ex)}
         if parity is not None:
