@@ -82,3 +82,54 @@ def test_no_gpu_means_loud_failure():
     assert rc != 0
     with pytest.raises(wx.WenoextError):
         wx.BoxCase((4, 4, 4), 2, useClassCache=False, gpuPinv=True)
+
+
+def test_plan_create_rejects_out_of_range_ids():
+    """Every index the kernels follow unchecked is validated once at plan creation: a bad
+    descriptor or a stale cache fails with a message, with or without a GPU."""
+    case = wx.BoxCase((5, 5, 5), 2, useClassCache=False)
+    d = case.desc
+
+    def expect(msg):
+        with pytest.raises(wx.WenoextError, match=msg):
+            wx.Plan(d)
+
+    e = d.stencilEntryStart[0] + 1
+    keep = d.stencilsID[e]
+    d.stencilsID[e] = case.nCells + 7
+    expect("stencil cell id out of range")
+    d.stencilsID[e] = keep
+    keep = d.owner[3]
+    d.owner[3] = -2
+    expect("owner out of range")
+    d.owner[3] = keep
+    keep = d.stencilMatrix[0]
+    d.stencilMatrix[0] = d.nUniqueMatrices
+    expect("stencilMatrix out of range")
+    d.stencilMatrix[0] = keep
+    keep = d.cellFaces[0]
+    d.cellFaces[0] = case.nFaces
+    expect("cellFaces out of range")
+    d.cellFaces[0] = keep
+    keep = d.patches[0].start
+    d.patches[0].start = 0
+    expect("outside the boundary faces")
+    d.patches[0].start = keep
+    # parallel lists
+    par = wx.BoxCase((6, 4, 4), 2, nProc=(2, 1, 1), myProc=0)
+    other = wx.BoxCase((6, 4, 4), 2, nProc=(2, 1, 1), myProc=1)
+    wx.exchange_halo_lists([par, other])
+    dp = par.desc
+    keep = dp.receiveHaloSize[1]
+    dp.receiveHaloSize[1] = 1
+    with pytest.raises(wx.WenoextError, match="halo id beyond receiveHaloSize"):
+        wx.Plan(dp)
+    dp.receiveHaloSize[1] = keep
+    keep = dp.sendHaloCellID[0]
+    dp.sendHaloCellID[0] = par.nCells
+    with pytest.raises(wx.WenoextError, match="sendHaloCellID out of range"):
+        wx.Plan(dp)
+    dp.sendHaloCellID[0] = keep
+    if wx.lib().wenoext_device_count() == 0:
+        with pytest.raises(wx.WenoextError, match="no CUDA device"):  # the intact descriptor gets that far
+            wx.Plan(d)

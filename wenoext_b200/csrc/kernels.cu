@@ -172,39 +172,22 @@ __device__ __forceinline__ uint64_t evictLastPolicy() {
 }
 // Cell values are re-read by every neighbouring stencil while 26 GB of records
 // stream through the L2 once: keep them resident (evict_last) against the stream.
-// `coh` (warp-uniform): the values may have been written by a peer GPU while this kernel runs
-// (halo region of `vals`, boundary tiles of a gated launch). The non-coherent path (.nc) is only
-// defined for data that is read-only for the kernel's lifetime, so those tiles use the coherent
-// path, which the ld.acquire.sys on the halo flag orders against the peers' writes.
+// The gathers use the coherent path (ld.global, no .nc): on parallel plans the halo region of `vals` is
+// written by peer GPUs while the gated launch runs, and .nc is only defined for data that is read-only
+// for the kernel's lifetime; the ld.acquire.sys on the halo flag orders these loads against the peers'
+// writes. Same speed as .nc here (A/B in profiles/r02_kernel_experiments.md), and no per-load predicate.
 template <int CB>
-__device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB], uint64_t pol,
-                                         const bool coh = false) {
-    const uint32_t c = coh ? 1u : 0u;
+__device__ __forceinline__ void loadVals(const double* __restrict__ p, double (&v)[CB], uint64_t pol) {
     if constexpr (CB == 1) {
-        asm volatile(
-            "{\n.reg .pred q;\nsetp.ne.u32 q, %3, 0;\n"
-            "@q ld.global.L2::cache_hint.f64 %0, [%1], %2;\n"
-            "@!q ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;\n}\n"
-            : "=d"(v[0])
-            : "l"(p), "l"(pol), "r"(c));
+        asm volatile("ld.global.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v[0]) : "l"(p), "l"(pol));
+    } else if constexpr (CB == 3) {
+        // a 3-vector sits in a 32-byte slot (VS = 4): one 256-bit load, the pad is dropped
+        double pad;
+        asm volatile("ld.global.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;"
+                     : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(pad)
+                     : "l"(p), "l"(pol));
     } else {
-        if constexpr (CB == 3) {
-            // a 3-vector sits in a 32-byte slot (VS = 4): one 256-bit load, the pad is dropped
-            double pad;
-            asm volatile(
-                "{\n.reg .pred q;\nsetp.ne.u32 q, %6, 0;\n"
-                "@q ld.global.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;\n"
-                "@!q ld.global.nc.L2::cache_hint.v4.f64 {%0, %1, %2, %3}, [%4], %5;\n}\n"
-                : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(pad)
-                : "l"(p), "l"(pol), "r"(c));
-            return;
-        }
-        asm volatile(
-            "{\n.reg .pred q;\nsetp.ne.u32 q, %4, 0;\n"
-            "@q ld.global.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;\n"
-            "@!q ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;\n}\n"
-            : "=d"(v[0]), "=d"(v[1])
-            : "l"(p), "l"(pol), "r"(c));
+        asm volatile("ld.global.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;" : "=d"(v[0]), "=d"(v[1]) : "l"(p), "l"(pol));
     }
 }
 
@@ -225,6 +208,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     constexpr int TILE = CELLS == 1 ? 16 : 4 * CELLS;  // consecutive work items a warp takes at a time
     constexpr int KP = K / 2;       // coefficient pairs per column
     constexpr bool ODD = (K & 1) != 0;
+    constexpr bool LOOKAHEAD = K * CB <= 27;  // RecInfo of the pass three ahead loaded a pass early
     const int NW = a.nWarps;
     // broadcast through a shuffle: tells the compiler the warp index is warp-uniform
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
@@ -474,19 +458,16 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                              (uint32_t)cslot * (fastCur ? a.tmaBytes[0] : (uint32_t)a.headSlotBytes);
         const uint32_t tail = tailBuf + (uint32_t)cslot * (fastCur ? a.tmaBytes[1] : (uint32_t)a.tailSlotBytes);
         const int cell = valid ? workToCell(item) : 0;
-        // boundary tiles of a gated launch read halo values that peers push during this kernel
-#ifdef WENOEXT_NO_COH  // developer A/B switch
-        const bool coh = false;
-#else
-        const bool coh = split && curTile >= nTilesA;
-#endif
         double cen[CB];
-        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV, coh);
+        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV);
         // RecInfo of the pass three ahead: with the state of this pass it is workItem(3, .), which is
         // what fetchInfo(2, .) gives once tp has moved on at the bottom of the pass (the next tile is
         // resolved at tp == 1, before any pass needs it here)
-        int cellN3;
-        const int4 rawN3 = loadInfo(3, cellN3);
+        // (only where registers allow: the K = 19 and larger instances sit at the 255-register limit and
+        // would pay for the five live registers with spills in the matrix loop)
+        int cellN3 = -1;
+        int4 rawN3 = make_int4(0, 0, 0, -1);
+        if constexpr (LOOKAHEAD) rawN3 = loadInfo(3, cellN3);
 
         // the other head slot and the tail slot were last read by the previous pass
         issueHead(infoNext, fNext, hb ^ 1);
@@ -537,7 +518,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #endif
             pfFlux = __ldg(a.flux + pfFace.x);
             if (fitBounded && (pfFace.z >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
-                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN, polV, coh);
+                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN, polV);
         }
 
         // gather of column j of this lane's stencil (WENOCoeff.C:138-156), branch-free:
@@ -558,7 +539,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                     id = 0;
                 }
 #endif
-                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d], polV, coh);
+                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d], polV);
             }
         };
         // two buffers: the columns of step ch are gathered GATHER_AHEAD = 2 steps earlier
@@ -825,7 +806,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                             for (int c = 0; c < CB; ++c) psiN[c] = pfPsiN[c];
                         } else {
-                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN, polV, coh);
+                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN, polV);
                         }
 #pragma unroll
                         for (int c = 0; c < CB; ++c) {
@@ -857,7 +838,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         infoNext = infoNN;
         fCur = fNext;
         fNext = fNN;
-        infoNN = finishInfo(rawN3, cellN3, fNN);
+        if constexpr (LOOKAHEAD)
+            infoNN = finishInfo(rawN3, cellN3, fNN);
+        else
+            infoNN = fetchInfo(2, fNN);
     }
 }
 }  // namespace

@@ -272,6 +272,87 @@ static int validateDesc(const wenoext_plan_desc* d) {
     return 0;
 }
 
+// Every index the kernels will follow without a bounds check: cell ids of the stencils (local, or
+// halo ids against receiveHaloSize of their processor), matrix ids, face and cell ids of the mesh
+// addressing, patches and their partners, the send lists. A stale constant/WENOBase* cache with matching
+// counts or a bad descriptor fails here with a message instead of an illegal address in a kernel.
+static int validateIds(const wenoext_plan_desc* d) {
+    auto bad = [](const std::string& what) {
+        setError("desc: " + what);
+        return WENOEXT_ERR_INVALID;
+    };
+    const int nC = d->nCells, nF = d->nFaces, nI = d->nInternalFaces, R = d->nProcs > 1 ? d->nProcs : 0;
+    if (d->nStencils < 0 || d->cellStencilStart[0] != 0 || d->cellStencilStart[nC] != d->nStencils)
+        return bad("cellStencilStart does not span [0, nStencils]");
+    for (int c = 0; c < nC; ++c)
+        if (d->cellStencilStart[c + 1] < d->cellStencilStart[c]) return bad("cellStencilStart is not monotone");
+    if (d->stencilEntryStart[0] != 0) return bad("stencilEntryStart does not start at 0");
+    if (d->nUniqueMatrices < 0 || d->matrixStart[0] != 0) return bad("matrix pool offsets");
+    for (int m = 0; m < d->nUniqueMatrices; ++m)
+        if (d->matrixCols[m] < 0 || d->matrixStart[m + 1] - d->matrixStart[m] != (int64_t)d->nDvt * d->matrixCols[m])
+            return bad("matrixStart does not match nDvt x matrixCols of matrix " + std::to_string(m));
+    if (R) {
+        if (d->myProc < 0 || d->myProc >= R) return bad("myProc out of range");
+        if (d->sendHaloStart[0] != 0) return bad("sendHaloStart does not start at 0");
+        for (int p = 0; p < R; ++p) {
+            if (d->receiveHaloSize[p] < 0 || d->sendHaloStart[p + 1] < d->sendHaloStart[p])
+                return bad("halo sizes of processor " + std::to_string(p));
+            for (int64_t i = d->sendHaloStart[p]; i < d->sendHaloStart[p + 1]; ++i)
+                if (d->sendHaloCellID[i] < 0 || d->sendHaloCellID[i] >= nC)
+                    return bad("sendHaloCellID out of range for processor " + std::to_string(p));
+        }
+    }
+    for (int64_t s = 0; s < d->nStencils; ++s) {
+        const int64_t e0 = d->stencilEntryStart[s], e1 = d->stencilEntryStart[s + 1];
+        if (e1 <= e0) return bad("stencil " + std::to_string(s) + " has no entries (deleted stencils keep one)");
+        if (d->stencilMatrix[s] >= d->nUniqueMatrices) return bad("stencilMatrix out of range");
+        const int32_t first = d->stencilsID[e0];
+        if (d->stencilMatrix[s] < 0 || first == WENOEXT_CELL_DELETED || first == WENOEXT_CELL_EMPTY) continue;
+        for (int64_t e = e0 + 1; e < e1; ++e) {
+            const int32_t id = d->stencilsID[e];
+            const int32_t pm = d->cellToProcMap ? d->cellToProcMap[e] : WENOEXT_CELL_LOCAL;
+            if (pm == WENOEXT_CELL_LOCAL) {
+                if (id < 0 || id >= nC) return bad("stencil cell id out of range in stencil " + std::to_string(s));
+            } else if (pm != WENOEXT_CELL_DELETED) {
+                if (pm < 0 || pm >= R) return bad("cellToProcMap names a processor out of range");
+                if (id < 0 || id >= d->receiveHaloSize[pm])
+                    return bad("halo id beyond receiveHaloSize[" + std::to_string(pm) + "] in stencil " + std::to_string(s));
+            }
+        }
+    }
+    for (int f = 0; f < nF; ++f)
+        if (d->owner[f] < 0 || d->owner[f] >= nC) return bad("owner out of range");
+    for (int f = 0; f < nI; ++f)
+        if (d->neighbour[f] < 0 || d->neighbour[f] >= nC) return bad("neighbour out of range");
+    if (d->cellFaceStart[0] != 0) return bad("cellFaceStart does not start at 0");
+    for (int c = 0; c < nC; ++c) {
+        if (d->cellFaceStart[c + 1] < d->cellFaceStart[c]) return bad("cellFaceStart is not monotone");
+        for (int i = d->cellFaceStart[c]; i < d->cellFaceStart[c + 1]; ++i)
+            if (d->cellFaces[i] < 0 || d->cellFaces[i] >= nF) return bad("cellFaces out of range");
+    }
+    if (d->nPatches < 0 || (d->nPatches > 0 && !d->patches)) return bad("patches");
+    for (int p = 0; p < d->nPatches; ++p) {
+        const wenoext_patch& pt = d->patches[p];
+        if (pt.size < 0 || pt.start < nI || (int64_t)pt.start + pt.size > nF)
+            return bad("patch " + std::to_string(p) + " lies outside the boundary faces");
+        if (pt.type == WENOEXT_PATCH_CYCLIC) {
+            if (pt.nbr < 0 || pt.nbr >= d->nPatches || d->patches[pt.nbr].type != WENOEXT_PATCH_CYCLIC ||
+                d->patches[pt.nbr].size != pt.size)
+                return bad("cyclic patch " + std::to_string(p) + " has no matching neighbour patch");
+        } else if (pt.type == WENOEXT_PATCH_PROCESSOR) {
+            if (R == 0 || pt.nbr < 0 || pt.nbr >= R || pt.nbr == d->myProc)
+                return bad("processor patch " + std::to_string(p) + " names a rank out of range");
+        }
+    }
+    if (d->patchNbrCell) {
+        int64_t nHalo = 0;
+        for (int p = 0; p < R; ++p) nHalo += d->receiveHaloSize[p];
+        for (int f = 0; f < nF - nI; ++f)
+            if (d->patchNbrCell[f] < -1 || d->patchNbrCell[f] >= nC + nHalo) return bad("patchNbrCell out of range");
+    }
+    return 0;
+}
+
 extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoext_plan** out) {
     if (!out) {
         setError("out is NULL");
@@ -279,6 +360,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     }
     *out = nullptr;
     if (int rc = validateDesc(d)) return rc;
+    if (int rc = validateIds(d)) return rc;
     int nDev = 0;
     if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0) {
         setError("no CUDA device: wenoext_b200 has no CPU fallback");
@@ -369,14 +451,24 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     std::vector<int32_t> cellNSt(nC), cellNmax(nC), cellNFc(nC);
     std::vector<RecInfo> recInfo(nC);
     int64_t algFixed = 0, flopsPerComp = 0, nLive = 0, recOff = 0;
+    // ONE liveness rule for host sizing and device expansion: a stencil is live if it has a matrix, its
+    // first entry is not Cell::deleted and its cell is not Cell::empty (WENOCoeff.C:120, :333); everything
+    // else gets matrix id -1 in the array the expansion kernel reads
+    std::vector<int32_t> liveMatrix(d->stencilMatrix, d->stencilMatrix + d->nStencils);
+    for (int c = 0; c < nC; ++c) {
+        const int64_t s0 = d->cellStencilStart[c], sE = d->cellStencilStart[c + 1];
+        const bool empty = s0 == sE || d->stencilsID[d->stencilEntryStart[s0]] == WENOEXT_CELL_EMPTY;
+        for (int64_t s = s0; s < sE; ++s)
+            if (empty || d->stencilsID[d->stencilEntryStart[s]] == WENOEXT_CELL_DELETED) liveMatrix[s] = -1;
+    }
     for (int c = 0; c < nC; ++c) {
         int nSt = 0, totN = 0, Nmax = 0;
         const int64_t s0 = d->cellStencilStart[c], sE = d->cellStencilStart[c + 1];
-        const bool empty = d->stencilsID[d->stencilEntryStart[s0]] == WENOEXT_CELL_EMPTY;
+        const bool empty = false;  // (folded into liveMatrix)
         if (!empty)
             for (int64_t s = s0; s < sE; ++s) {
-                const int m = d->stencilMatrix[s];
-                if (m < 0 || d->stencilsID[d->stencilEntryStart[s]] == WENOEXT_CELL_DELETED) continue;
+                const int m = liveMatrix[s];
+                if (m < 0) continue;
                 const int N = d->matrixCols[m];
                 if (d->stencilEntryStart[s + 1] - d->stencilEntryStart[s] != N + 1) {
                     setError("desc: stencil size does not match its matrix columns");
@@ -489,7 +581,7 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     rc = rc ? rc : up(&dSES, d->stencilEntryStart, (size_t)d->nStencils + 1);
     rc = rc ? rc : up(&dSID, d->stencilsID, (size_t)nEntries);
     if (d->cellToProcMap) rc = rc ? rc : up(&dC2P, d->cellToProcMap, (size_t)nEntries);
-    rc = rc ? rc : up(&dSM, d->stencilMatrix, (size_t)d->nStencils);
+    rc = rc ? rc : up(&dSM, liveMatrix.data(), (size_t)d->nStencils);
     rc = rc ? rc : up(&dMS, d->matrixStart, (size_t)d->nUniqueMatrices + 1);
     rc = rc ? rc : up(&dMC, d->matrixCols, (size_t)d->nUniqueMatrices);
     rc = rc ? rc : up(&dMD, d->matrixData, (size_t)d->matrixStart[d->nUniqueMatrices]);
@@ -1355,9 +1447,10 @@ static int phase0(wenoext_plan* P, bool launchInterior = true) {
     if (P->p2p) {
         pushHalo(P, c.st);
         if (!launchInterior) return 0;
-        // One launch for interior and boundary cells when the halo region of `vals` starts on
-        // a 32-byte sector (the gathers use the non-coherent path: no sector that an interior
-        // gather can have pulled into an L1 may hold halo values).
+        // One launch for interior and boundary cells. The gathers are coherent loads ordered behind
+        // the ld.acquire.sys on the halo flags; the launch is additionally kept to the case where the
+        // halo region of `vals` starts on a 32-byte sector, so that no sector an interior gather
+        // touched holds halo values at all.
         P->mergedLaunch = P->cfgMerge && P->nBoundaryCells > 0 && ((int64_t)P->nCells * c.VS) % 4 == 0;
         if (P->mergedLaunch)
             return launchCells(P, P->cellListInterior, P->nInterior + P->nBoundaryCells, 0, P->nInterior);
