@@ -109,6 +109,46 @@ typedef struct wenoext_plan_desc {
     const int32_t* patchNbrCell;
 } wenoext_plan_desc;
 
+/* The same descriptor for a WM_LABEL_SIZE=64 build of OpenFOAM (labels are int64 there,
+ * libWENOEXT/CMakeLists.txt:216; the on-disk cache carries the width, WENOBase.C:1265-1312): every array the
+ * 32-bit descriptor holds as OpenFOAM `label`s is int64 here, so the shim can pass its lists as they are.
+ * Members have the meaning of their namesakes in wenoext_plan_desc. wenoext_plan_create_labels64 checks that
+ * every value fits 32 bits (180 GB of HBM hold about 14 M order-2 cells; ids beyond 2^31 cannot occur in a
+ * plan that fits one GPU), narrows into temporaries and creates the same plan. */
+typedef struct wenoext_patch64 {
+    int64_t type, start, size, nbr;
+} wenoext_patch64;
+typedef struct wenoext_plan_desc64 {
+    int64_t polOrder, nDvt, dim[3];
+    int64_t nCells, nFaces, nInternalFaces;
+    const int64_t* owner;
+    const int64_t* neighbour;
+    const int64_t* cellFaceStart;
+    const int64_t* cellFaces;
+    int64_t nPatches;
+    const wenoext_patch64* patches;
+    int64_t nStencils;
+    const int64_t* cellStencilStart;
+    const int64_t* stencilEntryStart;
+    const int64_t* stencilsID;
+    const int64_t* cellToProcMap;
+    const int64_t* stencilMatrix;
+    int64_t nUniqueMatrices;
+    const int64_t* matrixStart;
+    const int64_t* matrixCols;
+    const double* matrixData;
+    const double* B;
+    const double* intBasTrans;
+    const double* refFacAr;
+    int64_t nProcs, myProc;
+    const int64_t* sendProcList;
+    const int64_t* receiveProcList;
+    const int64_t* receiveHaloSize;
+    const int64_t* sendHaloStart;
+    const int64_t* sendHaloCellID;
+    const int64_t* patchNbrCell;
+} wenoext_plan_desc64;
+
 typedef struct wenoext_plan wenoext_plan;
 
 typedef struct wenoext_plan_info {
@@ -132,6 +172,9 @@ int wenoext_device_count(void);
 /* Flatten + upload (once). Replaces the WENOBase::instance() lookup done in
  * WENOCoeff's constructor (WENOCoeff.C:53-99, WENOBase.H:281-294). */
 int wenoext_plan_create(const wenoext_plan_desc* desc, int device, wenoext_plan** out);
+/* wenoext_plan_create for 64-bit labels (wenoext_plan_desc64 above); WENOEXT_ERR_INVALID with the name of
+ * the array if a value does not fit 32 bits. */
+int wenoext_plan_create_labels64(const wenoext_plan_desc64* desc, int device, wenoext_plan** out);
 int wenoext_plan_destroy(wenoext_plan* plan);
 int wenoext_plan_get_info(const wenoext_plan* plan, wenoext_plan_info* info);
 

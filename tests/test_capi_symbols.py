@@ -55,14 +55,15 @@ def test_struct_layouts_match_the_header(tmp_path):
     """sizeof of every public struct as gcc lays it out from the header == the ctypes mirror"""
     import subprocess
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include "wenoext_setup.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
+    src.write_text('#include <stdio.h>\n#include "wenoext_setup.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                    'sizeof(wenoext_patch),sizeof(wenoext_plan_desc),sizeof(wenoext_plan_info),sizeof(wenoext_box_spec),'
-                   'sizeof(wenoext_setup_params),sizeof(wenoext_mesh_desc),sizeof(int));return 0;}\n')
+                   'sizeof(wenoext_setup_params),sizeof(wenoext_mesh_desc),sizeof(int),sizeof(wenoext_patch64),'
+                   'sizeof(wenoext_plan_desc64));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     want = [C.sizeof(t) for t in (_capi.Patch, _capi.PlanDesc, _capi.PlanInfo, _capi.BoxSpec, _capi.SetupParams,
-                                  _capi.MeshDesc, C.c_int)]
+                                  _capi.MeshDesc, C.c_int, _capi.Patch64, _capi.PlanDesc64)]
     assert got == want
 
 
@@ -133,3 +134,26 @@ def test_plan_create_rejects_out_of_range_ids():
     if wx.lib().wenoext_device_count() == 0:
         with pytest.raises(wx.WenoextError, match="no CUDA device"):  # the intact descriptor gets that far
             wx.Plan(d)
+
+
+def test_labels64_descriptor_is_narrowed_and_checked():
+    """wenoext_plan_create_labels64 (WM_LABEL_SIZE=64 builds): a value that does not fit 32 bits is refused
+    with the array's name; an intact descriptor reaches the same checks as the 32-bit one."""
+    case = wx.BoxCase((5, 5, 5), 2, useClassCache=False)
+    d64, keep = wx.labels64(case.desc)
+    sid = next(a for a in keep if isinstance(a, np.ndarray) and a.size == case.desc.stencilEntryStart[case.desc.nStencils])
+    old = sid[1]
+    sid[1] = 1 << 40
+    with pytest.raises(wx.WenoextError, match="stencilsID holds a value that does not fit 32 bits"):
+        wx.Plan(d64)
+    sid[1] = case.nCells + 3  # fits, but is no cell: the id validation of the 32-bit path sees it
+    with pytest.raises(wx.WenoextError, match="stencil cell id out of range"):
+        wx.Plan(d64)
+    sid[1] = old
+    d64.nCells = 1 << 33
+    with pytest.raises(wx.WenoextError, match="nCells out of range"):
+        wx.Plan(d64)
+    d64.nCells = case.nCells
+    if wx.lib().wenoext_device_count() == 0:
+        with pytest.raises(wx.WenoextError, match="no CUDA device"):
+            wx.Plan(d64)

@@ -350,3 +350,18 @@ def test_pinned_host_buffers_from_the_library():
         np.testing.assert_array_equal(np.asarray(po), want)
     finally:
         plan.destroy()
+
+
+@pytest.mark.parametrize("name", ["hex8", "cyclic", "tets_bc"])
+def test_labels64_descriptor_gives_the_same_bits(name):
+    """wenoext_plan_create_labels64: the descriptor of a WM_LABEL_SIZE=64 build (every label array int64)
+    creates the same plan: bitwise the same correction as the 32-bit descriptor, and within TOL of the oracle."""
+    case = case_of(name)
+    vf, phi = _fields(case, 3), H.rotating_flux(case)
+    d64, keep = wx.labels64(case.desc)
+    p64 = wx.Plan(d64)
+    for scheme, bounded in SCHEMES:
+        got = np.asarray(p64.correction(scheme, bounded, vf, phi))
+        assert np.array_equal(got, np.asarray(_plan(case).correction(scheme, bounded, vf, phi)))
+        assert H.normwise_err(got, Oracle("c").correction(case, scheme, bounded, vf, phi)) < TOL
+    del keep

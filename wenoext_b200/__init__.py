@@ -241,13 +241,61 @@ def pinned_empty(shape, dtype=np.float64):
     return arr
 
 
+def labels64(desc):
+    """The descriptor as a WM_LABEL_SIZE=64 build of OpenFOAM would hand it over (wenoext_plan_desc64: every
+    label array int64). Returns (PlanDesc64, keepalive): the arrays live in `keepalive`."""
+    import numpy as np
+    d64, keep = _capi.PlanDesc64(), []
+
+    def wide(ptr, n):
+        if not ptr or n <= 0:
+            return None
+        a = np.ctypeslib.as_array(ptr, shape=(int(n),)).astype(np.int64)
+        keep.append(a)
+        return a.ctypes.data_as(_capi.i64p)
+
+    for f in ("polOrder", "nDvt", "nCells", "nFaces", "nInternalFaces", "nPatches", "nStencils",
+              "nUniqueMatrices", "nProcs", "myProc"):
+        setattr(d64, f, getattr(desc, f))
+    for k in range(3):
+        d64.dim[k] = desc.dim[k]
+    nC, nF, nI, nS = desc.nCells, desc.nFaces, desc.nInternalFaces, desc.nStencils
+    d64.owner, d64.neighbour = wide(desc.owner, nF), wide(desc.neighbour, nI)
+    d64.cellFaceStart = wide(desc.cellFaceStart, nC + 1)
+    d64.cellFaces = wide(desc.cellFaces, desc.cellFaceStart[nC])
+    if desc.nPatches > 0:
+        pa = (_capi.Patch64 * desc.nPatches)()
+        for i in range(desc.nPatches):
+            q = desc.patches[i]
+            pa[i].type, pa[i].start, pa[i].size, pa[i].nbr = q.type, q.start, q.size, q.nbr
+        keep.append(pa)
+        d64.patches = pa
+    d64.cellStencilStart, d64.stencilEntryStart = desc.cellStencilStart, desc.stencilEntryStart
+    nE = desc.stencilEntryStart[nS]
+    d64.stencilsID, d64.cellToProcMap = wide(desc.stencilsID, nE), wide(desc.cellToProcMap, nE)
+    d64.stencilMatrix = wide(desc.stencilMatrix, nS)
+    d64.matrixStart, d64.matrixCols = desc.matrixStart, wide(desc.matrixCols, desc.nUniqueMatrices)
+    d64.matrixData, d64.B, d64.intBasTrans, d64.refFacAr = desc.matrixData, desc.B, desc.intBasTrans, desc.refFacAr
+    P = desc.nProcs
+    d64.sendProcList, d64.receiveProcList = wide(desc.sendProcList, P), wide(desc.receiveProcList, P)
+    d64.receiveHaloSize, d64.sendHaloStart = wide(desc.receiveHaloSize, P), desc.sendHaloStart
+    if desc.sendHaloStart and P > 0:
+        d64.sendHaloCellID = wide(desc.sendHaloCellID, desc.sendHaloStart[P])
+    d64.patchNbrCell = wide(desc.patchNbrCell, nF - nI)
+    keep.append(desc)
+    return d64, keep
+
+
 class Plan:
     """Device plan (wenoext_plan): owns all device memory of one (mesh, order)."""
 
     def __init__(self, desc, device=0):
         self._h = C.c_void_p()
         self.device = device
-        check(lib().wenoext_plan_create(C.byref(desc), device, C.byref(self._h)))
+        if isinstance(desc, _capi.PlanDesc64):  # descriptor of a WM_LABEL_SIZE=64 build
+            check(lib().wenoext_plan_create_labels64(C.byref(desc), device, C.byref(self._h)))
+        else:
+            check(lib().wenoext_plan_create(C.byref(desc), device, C.byref(self._h)))
         self.info = _capi.PlanInfo()
         check(lib().wenoext_plan_get_info(self._h, C.byref(self.info)))
         self.nCells, self.nFaces = int(self.info.nCells), int(self.info.nFaces)

@@ -47,6 +47,29 @@ class PlanDesc(C.Structure):
     ]
 
 
+class Patch64(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("type", "start", "size", "nbr")]
+
+
+class PlanDesc64(C.Structure):
+    """wenoext_plan_desc64: the descriptor of a WM_LABEL_SIZE=64 build (labels are int64)"""
+    _fields_ = [
+        ("polOrder", C.c_int64), ("nDvt", C.c_int64), ("dim", C.c_int64 * 3),
+        ("nCells", C.c_int64), ("nFaces", C.c_int64), ("nInternalFaces", C.c_int64),
+        ("owner", i64p), ("neighbour", i64p), ("cellFaceStart", i64p), ("cellFaces", i64p),
+        ("nPatches", C.c_int64), ("patches", C.POINTER(Patch64)),
+        ("nStencils", C.c_int64), ("cellStencilStart", i64p), ("stencilEntryStart", i64p),
+        ("stencilsID", i64p), ("cellToProcMap", i64p),
+        ("stencilMatrix", i64p), ("nUniqueMatrices", C.c_int64), ("matrixStart", i64p),
+        ("matrixCols", i64p), ("matrixData", f64p),
+        ("B", f64p), ("intBasTrans", f64p), ("refFacAr", f64p),
+        ("nProcs", C.c_int64), ("myProc", C.c_int64),
+        ("sendProcList", i64p), ("receiveProcList", i64p), ("receiveHaloSize", i64p),
+        ("sendHaloStart", i64p), ("sendHaloCellID", i64p),
+        ("patchNbrCell", i64p),
+    ]
+
+
 class PlanInfo(C.Structure):
     _fields_ = [(n, C.c_int64) for n in (
         "nCells", "nFaces", "nInternalFaces", "nCoupledFaces", "nLiveStencils", "nHaloCells",
@@ -78,6 +101,7 @@ SYMBOLS = {
     "wenoext_last_error": (C.c_char_p, []),
     "wenoext_device_count": (C.c_int, []),
     "wenoext_plan_create": (C.c_int, [C.POINTER(PlanDesc), C.c_int, C.POINTER(vp)]),
+    "wenoext_plan_create_labels64": (C.c_int, [C.POINTER(PlanDesc64), C.c_int, C.POINTER(vp)]),
     "wenoext_plan_destroy": (C.c_int, [vp]),
     "wenoext_plan_get_info": (C.c_int, [vp, C.POINTER(PlanInfo)]),
     "wenoext_set_params": (C.c_int, [vp, C.c_double, C.c_double, C.c_double]),

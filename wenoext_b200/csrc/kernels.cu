@@ -658,6 +658,30 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             step(ch, nxA);
             if (ch + 1 < CH) step(ch + 1, nxB);
         }
+#ifdef WENOEXT_PREFETCH_NEXT
+        // The first gathers of a pass wait a whole L2 round trip right behind the head (the top
+        // long_scoreboard line of every capture). The next pass's head has been in flight since the
+        // start of this pass: pull the cell values its first WENOEXT_PREFETCH_NEXT columns will gather
+        // into L1 now, under the tail phase (no registers live across it).
+        {
+            const int itemN = cslot < CELLS ? workItem(1, cslot) : -1;
+            mbarWait(bars + (hb ^ 1) * 8, (uint32_t)((i + 1) >> 1) & 1u);
+            if (itemN >= 0) {
+                const uint32_t recN = headBuf + (uint32_t)((hb ^ 1) * CELLS) * a.headSlotBytes +
+                                      (uint32_t)cslot * (fNext >= 0 ? a.tmaBytes[0] : (uint32_t)a.headSlotBytes);
+                const int4 h0 = lds128i(recN), h1 = lds128i(recN + 16);
+                if (s < h0.x) {
+#pragma unroll
+                    for (int d = 0; d < WENOEXT_PREFETCH_NEXT; ++d)
+                        if (d < h0.z) {
+                            const int id = lds32(recN + (uint32_t)h1.y + (uint32_t)(d * h0.x + s) * 4);
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.vals + (size_t)id * a.VS));
+                        }
+                }
+                if (s == 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.vals + (size_t)workToCell(itemN) * a.VS));
+            }
+        }
+#endif
         // phase 2: IS = c^T (B c) per component                  (WENOCoeff.C:190-196)
         mbarWait(barTail, (uint32_t)i & 1u);
         double g[CB];
@@ -668,7 +692,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             // B arrives folded (diagonal, then B[k][q] + B[q][k] for q > k, device_plan.h):
             // IS = sum_k c_k (B_kk c_k + sum_{q>k} (B_kq + B_qk) c_q), K(K+1)/2 products per
             // component instead of K^2
-            uint32_t Bb = tail;
+            // (the triangle is read pairwise, 128 bits at a time: t counts its entries in storage order)
+            double2 bpair = make_double2(0.0, 0.0);
+            int t = 0;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 double u[CB];
@@ -676,8 +702,17 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 for (int c = 0; c < CB; ++c) u[c] = 0.0;
 #pragma unroll
                 for (int q = k; q < K; ++q) {
-                    const double bq = lds64(Bb);
-                    Bb += 8;
+                    double bq;
+                    if constexpr (LOOKAHEAD) {
+                        if ((t & 1) == 0)
+                            bpair = t + 1 < symTriSize(K) ? lds128(tail + (uint32_t)t * 8)
+                                                           : make_double2(lds64(tail + (uint32_t)t * 8), 0.0);
+                        bq = (t & 1) ? bpair.y : bpair.x;
+                    } else {
+                        // (the instances at the register limit: one word at a time, as measured faster there)
+                        bq = lds64(tail + (uint32_t)t * 8);
+                    }
+                    ++t;
 #pragma unroll
                     for (int c = 0; c < CB; ++c) u[c] = fma(bq, acc[q][c], u[c]);
                 }
@@ -692,9 +727,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 bs[c] = a.eps + IS[c];
                 pw[c] = 1.0;
             }
-            for (uint32_t e = 0; e < a.pExp; ++e)
+            if (a.pExp == 4) {
+                // the default p: the same products in the same order (1.0 * bs is exact), no loop
 #pragma unroll
-                for (int c = 0; c < CB; ++c) pw[c] *= bs[c];
+                for (int c = 0; c < CB; ++c) pw[c] = ((bs[c] * bs[c]) * bs[c]) * bs[c];
+            } else {
+                for (uint32_t e = 0; e < a.pExp; ++e)
+#pragma unroll
+                    for (int c = 0; c < CB; ++c) pw[c] *= bs[c];
+            }
 #pragma unroll
             for (int c = 0; c < CB; ++c) g[c] = act ? (s == 0 ? a.dm : 1.0) * safeRcp(pw[c]) : 0.0;
         }
@@ -811,7 +852,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                         for (int c = 0; c < CB; ++c) {
                             const double dpsi = fabs(cen[c] - psiN[c]);
-                            if (fabs(out[c]) > dpsi) out[c] = fmin(dpsi * safeRcp(fabs(out[c])), 1.0) * out[c];
+                            // theta = min(dpsi / |corr|, 1) with |corr| > dpsi: corr * theta is corr's sign on dpsi
+                            // (the product differs from it by rounding only; no division, no reciprocal)
+                            if (fabs(out[c]) > dpsi) out[c] = copysign(dpsi, out[c]);
                         }
                     }
                 }
@@ -1030,6 +1073,11 @@ int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t sme
         a.ringSteps > 27 || (a.cellsPerWarp != 5 && a.cellsPerWarp != 4 && a.cellsPerWarp != 1))
         return 1;
     switch (a.K) {
+#ifdef WENOEXT_DEV_ONLY_K  // developer builds: one polynomial space only (compile time)
+        case WENOEXT_DEV_ONLY_K: return launchK<WENOEXT_DEV_ONLY_K, chunkCols(WENOEXT_DEV_ONLY_K)>(a, CB, gridBlocks, smemBytes, st);
+        default: return 1;
+    }
+#else
         case 2: return launchK<2, chunkCols(2)>(a, CB, gridBlocks, smemBytes, st);
         case 3: return launchK<3, chunkCols(3)>(a, CB, gridBlocks, smemBytes, st);
         case 5: return launchK<5, chunkCols(5)>(a, CB, gridBlocks, smemBytes, st);
@@ -1040,6 +1088,7 @@ int launchCellKernel(const CellKernelArgs& a, int CB, int gridBlocks, size_t sme
         case 34: return launchK<34, chunkCols(34)>(a, CB, gridBlocks, smemBytes, st);
         default: return 1;
     }
+#endif
 }
 
 void launchGatherRows(const double* src, const int32_t* rows, int64_t n, int nComp, double* dst,

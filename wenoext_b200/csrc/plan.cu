@@ -795,6 +795,96 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     return 0;
 }
 
+// 64-bit labels (WM_LABEL_SIZE=64 builds): narrow every label array into temporaries, refusing values
+// that do not fit, and create the plan from the 32-bit descriptor. The lengths come from the CSR offsets
+// of the descriptor itself, so the offsets are looked at before the arrays they index.
+extern "C" int wenoext_plan_create_labels64(const wenoext_plan_desc64* d, int device, wenoext_plan** out) {
+    if (!d || !out) {
+        setError("desc64 or out is NULL");
+        return WENOEXT_ERR_INVALID;
+    }
+    const char* bad = nullptr;
+    auto fits = [](int64_t v) { return v >= INT32_MIN && v <= INT32_MAX; };
+    auto scalar = [&](int64_t v, const char* name) {
+        if (!fits(v) && !bad) bad = name;
+        return (int32_t)v;
+    };
+    auto narrow = [&](const int64_t* src, int64_t n, const char* name, std::vector<int32_t>& dst) -> const int32_t* {
+        if (!src || n <= 0) return nullptr;
+        dst.resize((size_t)n);
+        for (int64_t i = 0; i < n; ++i) {
+            if (!fits(src[i])) {
+                if (!bad) bad = name;
+                return nullptr;
+            }
+            dst[(size_t)i] = (int32_t)src[i];
+        }
+        return dst.data();
+    };
+    wenoext_plan_desc n{};
+    n.polOrder = scalar(d->polOrder, "polOrder");
+    n.nDvt = scalar(d->nDvt, "nDvt");
+    for (int k = 0; k < 3; ++k) n.dim[k] = scalar(d->dim[k], "dim");
+    n.nCells = scalar(d->nCells, "nCells");
+    n.nFaces = scalar(d->nFaces, "nFaces");
+    n.nInternalFaces = scalar(d->nInternalFaces, "nInternalFaces");
+    n.nPatches = scalar(d->nPatches, "nPatches");
+    n.nUniqueMatrices = scalar(d->nUniqueMatrices, "nUniqueMatrices");
+    n.nProcs = scalar(d->nProcs, "nProcs");
+    n.myProc = scalar(d->myProc, "myProc");
+    n.nStencils = d->nStencils;
+    if (!bad && (n.nCells <= 0 || n.nFaces < n.nInternalFaces || n.nInternalFaces < 0 || n.nPatches < 0 ||
+                 n.nStencils < 0 || n.nUniqueMatrices < 0 || n.nProcs < 0))
+        bad = "sizes";
+    if (!bad && (!d->cellFaceStart || !d->cellStencilStart || !d->stencilEntryStart)) bad = "CSR offsets (NULL)";
+    if (bad) {
+        setError(std::string("desc64: ") + bad + " out of range");
+        return WENOEXT_ERR_INVALID;
+    }
+    std::vector<int32_t> owner, nei, cfs, cf, sid, c2p, sm, mc, spl, rpl, rhs, shc, pnc;
+    std::vector<wenoext_patch> patches;
+    n.owner = narrow(d->owner, n.nFaces, "owner", owner);
+    n.neighbour = narrow(d->neighbour, n.nInternalFaces, "neighbour", nei);
+    n.cellFaceStart = narrow(d->cellFaceStart, (int64_t)n.nCells + 1, "cellFaceStart", cfs);
+    const int64_t nCF = n.cellFaceStart ? d->cellFaceStart[n.nCells] : 0;
+    n.cellFaces = narrow(d->cellFaces, nCF, "cellFaces", cf);
+    if (d->patches && n.nPatches > 0) {
+        patches.resize((size_t)n.nPatches);
+        for (int i = 0; i < n.nPatches; ++i) {
+            patches[i].type = scalar(d->patches[i].type, "patches.type");
+            patches[i].start = scalar(d->patches[i].start, "patches.start");
+            patches[i].size = scalar(d->patches[i].size, "patches.size");
+            patches[i].nbr = scalar(d->patches[i].nbr, "patches.nbr");
+        }
+        n.patches = patches.data();
+    }
+    n.cellStencilStart = d->cellStencilStart;
+    n.stencilEntryStart = d->stencilEntryStart;
+    const int64_t nEntries = d->stencilEntryStart[n.nStencils];
+    if (nEntries < 0) bad = "stencilEntryStart";
+    n.stencilsID = narrow(d->stencilsID, nEntries, "stencilsID", sid);
+    n.cellToProcMap = narrow(d->cellToProcMap, nEntries, "cellToProcMap", c2p);
+    n.stencilMatrix = narrow(d->stencilMatrix, n.nStencils, "stencilMatrix", sm);
+    n.matrixStart = d->matrixStart;
+    n.matrixCols = narrow(d->matrixCols, n.nUniqueMatrices, "matrixCols", mc);
+    n.matrixData = d->matrixData;
+    n.B = d->B;
+    n.intBasTrans = d->intBasTrans;
+    n.refFacAr = d->refFacAr;
+    n.sendProcList = narrow(d->sendProcList, n.nProcs, "sendProcList", spl);
+    n.receiveProcList = narrow(d->receiveProcList, n.nProcs, "receiveProcList", rpl);
+    n.receiveHaloSize = narrow(d->receiveHaloSize, n.nProcs, "receiveHaloSize", rhs);
+    n.sendHaloStart = d->sendHaloStart;
+    if (d->sendHaloStart && d->sendHaloCellID && n.nProcs > 0)
+        n.sendHaloCellID = narrow(d->sendHaloCellID, d->sendHaloStart[n.nProcs], "sendHaloCellID", shc);
+    n.patchNbrCell = narrow(d->patchNbrCell, (int64_t)n.nFaces - n.nInternalFaces, "patchNbrCell", pnc);
+    if (bad) {
+        setError(std::string("desc64: ") + bad + " holds a value that does not fit 32 bits");
+        return WENOEXT_ERR_INVALID;
+    }
+    return wenoext_plan_create(&n, device, out);
+}
+
 extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (!P) return 0;
     cudaSetDevice(P->device);
