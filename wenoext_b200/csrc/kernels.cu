@@ -288,6 +288,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
     // ---- issue side (lanes 0..CELLS-1; lane c serves cell c of a pass) ----
     const uint64_t pol = evictFirstPolicy();
     const uint64_t polV = evictLastPolicy();
+    // row `id` of the packed values: one 32 x 32 -> 64 bit multiply-add on the base (ids are >= 0)
+    const uint32_t valRowBytes = (uint32_t)a.VS * 8u;
+    // (TRIM: the changes of round 2's last kernel pass apply to the instances with K * CB <= 27 only; the
+    // K = 19 and larger instances sit at 255 registers with a stack frame, and every one of these changes
+    // moved their spills to worse places: c4 7.36 -> 7.64 ms, profiles/r02_kernel_experiments.md)
+    auto valRow = [&](int id) {
+        if constexpr (K * CB <= 27)
+            return reinterpret_cast<const double*>(reinterpret_cast<const unsigned char*>(a.vals) +
+                                                   (uint64_t)(uint32_t)id * valRowBytes);
+        else
+            return a.vals + (size_t)id * a.VS;
+    };
     const bool issuer = lane < CELLS;
     // RecInfo of cell `lane` of the pass k passes ahead; w < 0: no such cell
     // Fast passes: the CELLS cells are consecutive cells of the layout the tensor maps were
@@ -459,7 +471,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
         const uint32_t tail = tailBuf + (uint32_t)cslot * (fastCur ? a.tmaBytes[1] : (uint32_t)a.tailSlotBytes);
         const int cell = valid ? workToCell(item) : 0;
         double cen[CB];
-        loadVals<CB>(a.vals + (size_t)cell * a.VS, cen, polV);
+        loadVals<CB>(valRow(cell), cen, polV);
         // RecInfo of the pass three ahead: with the state of this pass it is workItem(3, .), which is
         // what fetchInfo(2, .) gives once tp has moved on at the bottom of the pass (the next tile is
         // resolved at tp == 1, before any pass needs it here)
@@ -518,7 +530,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #endif
             pfFlux = __ldg(a.flux + pfFace.x);
             if (fitBounded && (pfFace.z >> FACE_TYPE_SHIFT) == FACE_INTERNAL)
-                loadVals<CB>(a.vals + (size_t)pfFace.y * a.VS, pfPsiN, polV);
+                loadVals<CB>(valRow(pfFace.y), pfPsiN, polV);
         }
 
         // gather of column j of this lane's stencil (WENOCoeff.C:138-156), branch-free:
@@ -539,7 +551,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                     id = 0;
                 }
 #endif
-                loadVals<CB>(a.vals + (size_t)id * a.VS, g[d], polV);
+                loadVals<CB>(valRow(id), g[d], polV);
             }
         };
         // two buffers: the columns of step ch are gathered GATHER_AHEAD = 2 steps earlier
@@ -695,6 +707,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
             // (the triangle is read pairwise, 128 bits at a time: t counts its entries in storage order)
             double2 bpair = make_double2(0.0, 0.0);
             int t = 0;
+            uint32_t Bb = tail;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 double u[CB];
@@ -709,8 +722,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                                                            : make_double2(lds64(tail + (uint32_t)t * 8), 0.0);
                         bq = (t & 1) ? bpair.y : bpair.x;
                     } else {
-                        // (the instances at the register limit: one word at a time, as measured faster there)
-                        bq = lds64(tail + (uint32_t)t * 8);
+                        bq = lds64(Bb);  // one word at a time off a running pointer
+                        Bb += 8;
                     }
                     ++t;
 #pragma unroll
@@ -727,7 +740,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
                 bs[c] = a.eps + IS[c];
                 pw[c] = 1.0;
             }
-            if (a.pExp == 4) {
+            if (LOOKAHEAD && a.pExp == 4) {
                 // the default p: the same products in the same order (1.0 * bs is exact), no loop
 #pragma unroll
                 for (int c = 0; c < CB; ++c) pw[c] = ((bs[c] * bs[c]) * bs[c]) * bs[c];
@@ -847,14 +860,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1)
 #pragma unroll
                             for (int c = 0; c < CB; ++c) psiN[c] = pfPsiN[c];
                         } else {
-                            loadVals<CB>(a.vals + (size_t)fi.y * a.VS, psiN, polV);
+                            loadVals<CB>(valRow(fi.y), psiN, polV);
                         }
 #pragma unroll
                         for (int c = 0; c < CB; ++c) {
                             const double dpsi = fabs(cen[c] - psiN[c]);
                             // theta = min(dpsi / |corr|, 1) with |corr| > dpsi: corr * theta is corr's sign on dpsi
                             // (the product differs from it by rounding only; no division, no reciprocal)
-                            if (fabs(out[c]) > dpsi) out[c] = copysign(dpsi, out[c]);
+                            if constexpr (LOOKAHEAD) {
+                                if (fabs(out[c]) > dpsi) out[c] = copysign(dpsi, out[c]);
+                            } else {
+                                if (fabs(out[c]) > dpsi) out[c] = fmin(dpsi * safeRcp(fabs(out[c])), 1.0) * out[c];
+                            }
                         }
                     }
                 }
