@@ -296,6 +296,49 @@ int wenoext_pinv_batched(int32_t nMat, int32_t n, const int32_t* rows, const int
                          const double* A, double minCondition, double* Ainv, int32_t* nZeros,
                          double* condition, int32_t* converged, int device);
 
+/* Least-squares matrices assembled on the GPU and pseudo-inverted there: the device
+ * counterpart of the row loop of WENOBase::calcMatrix (WENOBase.C:410-597) -- geometryWENO::transformIntegral
+ * (geometryWENO.C:222-325, divergence theorem over the triangulated cell surface with the 13-point rule of
+ * geometryWENO.C:346-460) and WENOBase::calcGeom / addCoeffs (WENOBase.C:600-670) for every (target cell,
+ * stencil cell) pair -- followed by the batched pseudo-inverse of wenoext_pinv_batched on the same device
+ * buffers: only the mesh, the frames and index lists go up, only the pseudo-inverses come back.
+ *   source mesh   points [nPoints][3]; triangles of cell c: triPoints[triStart[c] .. triStart[c+1])[3]
+ *                 (fan of every face, in the cell's face order); cellCentres [nSrcCells][3]; cellVolumes
+ *   frames        reference frame of a target cell (geometryWENO::initIntegrals, geometryWENO.C:42-219):
+ *                 JInv [9] row-major, refPoint [3], refDet, frameCell = its cell in the source mesh,
+ *                 volI = its own volume moments, cube of (polOrder+1)^3 (List3D.H:238)
+ *   pairs         row p of the LS system: stencil cell pairCell[p] seen from frame pairFrame[p]
+ *   matrices      matrix i has rows[i] rows of nDvt at start[i] (doubles, dense: start[i+1] = start[i] +
+ *                 rows[i]*nDvt); its row r is pair rowPair[start[i]/nDvt + r]
+ * Ainv_i is nDvt x rows[i] row-major at Ainv + start[i]; nZeros, condition (nullable), converged as in
+ * wenoext_pinv_batched. rowsOut (nullable) [nPairs][nDvt] and Aout (nullable) return the assembled rows and
+ * matrices (tests). Host pointers. The rows are bitwise those of the host setup path. */
+typedef struct wenoext_ls_batch {
+    int32_t polOrder, nDvt, dim[3];
+    int32_t nPoints, nSrcCells;
+    const double* points;
+    const int64_t* triStart;
+    const int32_t* triPoints;
+    const double* cellCentres;
+    const double* cellVolumes;
+    int32_t nFrames;
+    const double* JInv;
+    const double* refPoint;
+    const double* refDet;
+    const int32_t* frameCell;
+    const double* volI;
+    int64_t nPairs;
+    const int32_t* pairFrame;
+    const int32_t* pairCell;
+    int32_t nMat;
+    const int32_t* rows;
+    const int64_t* start;
+    const int64_t* rowPair;
+} wenoext_ls_batch;
+int wenoext_ls_pinv_batched(const wenoext_ls_batch* batch, double minCondition, double* Ainv,
+                            int32_t* nZeros, double* condition, int32_t* converged, double* rowsOut,
+                            double* Aout, int device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,15 +55,15 @@ def test_struct_layouts_match_the_header(tmp_path):
     """sizeof of every public struct as gcc lays it out from the header == the ctypes mirror"""
     import subprocess
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include "wenoext_setup.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
+    src.write_text('#include <stdio.h>\n#include "wenoext_setup.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                    'sizeof(wenoext_patch),sizeof(wenoext_plan_desc),sizeof(wenoext_plan_info),sizeof(wenoext_box_spec),'
                    'sizeof(wenoext_setup_params),sizeof(wenoext_mesh_desc),sizeof(int),sizeof(wenoext_patch64),'
-                   'sizeof(wenoext_plan_desc64));return 0;}\n')
+                   'sizeof(wenoext_plan_desc64),sizeof(wenoext_ls_batch));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     want = [C.sizeof(t) for t in (_capi.Patch, _capi.PlanDesc, _capi.PlanInfo, _capi.BoxSpec, _capi.SetupParams,
-                                  _capi.MeshDesc, C.c_int, _capi.Patch64, _capi.PlanDesc64)]
+                                  _capi.MeshDesc, C.c_int, _capi.Patch64, _capi.PlanDesc64, _capi.LsBatch)]
     assert got == want
 
 

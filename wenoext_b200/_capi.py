@@ -70,6 +70,19 @@ class PlanDesc64(C.Structure):
     ]
 
 
+class LsBatch(C.Structure):
+    """wenoext_ls_batch: least-squares rows, matrices and pseudo-inverses in one device batch"""
+    _fields_ = [
+        ("polOrder", C.c_int32), ("nDvt", C.c_int32), ("dim", C.c_int32 * 3),
+        ("nPoints", C.c_int32), ("nSrcCells", C.c_int32),
+        ("points", f64p), ("triStart", i64p), ("triPoints", i32p), ("cellCentres", f64p), ("cellVolumes", f64p),
+        ("nFrames", C.c_int32), ("JInv", f64p), ("refPoint", f64p), ("refDet", f64p), ("frameCell", i32p),
+        ("volI", f64p),
+        ("nPairs", C.c_int64), ("pairFrame", i32p), ("pairCell", i32p),
+        ("nMat", C.c_int32), ("rows", i32p), ("start", i64p), ("rowPair", i64p),
+    ]
+
+
 class PlanInfo(C.Structure):
     _fields_ = [(n, C.c_int64) for n in (
         "nCells", "nFaces", "nInternalFaces", "nCoupledFaces", "nLiveStencils", "nHaloCells",
@@ -122,6 +135,7 @@ SYMBOLS = {
     "wenoext_last_launch_count": (C.c_int, [vp]),
     "wenoext_enable_kernel_timing": (C.c_int, [vp, C.c_int]),
     "wenoext_kernel_time": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_int]),
+    "wenoext_ls_pinv_batched": (C.c_int, [C.POINTER(LsBatch), C.c_double, f64p, i32p, f64p, i32p, f64p, f64p, C.c_int]),
     "wenoext_pinv_batched": (C.c_int, [C.c_int32, C.c_int32, i32p, i64p, f64p, C.c_double, f64p, i32p, f64p,
                                         i32p, C.c_int]),
 }

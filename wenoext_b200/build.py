@@ -17,7 +17,10 @@ CSRC = os.path.join(ROOT, "wenoext_b200", "csrc")
 LIB = os.path.join(ROOT, "wenoext_b200", "libwenoext_b200.so")
 SETUP_LIB = os.path.join(ROOT, "wenoext_b200", "libwenoext_setup.so")
 
-CU_SOURCES = ["kernels.cu", "plan.cu", "pinv.cu", "noalloc.cu"]
+CU_SOURCES = ["kernels.cu", "plan.cu", "pinv.cu", "noalloc.cu", "ls_rows.cu"]
+# ls_rows.cu repeats the host setup arithmetic operation for operation: no FMA contraction, so that its
+# rows are bitwise the host's (the host library is built for baseline x86-64, which has no FMA)
+CU_EXTRA_FLAGS = {"ls_rows.cu": ["--fmad=false"]}
 CPP_SOURCES = [
     "capi_setup.cpp",
     "setup/polymesh.cpp",
@@ -76,6 +79,7 @@ def build_product(force=False, verbose=False):
             cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo"] + common
             if src.endswith(".cu"):
                 cmd += ["-Xptxas", "-v"] if verbose else []
+            cmd += CU_EXTRA_FLAGS.get(src, [])
             cmd += ["-c", path, "-o", obj]
             subprocess.run(cmd, check=True)
             rebuilt = True

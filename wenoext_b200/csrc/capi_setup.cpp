@@ -9,6 +9,7 @@
 
 #include <dlfcn.h>
 
+#include "../../include/wenoext_b200.h"
 #include "../../include/wenoext_setup.h"
 #include "setup/pinv_device.h"
 #include "setup/box_fast.h"
@@ -27,12 +28,7 @@ extern "C" const char* wenoext_setup_last_error(void) { return g_setupError.c_st
 // The optional device batch of the pseudo-inverses (wenoext_setup_params::gpuPinv) lives in the product
 // library; it is looked up at run time in libwenoext_b200.so next to this library, so that nothing here
 // links against CUDA.
-int wenoext::pinvBatchedDevice(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
-                               const double* A, double minCondition, double* Ainv, int32_t* nZeros,
-                               double* condition, int32_t* converged, std::string& err) {
-    typedef int (*Fn)(int32_t, int32_t, const int32_t*, const int64_t*, const double*, double, double*, int32_t*,
-                      double*, int32_t*, int);
-    typedef const char* (*ErrFn)(void);
+static void* productLibrary() {
     static void* handle = nullptr;
     if (!handle) {
         Dl_info info{};
@@ -45,6 +41,16 @@ int wenoext::pinvBatchedDevice(int device, int32_t nMat, int32_t n, const int32_
         handle = dlopen((dir + "/libwenoext_b200.so").c_str(), RTLD_NOW | RTLD_LOCAL);
         if (!handle) handle = dlopen("libwenoext_b200.so", RTLD_NOW | RTLD_LOCAL);
     }
+    return handle;
+}
+
+int wenoext::pinvBatchedDevice(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
+                               const double* A, double minCondition, double* Ainv, int32_t* nZeros,
+                               double* condition, int32_t* converged, std::string& err) {
+    typedef int (*Fn)(int32_t, int32_t, const int32_t*, const int64_t*, const double*, double, double*, int32_t*,
+                      double*, int32_t*, int);
+    typedef const char* (*ErrFn)(void);
+    void* handle = productLibrary();
     Fn fn = handle ? (Fn)dlsym(handle, "wenoext_pinv_batched") : nullptr;
     if (!fn) {
         err = "gpuPinv: libwenoext_b200.so (wenoext_pinv_batched) not found next to libwenoext_setup.so";
@@ -54,6 +60,49 @@ int wenoext::pinvBatchedDevice(int device, int32_t nMat, int32_t n, const int32_
     if (rc) {
         ErrFn ef = (ErrFn)dlsym(handle, "wenoext_last_error");
         err = ef ? ef() : "wenoext_pinv_batched failed";
+    }
+    return rc;
+}
+
+// wenoext_ls_pinv_batched of the product library (csrc/ls_rows.cu), found the same way
+int wenoext::lsPinvBatchedDevice(int device, const LsBatchHost& h, double minCondition, double* Ainv,
+                                 int32_t* nZeros, double* condition, int32_t* converged, std::string& err) {
+    typedef int (*Fn)(const wenoext_ls_batch*, double, double*, int32_t*, double*, int32_t*, double*, double*, int);
+    typedef const char* (*ErrFn)(void);
+    void* handle = productLibrary();
+    Fn fn = handle ? (Fn)dlsym(handle, "wenoext_ls_pinv_batched") : nullptr;
+    if (!fn) {
+        err = "gpuPinv: libwenoext_b200.so (wenoext_ls_pinv_batched) not found next to libwenoext_setup.so";
+        return WENOEXT_ERR_SETUP;
+    }
+    wenoext_ls_batch b{};
+    b.polOrder = h.polOrder;
+    b.nDvt = h.nDvt;
+    for (int k = 0; k < 3; ++k) b.dim[k] = h.dim[k];
+    b.nPoints = (int32_t)(h.points.size() / 3);
+    b.nSrcCells = (int32_t)h.cellVolumes.size();
+    b.points = h.points.data();
+    b.triStart = h.triStart.data();
+    b.triPoints = h.triPoints.data();
+    b.cellCentres = h.cellCentres.data();
+    b.cellVolumes = h.cellVolumes.data();
+    b.nFrames = (int32_t)h.frameCell.size();
+    b.JInv = h.JInv.data();
+    b.refPoint = h.refPoint.data();
+    b.refDet = h.refDet.data();
+    b.frameCell = h.frameCell.data();
+    b.volI = h.volI.data();
+    b.nPairs = (int64_t)h.pairCell.size();
+    b.pairFrame = h.pairFrame.data();
+    b.pairCell = h.pairCell.data();
+    b.nMat = (int32_t)h.rows.size();
+    b.rows = h.rows.data();
+    b.start = h.start.data();
+    b.rowPair = h.rowPair.data();
+    const int rc = fn(&b, minCondition, Ainv, nZeros, condition, converged, nullptr, nullptr, device);
+    if (rc) {
+        ErrFn ef = (ErrFn)dlsym(handle, "wenoext_last_error");
+        err = ef ? ef() : "wenoext_ls_pinv_batched failed";
     }
     return rc;
 }

@@ -142,19 +142,16 @@ struct DevBuf {
 
 namespace wenoext {
 
-int pinvBatchedImpl(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
-                      const double* A, double minCondition, double* Ainv, int32_t* nZeros, double* condition,
-                      int32_t* converged, std::string& err) {
+// The batch on matrices that already sit on the device (ls_rows.cu assembles them there): launch geometry,
+// shared-memory opt-in, one launch, synchronised on return.
+int pinvBatchedOnDevice(int device, int32_t nMat, int32_t n, int maxRows, const int32_t* dRows,
+                        const int64_t* dStart, const double* dA, double minCondition, double* dP,
+                        int32_t* dZeros, double* dCond, int32_t* dConv, std::string& err) {
     if (nMat <= 0) return 0;
     auto fail = [&](const char* what, cudaError_t e) {
         err = std::string(what) + ": " + cudaGetErrorString(e);
         return WENOEXT_ERR_CUDA;
     };
-    cudaError_t e = cudaSetDevice(device);
-    if (e != cudaSuccess) return fail("pinv: cudaSetDevice", e);
-    int maxRows = 0;
-    for (int i = 0; i < nMat; ++i) maxRows = std::max(maxRows, rows[i]);
-    const size_t total = (size_t)start[nMat];
     const size_t smem = PINV_WARPS * ((size_t)maxRows * n + (size_t)n * n + n) * sizeof(double);
     int smemMax = 0;
     cudaDeviceGetAttribute(&smemMax, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
@@ -162,20 +159,8 @@ int pinvBatchedImpl(int device, int32_t nMat, int32_t n, const int32_t* rows, co
         err = "pinv: matrices do not fit the shared memory";
         return WENOEXT_ERR_INVALID;
     }
-    DevBuf<int32_t> dRows, dZ, dConv;
-    DevBuf<int64_t> dStart;
-    DevBuf<double> dA, dP, dCond;
-    if ((e = dRows.alloc(nMat)) != cudaSuccess || (e = dZ.alloc(nMat)) != cudaSuccess ||
-        (e = dConv.alloc(nMat)) != cudaSuccess || (e = dStart.alloc((size_t)nMat + 1)) != cudaSuccess ||
-        (e = dA.alloc(total)) != cudaSuccess || (e = dP.alloc(total)) != cudaSuccess ||
-        (e = dCond.alloc(nMat)) != cudaSuccess)
-        return fail("pinv: cudaMalloc", e);
-    cudaMemcpy(dRows.p, rows, (size_t)nMat * 4, cudaMemcpyHostToDevice);
-    cudaMemcpy(dStart.p, start, ((size_t)nMat + 1) * 8, cudaMemcpyHostToDevice);
-    e = cudaMemcpy(dA.p, A, total * 8, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) return fail("pinv: upload", e);
-    PinvArgs a{nMat, n, maxRows, dRows.p, dStart.p, dA.p, minCondition, dP.p, dZ.p, dCond.p, dConv.p};
-    e = cudaFuncSetAttribute(pinv_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    PinvArgs a{nMat, n, maxRows, dRows, dStart, dA, minCondition, dP, dZeros, dCond, dConv};
+    cudaError_t e = cudaFuncSetAttribute(pinv_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail("pinv: shared memory", e);
     int nSM = 148;
     cudaDeviceGetAttribute(&nSM, cudaDevAttrMultiProcessorCount, device);
@@ -197,6 +182,37 @@ int pinvBatchedImpl(int device, int32_t nMat, int32_t n, const int32_t* rows, co
     cudaEventDestroy(t0);
     cudaEventDestroy(t1);
     if (e != cudaSuccess) return fail("pinv_batched_kernel", e);
+    return 0;
+}
+
+int pinvBatchedImpl(int device, int32_t nMat, int32_t n, const int32_t* rows, const int64_t* start,
+                      const double* A, double minCondition, double* Ainv, int32_t* nZeros, double* condition,
+                      int32_t* converged, std::string& err) {
+    if (nMat <= 0) return 0;
+    auto fail = [&](const char* what, cudaError_t e) {
+        err = std::string(what) + ": " + cudaGetErrorString(e);
+        return WENOEXT_ERR_CUDA;
+    };
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail("pinv: cudaSetDevice", e);
+    int maxRows = 0;
+    for (int i = 0; i < nMat; ++i) maxRows = std::max(maxRows, rows[i]);
+    const size_t total = (size_t)start[nMat];
+    DevBuf<int32_t> dRows, dZ, dConv;
+    DevBuf<int64_t> dStart;
+    DevBuf<double> dA, dP, dCond;
+    if ((e = dRows.alloc(nMat)) != cudaSuccess || (e = dZ.alloc(nMat)) != cudaSuccess ||
+        (e = dConv.alloc(nMat)) != cudaSuccess || (e = dStart.alloc((size_t)nMat + 1)) != cudaSuccess ||
+        (e = dA.alloc(total)) != cudaSuccess || (e = dP.alloc(total)) != cudaSuccess ||
+        (e = dCond.alloc(nMat)) != cudaSuccess)
+        return fail("pinv: cudaMalloc", e);
+    cudaMemcpy(dRows.p, rows, (size_t)nMat * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(dStart.p, start, ((size_t)nMat + 1) * 8, cudaMemcpyHostToDevice);
+    e = cudaMemcpy(dA.p, A, total * 8, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return fail("pinv: upload", e);
+    if (int rc = pinvBatchedOnDevice(device, nMat, n, maxRows, dRows.p, dStart.p, dA.p, minCondition, dP.p, dZ.p,
+                                     dCond.p, dConv.p, err))
+        return rc;
     cudaMemcpy(Ainv, dP.p, total * 8, cudaMemcpyDeviceToHost);
     cudaMemcpy(nZeros, dZ.p, (size_t)nMat * 4, cudaMemcpyDeviceToHost);
     cudaMemcpy(converged, dConv.p, (size_t)nMat * 4, cudaMemcpyDeviceToHost);

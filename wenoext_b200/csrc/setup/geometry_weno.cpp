@@ -95,6 +95,10 @@ void surfaceMoments(const PolyMesh& mesh, int cell, int maxOrder, const Mat3& JI
 }
 }  // namespace
 
+void cellTriangleList(const PolyMesh& mesh, int cellI, std::vector<std::array<int32_t, 3>>& out) {
+    cellTriangles(mesh, cellI, out);
+}
+
 double det2(double a, double d, double c, double b) {
     double cb = c * b;
     double err = std::fma(-c, b, cb);

@@ -2,6 +2,7 @@
 // (libWENOEXT/WENOBase/geometryWENO/geometryWENO.{H,C}, mathFunctionsWENO.H,
 // List3D.H). Setup only: runs once on the host, never on the per-step path.
 #pragma once
+#include <array>
 #include <vector>
 
 #include "polymesh.h"
@@ -39,6 +40,9 @@ void pivot(Mat3& A);
 void eigenMagnitudes(const Mat3& A, double out[3]);
 double cond(const Mat3& J);
 
+// all triangles of a cell's faces, face after face, each face as a fan from its first point
+// (polyMeshTetDecomposition::cellTetIndices stand-in)
+void cellTriangleList(const PolyMesh& mesh, int cellI, std::vector<std::array<int32_t, 3>>& out);
 // geometryWENO.C:327-343
 Vec3 transformPoint(const Mat3& Jinv, const Vec3& xP, const Vec3& x0);
 // geometryWENO.C:346-460 (scalar branch)

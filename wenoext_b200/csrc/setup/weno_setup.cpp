@@ -163,6 +163,13 @@ void calcMatrix(const PolyMesh& gm, int g, int stencilI, int nDvt, const int dim
     const int stencilSize = (int)st.size();
     int nCells = stencilSize - 1;
     const int P = prm.polOrder;
+    if (prm.gpuPinvDevice >= 0 && !prm.bestConditioned) {
+        // deferred: rows, matrices and pseudo-inverses of all stencils of the mesh are formed in one device
+        // batch (finishPending -> wenoext_ls_pinv_batched)
+        cs.Ainv[stencilI].clear();
+        cs.pending[stencilI] = 1;
+        return;
+    }
     std::vector<double> A((size_t)nCells * nDvt, 0.0);
     const Vec3 tI = geom::transformPoint(cs.JInv, gm.cellCentres[g], cs.refPoint);
     List3D transVolMom;
@@ -183,12 +190,6 @@ void calcMatrix(const PolyMesh& gm, int g, int stencilI, int nDvt, const int dim
             it = rowCache.emplace(st[cj], std::move(row)).first;
         }
         std::copy(it->second.begin(), it->second.end(), A.begin() + (size_t)(cj - 1) * nDvt);
-    }
-    if (prm.gpuPinvDevice >= 0 && !prm.bestConditioned) {
-        // deferred: the batch over all stencils of the mesh runs on the device (finishPending)
-        cs.Ainv[stencilI] = std::move(A);
-        cs.pending[stencilI] = 1;
-        return;
     }
     SvdResult cur = svd(A, nCells, nDvt, prm.maxCondition);
     if (prm.bestConditioned) {
@@ -245,35 +246,69 @@ CellSetup detail::computeCell(const PolyMesh& gm, int g, int nDvt, const int dim
 
 // matrixDB stand-in (libWENOEXT/WENOBase/matrixDB.C:75-199): tolerance-based
 // de-duplication, same key, same search window, same comparison.
-void detail::finishPending(std::vector<CellSetup>& cells, int nDvt, const SetupParams& prm) {
-    std::vector<int32_t> rows;
-    std::vector<int64_t> start(1, 0);
-    std::vector<double> A;
+void detail::finishPending(std::vector<CellSetup>& cells, const PolyMesh& gm, const std::vector<int32_t>& cellGlobal,
+                           int nDvt, const int dim[3], const SetupParams& prm) {
+    // source mesh: points, fan triangles of every cell's faces (geom::cellTriangleList), centres, volumes
+    LsBatchHost b;
+    b.polOrder = prm.polOrder;
+    b.nDvt = nDvt;
+    for (int k = 0; k < 3; ++k) b.dim[k] = dim[k];
+    b.points.resize((size_t)gm.points.size() * 3);
+    for (size_t p = 0; p < gm.points.size(); ++p)
+        for (int k = 0; k < 3; ++k) b.points[p * 3 + k] = gm.points[p][k];
+    b.triStart.assign(1, 0);
+    b.cellCentres.resize((size_t)gm.nCells * 3);
+    std::vector<std::array<int32_t, 3>> tris;
+    for (int c = 0; c < gm.nCells; ++c) {
+        geom::cellTriangleList(gm, c, tris);
+        for (const auto& t : tris) b.triPoints.insert(b.triPoints.end(), t.begin(), t.end());
+        b.triStart.push_back((int64_t)b.triPoints.size() / 3);
+        for (int k = 0; k < 3; ++k) b.cellCentres[(size_t)c * 3 + k] = gm.cellCentres[c][k];
+    }
+    b.cellVolumes = gm.cellVolumes;
+    // one frame per cell with pending stencils; one pair per distinct stencil cell of that cell (the row of
+    // (I, J) does not depend on the stencil); one matrix per pending stencil
+    const int cube = (prm.polOrder + 1) * (prm.polOrder + 1) * (prm.polOrder + 1);
     std::vector<std::pair<int32_t, int32_t>> where;
-    size_t total = 0, count = 0;
-    for (const CellSetup& cs : cells)
-        for (size_t s = 0; s < cs.pending.size(); ++s)
-            if (cs.pending[s]) total += cs.Ainv[s].size(), ++count;
-    A.reserve(total);
-    rows.reserve(count);
-    start.reserve(count + 1);
-    where.reserve(count);
-    for (size_t c = 0; c < cells.size(); ++c)
-        for (size_t s = 0; s < cells[c].pending.size(); ++s)
-            if (cells[c].pending[s]) {
-                const auto& a = cells[c].Ainv[s];
-                rows.push_back((int32_t)(a.size() / nDvt));
-                A.insert(A.end(), a.begin(), a.end());
-                start.push_back((int64_t)A.size());
-                where.push_back({(int32_t)c, (int32_t)s});
+    b.start.assign(1, 0);
+    for (size_t c = 0; c < cells.size(); ++c) {
+        const CellSetup& cs = cells[c];
+        bool any = false;
+        for (uint8_t pnd : cs.pending) any = any || pnd;
+        if (!any) continue;
+        const int32_t f = (int32_t)b.frameCell.size();
+        b.frameCell.push_back(cellGlobal[c]);
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) b.JInv.push_back(cs.JInv(i, j));
+        for (int k = 0; k < 3; ++k) b.refPoint.push_back(cs.refPoint[k]);
+        b.refDet.push_back(cs.refDet);
+        if ((int)cs.volI.d.size() != cube) throw std::runtime_error("finishPending: volume moments of unexpected size");
+        b.volI.insert(b.volI.end(), cs.volI.d.begin(), cs.volI.d.end());
+        std::map<int32_t, int64_t> pairOf;
+        for (size_t s = 0; s < cs.pending.size(); ++s) {
+            if (!cs.pending[s]) continue;
+            const auto& st = cs.globalID[s];
+            for (size_t cj = 1; cj < st.size(); ++cj) {
+                auto it = pairOf.find(st[cj]);
+                if (it == pairOf.end()) {
+                    it = pairOf.emplace(st[cj], (int64_t)b.pairCell.size()).first;
+                    b.pairFrame.push_back(f);
+                    b.pairCell.push_back(st[cj]);
+                }
+                b.rowPair.push_back(it->second);
             }
+            b.rows.push_back((int32_t)st.size() - 1);
+            b.start.push_back(b.start.back() + (int64_t)(st.size() - 1) * nDvt);
+            where.push_back({(int32_t)c, (int32_t)s});
+        }
+    }
     if (where.empty()) return;
     const int32_t nMat = (int32_t)where.size();
-    std::vector<double> P(A.size());
+    const std::vector<int64_t>& start = b.start;
+    std::vector<double> P((size_t)start.back());
     std::vector<int32_t> nZeros(nMat), conv(nMat);
     std::string err;
-    if (pinvBatchedDevice(prm.gpuPinvDevice, nMat, nDvt, rows.data(), start.data(), A.data(), prm.maxCondition,
-                          P.data(), nZeros.data(), nullptr, conv.data(), err))
+    if (lsPinvBatchedDevice(prm.gpuPinvDevice, b, prm.maxCondition, P.data(), nZeros.data(), nullptr, conv.data(), err))
         throw std::runtime_error(err);
     for (int32_t i = 0; i < nMat; ++i) {
         CellSetup& cs = cells[where[i].first];
@@ -429,10 +464,10 @@ HostPlan buildPlanGeneric(const PolyMesh& gm, const std::vector<int32_t>& cellPr
             if (!e.empty()) throw std::runtime_error(e);
     }
 
-    mark(prm.gpuPinvDevice >= 0 ? "stencils + LS matrices" : "stencils + pseudo-inverses");
+    mark(prm.gpuPinvDevice >= 0 ? "stencils" : "stencils + pseudo-inverses");
     if (prm.gpuPinvDevice >= 0) {
-        detail::finishPending(cells, K, prm);
-        mark("pseudo-inverses (device batch)");
+        detail::finishPending(cells, gm, L.localToGlobalCell, K, hp.dim, prm);
+        mark("LS rows + pseudo-inverses (device batch)");
     }
     // correctParallelRun (WENOBase.C:1030-1126): halo ids in order of first
     // appearance over the (uncut) central lists

@@ -77,7 +77,7 @@ struct CellSetup {
     std::vector<int32_t> central;                // sorted central list before the cut
     std::vector<std::vector<int32_t>> globalID;  // [stencil][j]; {CELL_DELETED} if deleted
     std::vector<std::vector<double>> Ainv;       // [stencil] nDvt x (size-1), row-major
-    std::vector<uint8_t> pending;                // [stencil] 1: Ainv still holds A ((size-1) x nDvt), see finishPending
+    std::vector<uint8_t> pending;                // [stencil] 1: matrix and pseudo-inverse still to come (finishPending)
     bool empty = false;                          // Cell::empty
     List3D volI;
     Mat3 JInv;
@@ -86,9 +86,10 @@ struct CellSetup {
 };
 CellSetup computeCell(const PolyMesh& gm, int g, int nDvt, const int dim[3], const SetupParams& prm);
 int computeNDvt(const PolyMesh& m, int polOrder, int dim[3]);
-// Deferred pseudo-inverses (SetupParams::gpuPinvDevice): one device batch over all pending
+// Deferred LS matrices and pseudo-inverses (SetupParams::gpuPinvDevice): one device batch over all pending
 // stencils of `cells`, then the per-stencil decisions of calcMatrix / LSMatrixCheck.
-void finishPending(std::vector<CellSetup>& cells, int nDvt, const SetupParams& prm);
+void finishPending(std::vector<CellSetup>& cells, const PolyMesh& gm, const std::vector<int32_t>& cellGlobal,
+                   int nDvt, const int dim[3], const SetupParams& prm);
 // matrixDB stand-in (libWENOEXT/WENOBase/matrixDB.C:75-199): tolerance-based
 // de-duplication, same key, same search window, same comparison.
 struct MatrixPool {
