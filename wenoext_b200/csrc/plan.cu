@@ -1410,12 +1410,17 @@ int wenoext::launchCells(wenoext_plan* P, const int32_t* list, int nWork, int wo
                               (size_t)ring * a.chunkSlotBytes);
     };
     auto perWarp = [&](int ring) { return warpBytesFor(ring) + (size_t)(3 + ring) * 8; };
-    // ring depth: 3 (one step being consumed, two in flight) or 2, whichever lets more
-    // warps run; never deeper than the number of steps of a cell
-    int ring = 0, nw = 0;
+    // ring depth 3 (one step being consumed, two in flight), 2 or 1, never deeper than the number of steps
+    // of a cell: the geometry with the most steps that can be in flight while their warp computes, i.e.
+    // warps x min(ring, 2) (a ring of 1 refills only after it has consumed: nothing of the warp's own
+    // stream overlaps its arithmetic; the third slot adds little once there are two). Ties go to the
+    // deeper ring. Order 3 (K = 19): 7 warps x 2 instead of 8 x 1, 0.886 -> 0.983 of the roofline at 64^3
+    // (profiles/r02_kernel_experiments.md, experiment 10).
+    int ring = 0, nw = 0, best = 0;
     for (int r = std::min(3, a.nChunks); r >= 1; --r) {
         const int w = (int)std::min<size_t>(cellKernelMaxWarps(), budget / perWarp(r));
-        if (w > nw) {
+        if (w * std::min(r, 2) > best) {
+            best = w * std::min(r, 2);
             nw = w;
             ring = r;
         }
