@@ -676,7 +676,9 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
     // Slabs for the pipelined host-buffer path (serial plans): what a prefix of the cells
     // reads (cell values, fluxes) and which faces are final once it has been processed.
     if (!rc && P->nProcs == 1) {
-        int S = 32;
+        // (24 slabs: 128^3 end to end 4.30-4.34 ms per step against 4.40-4.45 with 32 and 4.38-4.45 with 16, two
+        // boxes, round 2; ends on whole waves of tiles made no difference)
+        int S = 24;
         if (const char* e = getenv("WENOEXT_E2E_SLABS")) S = std::max(1, atoi(e));
         S = std::min(S, 64);  // (tile counter slots of overlapping launches)
         if (!getenv("WENOEXT_E2E_SLABS"))
