@@ -914,6 +914,8 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (P->commStream) cudaStreamDestroy(P->commStream);
     if (P->sIn) cudaStreamDestroy(P->sIn);
     if (P->sAlt) cudaStreamDestroy(P->sAlt);
+    if (P->sPack) cudaStreamDestroy(P->sPack);
+    for (cudaEvent_t e : P->evCopy) cudaEventDestroy(e);
     if (P->sOut) cudaStreamDestroy(P->sOut);
     for (cudaEvent_t e : P->evSlab) cudaEventDestroy(e);
     cudaEvent_t evs[] = {P->evA, P->evB, P->evC};
@@ -1818,10 +1820,24 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         CUDA_TRY(cudaStreamCreateWithFlags(&P->sOut, cudaStreamNonBlocking));
     }
     if (!P->sAlt) CUDA_TRY(cudaStreamCreateWithFlags(&P->sAlt, cudaStreamNonBlocking));
+    // The pack of a slab's cell values is a kernel: while a slab kernel fills the SMs it gets a slot only now
+    // and then. On the input stream it held up the NEXT slab's copies (inputs arrived every 0.205 ms per slab
+    // of 106 K cells, the kernels need one every 0.197 ms: the kernels waited for their inputs). The packs
+    // therefore have a stream of their own, of the highest priority, and the copy engine runs ahead.
+    if (!P->sPack) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        CUDA_TRY(cudaStreamCreateWithPriority(&P->sPack, cudaStreamNonBlocking, hi));
+    }
     while ((int)P->evSlab.size() < 2 * S + 2) {
         cudaEvent_t e;
         CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         P->evSlab.push_back(e);
+    }
+    while ((int)P->evCopy.size() < S) {
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        P->evCopy.push_back(e);
     }
     // the staging buffers may still be in use by the caller's stream
     cudaEvent_t evStart = P->evSlab[2 * S], evEnd = P->evSlab[2 * S + 1];
@@ -1834,7 +1850,27 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
     if (pnf && P->nBnd)
         CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.pnf), pnf, (size_t)P->nBnd * nComp * 8,
                                  cudaMemcpyHostToDevice, P->sIn));
+    // Without coupled patches the boundary part of the result is final as prepareCall left it (zero,
+    // WENOUpwindFit.C:230-246): it goes out first, under the kernels, instead of behind the last one
+    int tailEnd = P->nFaces;
+    if (!P->hasCoupled && !P->skipD2H && P->nFaces > P->nInt) {
+        CUDA_TRY(cudaMemcpyAsync(corr + (size_t)P->nInt * nComp, c.corr + (size_t)P->nInt * nComp,
+                                 (size_t)(P->nFaces - P->nInt) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+        tailEnd = P->nInt;
+    }
     int haveVf = 0, haveFlux = 0, sent = 0, cell0 = 0;
+    // developer aid (WENOEXT_E2E_TRACE=1): device timeline of the call, per slab: inputs there, kernel done,
+    // output copy done, in ms after the start of the call
+    static const bool trace = getenv("WENOEXT_E2E_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tr;
+    auto mark = [&](cudaStream_t st) {
+        if (!trace) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, st);
+        tr.push_back(e);
+    };
+    mark(c.st);
     for (int k = 0; k < S; ++k) {
         const int nv = P->needVf[k], nf = k == S - 1 ? P->nFaces : std::max(haveFlux, (int)P->needFlux[k]);
         if (nv > haveVf)
@@ -1843,14 +1879,17 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         if (flux && nf > haveFlux)
             CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
                                      cudaMemcpyHostToDevice, P->sIn));
-        // the pack follows its copy on the input stream, so that a slab's kernel depends on
-        // one event only
+        // the pack follows its copies on the pack stream (in slab order, so a slab's kernel depends on one
+        // event only); the input stream goes straight on with the next slab's copies
+        CUDA_TRY(cudaEventRecord(P->evCopy[k], P->sIn));
+        CUDA_TRY(cudaStreamWaitEvent(P->sPack, P->evCopy[k], 0));
         if (nv > haveVf) {
             launchPackValues(c.vf + (size_t)haveVf * nComp, nv - haveVf, nComp, c.c0, c.CB, c.VS,
-                             P->vals + (size_t)haveVf * c.VS, P->sIn);
+                             P->vals + (size_t)haveVf * c.VS, P->sPack);
             P->lastLaunches++;
         }
-        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sIn));
+        CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sPack));
+        mark(P->sPack);
         // slabs alternate between two streams: the CTAs of slab k+1 move onto the SMs as those
         // of slab k run out of tiles, instead of waiting for the whole grid to drain (slabs
         // write disjoint faces and only read the inputs)
@@ -1861,6 +1900,7 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
         if (int rc = launchCells(P, nullptr, P->slabEnd[k] - cell0, cell0, -1, false, ks, k)) return rc;
         cell0 = P->slabEnd[k];
         CUDA_TRY(cudaEventRecord(P->evSlab[2 * k + 1], ks));
+        mark(ks);
         // (the output stream waits for every slab in order: doneFaces[k] counts on slabs <= k)
         CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evSlab[2 * k + 1], 0));
         if (k == S - 1 && S > 1) {  // join: what follows on the caller's stream needs all slabs
@@ -1877,21 +1917,38 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
                                          P->sOut));
             sent = done;
         }
+        mark(P->sOut);
     }
     if (int rc = phase2(P)) return rc;  // cyclic patches
     if (P->skipD2H) {  // wenoext_div: the face field stays on the device
         CUDA_TRY(cudaStreamSynchronize(P->sIn));
+        for (cudaEvent_t e : tr) cudaEventDestroy(e);
         return 0;
     }
     CUDA_TRY(cudaEventRecord(evEnd, c.st));
     CUDA_TRY(cudaStreamWaitEvent(P->sOut, evEnd, 0));
-    CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
-                             (size_t)(P->nFaces - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    if (tailEnd > sent)
+        CUDA_TRY(cudaMemcpyAsync(corr + (size_t)sent * nComp, c.corr + (size_t)sent * nComp,
+                                 (size_t)(tailEnd - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
     if (fv && P->nInt > sent)
         CUDA_TRY(cudaMemcpyAsync(fv + (size_t)sent * nComp, c.fv + (size_t)sent * nComp,
                                  (size_t)(P->nInt - sent) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+    mark(P->sOut);
     CUDA_TRY(cudaStreamSynchronize(P->sOut));
     CUDA_TRY(cudaStreamSynchronize(c.st));
+    if (trace) {
+        auto at = [&](size_t i) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, tr[0], tr[i]);
+            return ms;
+        };
+        fprintf(stderr, "[wenoext e2e trace] slab: cells, inputs there, kernel done, output copy done (ms)\n");
+        for (int k = 0; k < S; ++k)
+            fprintf(stderr, "  %2d %8d %7.3f %7.3f %7.3f\n", k, P->slabEnd[k] - (k ? P->slabEnd[k - 1] : 0),
+                    at(1 + 3 * k), at(2 + 3 * k), at(3 + 3 * k));
+        fprintf(stderr, "  last copy done %7.3f\n", at(tr.size() - 1));
+        for (cudaEvent_t e : tr) cudaEventDestroy(e);
+    }
     return 0;
 }
 

@@ -150,6 +150,8 @@ struct wenoext_plan {
     size_t h_fixCap = 0;
     cudaStream_t sIn = nullptr, sOut = nullptr;
     cudaStream_t sAlt = nullptr;  // every second slab's kernel (overlaps the drain of the one before)
+    cudaStream_t sPack = nullptr;  // packs of the slabs' cell values (high priority), so that the input copies run ahead
+    std::vector<cudaEvent_t> evCopy;  // [slab] its input copies are done
     std::vector<cudaEvent_t> evSlab;  // [2 * slabs]: inputs arrived, slab computed
     // WENODict factors
     double p = 4.0, dm = 1000.0, eps = 1e-40;
