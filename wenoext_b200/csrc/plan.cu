@@ -2036,6 +2036,18 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
         // that completes the cell values (the peers need it only for their boundary cells).
         if (!P->sAlt) CUDA_TRY(cudaStreamCreateWithFlags(&P->sAlt, cudaStreamNonBlocking));
         CUDA_TRY(cudaStreamWaitEvent(P->sAlt, evStart, 0));
+        // packs (and the halo push behind the last of them) on their own stream of the highest priority, so that
+        // the input copies run ahead of the slab kernels (see pipelinedHostCall)
+        if (!P->sPack) {
+            int lo = 0, hi = 0;
+            cudaDeviceGetStreamPriorityRange(&lo, &hi);
+            CUDA_TRY(cudaStreamCreateWithPriority(&P->sPack, cudaStreamNonBlocking, hi));
+        }
+        while ((int)P->evCopy.size() < S) {
+            cudaEvent_t e;
+            CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            P->evCopy.push_back(e);
+        }
         ++P->haloEpoch;
         P->vals = P->valsIpc[P->haloEpoch & 1];
         P->mergedLaunch = false;
@@ -2049,23 +2061,27 @@ static int pipelinedHostCallParallel(wenoext_plan* P, const double* vf, const do
         for (int k = 0; k < S; ++k) {
             const int nv = k == S - 1 ? P->nCells : P->needVf[k];
             const int nf = k == S - 1 ? P->nFaces : std::max(haveFlux, (int)P->needFlux[k]);
-            if (nv > haveVf) {
+            const int packFrom = haveVf;
+            if (nv > haveVf)
                 CUDA_TRY(cudaMemcpyAsync(dvf + (size_t)haveVf * nComp, vf + (size_t)haveVf * nComp,
                                          (size_t)(nv - haveVf) * nComp * 8, cudaMemcpyHostToDevice, P->sIn));
-                launchPackValues(c.vf + (size_t)haveVf * nComp, nv - haveVf, nComp, c.c0, c.CB, c.VS,
-                                 P->vals + (size_t)haveVf * c.VS, P->sIn);
-                P->lastLaunches++;
-                haveVf = nv;
-            }
-            if (!pushed && haveVf == P->nCells) {
-                pushHalo(P, P->sIn);
-                pushed = true;
-            }
             if (flux && nf > haveFlux)
                 CUDA_TRY(cudaMemcpyAsync(dflux + haveFlux, flux + haveFlux, (size_t)(nf - haveFlux) * 8,
                                          cudaMemcpyHostToDevice, P->sIn));
             haveFlux = nf;
-            CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sIn));
+            CUDA_TRY(cudaEventRecord(P->evCopy[k], P->sIn));
+            CUDA_TRY(cudaStreamWaitEvent(P->sPack, P->evCopy[k], 0));
+            if (nv > packFrom) {
+                launchPackValues(c.vf + (size_t)packFrom * nComp, nv - packFrom, nComp, c.c0, c.CB, c.VS,
+                                 P->vals + (size_t)packFrom * c.VS, P->sPack);
+                P->lastLaunches++;
+                haveVf = nv;
+            }
+            if (!pushed && haveVf == P->nCells) {
+                pushHalo(P, P->sPack);
+                pushed = true;
+            }
+            CUDA_TRY(cudaEventRecord(P->evSlab[2 * k], P->sPack));
             cudaStream_t ks = (k & 1) ? P->sAlt : c.st;
             CUDA_TRY(cudaStreamWaitEvent(ks, P->evSlab[2 * k], 0));
             if (int rc = launchCells(P, P->cellListInterior, P->slabEnd[k] - item0, item0, -1, false, ks, k))
