@@ -157,3 +157,41 @@ def test_labels64_descriptor_is_narrowed_and_checked():
     if wx.lib().wenoext_device_count() == 0:
         with pytest.raises(wx.WenoextError, match="no CUDA device"):
             wx.Plan(d64)
+
+
+def test_ls_batch_is_validated_before_any_device_work():
+    """wenoext_ls_pinv_batched checks its index lists on the host (bad input fails with a message, with or without a
+    GPU); an intact batch then needs the device and fails loudly without one."""
+    f64, i32, i64 = _capi.f64p, _capi.i32p, _capi.i64p
+    pts = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]], dtype=np.float64)
+    tri = np.array([[0, 2, 1], [0, 1, 3], [0, 3, 2], [1, 2, 3]], dtype=np.int32)
+    triStart = np.array([0, 4], dtype=np.int64)
+    cen, vol = np.array([[0.25, 0.25, 0.25]]), np.array([1.0 / 6.0])
+    J, ref, det = np.eye(3).ravel().copy(), np.zeros(3), np.ones(1)
+    fc = np.zeros(1, dtype=np.int32)
+    volI = np.zeros(27)
+    pf, pc = np.zeros(1, dtype=np.int32), np.zeros(1, dtype=np.int32)
+    b = _capi.LsBatch()
+    b.polOrder, b.nDvt = 2, 9
+    for k in range(3):
+        b.dim[k] = 2
+    b.nPoints, b.nSrcCells, b.nFrames, b.nPairs, b.nMat = 4, 1, 1, 1, 0
+    p = lambda a, t: a.ctypes.data_as(t)  # noqa: E731
+    b.points, b.triStart, b.triPoints, b.cellCentres, b.cellVolumes = p(pts, f64), p(triStart, i64), p(tri, i32), p(cen, f64), p(vol, f64)
+    b.JInv, b.refPoint, b.refDet, b.frameCell, b.volI = p(J, f64), p(ref, f64), p(det, f64), p(fc, i32), p(volI, f64)
+    b.pairFrame, b.pairCell = p(pf, i32), p(pc, i32)
+    rows = np.empty((1, 9))
+    call = lambda: wx.lib().wenoext_ls_pinv_batched(C.byref(b), 1e-5, None, None, None, None, p(rows, f64), None, 0)  # noqa: E731
+    tri[1, 2] = 9
+    assert call() == 1 and b"triPoints out of range" in wx.lib().wenoext_last_error()
+    tri[1, 2] = 3
+    pc[0] = 5
+    assert call() == 1 and b"pair out of range" in wx.lib().wenoext_last_error()
+    pc[0] = 0
+    b.polOrder = 9
+    assert call() == 1 and b"order" in wx.lib().wenoext_last_error()
+    b.polOrder = 2
+    if wx.lib().wenoext_device_count() == 0:
+        assert call() != 0  # no CPU fallback
+    else:
+        assert call() == 0 and np.isfinite(rows).all()
