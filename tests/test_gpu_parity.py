@@ -365,3 +365,22 @@ def test_labels64_descriptor_gives_the_same_bits(name):
         assert np.array_equal(got, np.asarray(_plan(case).correction(scheme, bounded, vf, phi)))
         assert H.normwise_err(got, Oracle("c").correction(case, scheme, bounded, vf, phi)) < TOL
     del keep
+
+
+@pytest.mark.parametrize("slabs", ["3", "6", "8"])
+def test_first_host_buffer_call_of_a_fresh_plan_with_many_slabs(monkeypatch, slabs):
+    """The slab pipeline of a host-buffer call (copies, packs on their own stream, slab kernels on alternating streams,
+    output copies) on the FIRST call of a fresh plan, whose staging buffers hold nothing yet: a read ahead of its
+    data cannot hide behind an identical previous result. 6 and more slabs are tapered."""
+    import torch
+    monkeypatch.setenv("WENOEXT_E2E_SLABS", slabs)
+    case = wx.BoxCase((48, 48, 40), 2)
+    plan = wx.Plan(case.desc)
+    try:
+        vf = _fields(case, 3, seed=9)
+        flux = H.face_flux(case.Sf, U=(1.0, -1.0, 0.5), zero_frac=0.02)
+        host = np.asarray(plan.correction(FIT, 1, vf, flux)).reshape(case.nFaces, -1)
+        dev = plan.correction(FIT, 1, torch.from_numpy(np.ascontiguousarray(vf)).cuda(), torch.from_numpy(flux).cuda())
+        np.testing.assert_array_equal(host, dev.cpu().numpy())
+    finally:
+        plan.destroy()
