@@ -237,7 +237,8 @@ int wenoext_interpolate(wenoext_plan* plan, int scheme, int bounded, int nComp,
  *                 neighbour) / cellVolumes[cell]
  * Only [nCells][nComp] returns to the host instead of [nFaces][nComp]; with host buffers
  * the reconstruction runs slab-pipelined like wenoext_correction (copies of the next slab under the kernel
- * of the current one), on serial and on parallel plans. faceFlux may be NULL after wenoext_set_face_flux.
+ * of the current one), on serial and on parallel plans; on serial plans without coupled patches the divergence
+ * itself is formed and copied out slab by slab under the kernels. faceFlux may be NULL after wenoext_set_face_flux.
  *   bndValue    [nFaces-nInternalFaces][nComp]  vf.boundaryField() on the patch faces (read on
  *               non-coupled patches only)
  *   cellVolumes [nCells]                        mesh.V(); host-buffer calls: NULL reuses the volumes the

@@ -109,3 +109,26 @@ def test_div_host_buffers_pipelined_equals_device_buffers(sides):
         np.testing.assert_array_equal(corr, corr_d)
     finally:
         plan.destroy()
+
+
+@pytest.mark.parametrize("slabs", ["2", "6", "8"])
+def test_div_first_host_buffer_call_of_a_fresh_plan_with_many_slabs(monkeypatch, slabs):
+    """Host-buffer wenoext_div forms the divergence slab by slab under the kernels (cells whose faces are final
+    after slab k). On the FIRST call of a fresh plan nothing stale can stand in for data that is read too early
+    (the flux on boundary faces, at the end of the flux field, once was)."""
+    import torch
+    monkeypatch.setenv("WENOEXT_E2E_SLABS", slabs)
+    case = wx.BoxCase((48, 48, 40), 2)
+    plan = wx.Plan(case.desc)
+    try:
+        rng = np.random.default_rng(4)
+        vf = H.vector_field(case.C, seed=9)
+        flux = H.face_flux(case.Sf, U=(1.0, -1.0, 0.5), zero_frac=0.02)
+        bnd = rng.uniform(-1, 1, (case.nFaces - case.nInternalFaces, 3))
+        vol = rng.uniform(0.5, 1.5, case.nCells) * 1e-3
+        got = np.asarray(plan.div(FIT, 1, vf, flux, bnd, vol))  # first call
+        t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).cuda()  # noqa: E731
+        want = plan.div(FIT, 1, t(vf), t(flux), t(bnd), t(vol)).cpu().numpy()
+        np.testing.assert_array_equal(got, want)
+    finally:
+        plan.destroy()

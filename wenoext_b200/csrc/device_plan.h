@@ -195,7 +195,8 @@ struct PatchKernelArgs {
 
 // fvc::surfaceIntegrate(flux * face value) per cell (wenoext_div)
 struct DivKernelArgs {
-    int32_t nCells, nInternalFaces, nComp;
+    int32_t nCells, nInternalFaces, nComp;  // nCells: how many cells this launch integrates
+    int32_t cell0;                 // ... starting at this one
     const int32_t* cellFaceStart;  // [nCells+1]
     const int32_t* cellFaces;      // faces of a cell in ascending face index
     const int32_t* owner;          // [nFaces]

@@ -981,8 +981,11 @@ __global__ void gather_rows_kernel(const double* __restrict__ src, const int32_t
 // fvc::surfaceIntegrate(faceFlux * interpolate(vf)) (wenoext_div): one thread per
 // (cell, component), faces in ascending index so the sum has OpenFOAM's order.
 __global__ void surface_integrate_kernel(const DivKernelArgs a) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (int64_t)a.nCells * a.nComp) return;
+    // (cells [cell0, cell0 + nCells): the pipelined host-buffer path integrates the cells of a slab as soon as
+    // their faces are final)
+    const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i0 >= (int64_t)a.nCells * a.nComp) return;
+    const int64_t i = i0 + (int64_t)a.cell0 * a.nComp;
     const int cell = (int)(i / a.nComp), c = (int)(i - (int64_t)cell * a.nComp);
     const double own = a.vf[i];
     double sum = 0.0;

@@ -723,6 +723,19 @@ extern "C" int wenoext_plan_create(const wenoext_plan_desc* d, int device, wenoe
                 for (; c > P->slabEnd[k]; --c) lo = std::min(lo, ext[(size_t)(c - 1) * 3 + 1]);
                 P->doneFaces[k] = std::min(lo, P->nInt);
             }
+            // cells whose internal faces are all final after slab k (a prefix of the cells): wenoext_div
+            P->doneCells.assign(S, 0);
+            int dc = 0;
+            for (int k = 0; k < S; ++k) {
+                const int lim = k == S - 1 ? P->nInt : P->doneFaces[k];
+                for (; dc < nC; ++dc) {
+                    bool ok = true;
+                    for (int i = d->cellFaceStart[dc]; i < d->cellFaceStart[dc + 1] && ok; ++i)
+                        ok = d->cellFaces[i] >= P->nInt || d->cellFaces[i] < lim;
+                    if (!ok) break;
+                }
+                P->doneCells[k] = k == S - 1 ? nC : dc;
+            }
         }
     }
     // Parallel plans: slabs over the interior cell list; faces of boundary cells are fixed up.
@@ -915,7 +928,9 @@ extern "C" int wenoext_plan_destroy(wenoext_plan* P) {
     if (P->sIn) cudaStreamDestroy(P->sIn);
     if (P->sAlt) cudaStreamDestroy(P->sAlt);
     if (P->sPack) cudaStreamDestroy(P->sPack);
+    if (P->sDiv) cudaStreamDestroy(P->sDiv);
     for (cudaEvent_t e : P->evCopy) cudaEventDestroy(e);
+    for (cudaEvent_t e : P->evDiv) cudaEventDestroy(e);
     if (P->sOut) cudaStreamDestroy(P->sOut);
     for (cudaEvent_t e : P->evSlab) cudaEventDestroy(e);
     cudaEvent_t evs[] = {P->evA, P->evB, P->evC};
@@ -1858,6 +1873,26 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
                                  (size_t)(P->nFaces - P->nInt) * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
         tailEnd = P->nInt;
     }
+    // wenoext_div (see plan_internal.h: doneCells)
+    const bool divPipe = P->skipD2H && P->divPipeOn && !P->hasCoupled && (int)P->doneCells.size() == S &&
+                         !getenv("WENOEXT_DIV_PIPE_OFF");
+    int divSent = 0;
+    if (divPipe && !P->sDiv) {  // (not the pack stream: a pack queued behind a div kernel would wait for that slab's kernel)
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        CUDA_TRY(cudaStreamCreateWithPriority(&P->sDiv, cudaStreamNonBlocking, hi));
+    }
+    // the divergence of a boundary cell needs the flux on its boundary faces, which sit at the end of the flux
+    // field and would otherwise arrive with the last slab only (the cell kernel never reads them on meshes
+    // without coupled patches)
+    if (divPipe && flux && P->nFaces > P->nInt)
+        CUDA_TRY(cudaMemcpyAsync(const_cast<double*>(c.flux) + P->nInt, flux + P->nInt,
+                                 (size_t)(P->nFaces - P->nInt) * 8, cudaMemcpyHostToDevice, P->sIn));
+    while (divPipe && (int)P->evDiv.size() < S) {
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        P->evDiv.push_back(e);
+    }
     int haveVf = 0, haveFlux = 0, sent = 0, cell0 = 0;
     // developer aid (WENOEXT_E2E_TRACE=1): device timeline of the call, per slab: inputs there, kernel done,
     // output copy done, in ms after the start of the call
@@ -1917,11 +1952,37 @@ static int pipelinedHostCall(wenoext_plan* P, const double* vf, const double* fl
                                          P->sOut));
             sent = done;
         }
+        if (divPipe && P->doneCells[k] > divSent) {
+            // the cells whose faces are final now: integrate them (pack stream: highest priority, a small
+            // kernel that must not queue behind the slab kernels) and send the rows home
+            wenoext::DivKernelArgs da = P->divPipeArgs;
+            da.vf = c.vf;
+            da.flux = c.flux;
+            da.corr = c.corr;
+            da.cell0 = divSent;
+            da.nCells = P->doneCells[k] - divSent;
+            CUDA_TRY(cudaStreamWaitEvent(P->sDiv, P->evSlab[2 * k], 0));      // inputs (and evStart behind them)
+            CUDA_TRY(cudaStreamWaitEvent(P->sDiv, P->evSlab[2 * k + 1], 0));  // this slab's kernel
+            if (k > 0) CUDA_TRY(cudaStreamWaitEvent(P->sDiv, P->evSlab[2 * (k - 1) + 1], 0));  // and the one on the other stream
+            launchDivKernel(da, P->sDiv);
+            P->lastLaunches++;
+            CUDA_TRY(cudaEventRecord(P->evDiv[k], P->sDiv));
+            CUDA_TRY(cudaStreamWaitEvent(P->sOut, P->evDiv[k], 0));
+            CUDA_TRY(cudaMemcpyAsync(P->divPipeHost + (size_t)divSent * nComp, da.div + (size_t)divSent * nComp,
+                                     (size_t)da.nCells * nComp * 8, cudaMemcpyDeviceToHost, P->sOut));
+            divSent = P->doneCells[k];
+        }
         mark(P->sOut);
     }
     if (int rc = phase2(P)) return rc;  // cyclic patches
     if (P->skipD2H) {  // wenoext_div: the face field stays on the device
         CUDA_TRY(cudaStreamSynchronize(P->sIn));
+        if (divPipe) {  // ... and the divergence is already on its way home
+            CUDA_TRY(cudaStreamSynchronize(P->sOut));
+            CUDA_TRY(cudaStreamSynchronize(c.st));
+            CUDA_TRY(cudaStreamSynchronize(P->sDiv));
+            P->divPipeDone = true;
+        }
         for (cudaEvent_t e : tr) cudaEventDestroy(e);
         return 0;
     }
@@ -2248,11 +2309,31 @@ extern "C" int wenoext_div(wenoext_plan* P, int scheme, int bounded, int nComp, 
             CUDA_TRY(cudaMemcpyAsync(P->d_bnd, bndValue, nB * 8, cudaMemcpyHostToDevice, st));
             dbnd = P->d_bnd;
         }
+        {   // what the pipelined path needs to integrate cells as their faces become final
+            DivKernelArgs& pa = P->divPipeArgs;
+            pa = DivKernelArgs{};
+            pa.nInternalFaces = P->nInt;
+            pa.nComp = nComp;
+            pa.cellFaceStart = P->cellFaceStartD;
+            pa.cellFaces = P->cellFacesSortedD;
+            pa.owner = P->owner;
+            pa.neighbour = P->neighbourD;
+            pa.bfPatchType = P->bfPatchType;
+            pa.bfNbrCell = P->bfNbrCell;
+            pa.bndValue = dbnd;
+            pa.cellVolumes = P->d_vol;
+            pa.div = P->d_div;
+            P->divPipeHost = div;
+            P->divPipeOn = P->nProcs == 1 && nComp <= cellKernelMaxCB(P->K);
+            P->divPipeDone = false;
+        }
         P->skipD2H = true;
         const int rc = wenoext_interpolate(P, scheme, bounded, nComp, vf, faceFlux, patchNbrField, div /*unused*/,
                                            nullptr, WENOEXT_MEM_HOST, stream);
         P->skipD2H = false;
+        P->divPipeOn = false;
         if (rc) return rc;
+        if (P->divPipeDone) return haloStatus(P);
         dvf = P->s_vf;
         dflux = faceFlux ? P->s_flux : P->stepFlux;
         dpnf = patchNbrField ? P->s_pnf : nullptr;

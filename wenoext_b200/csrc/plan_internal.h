@@ -124,6 +124,15 @@ struct wenoext_plan {
     int32_t* cellFaceStartD = nullptr;
     int32_t* cellFacesSortedD = nullptr;
     int32_t* neighbourD = nullptr;  // mesh.neighbour() [nInternalFaces]: upwind cell of a face in wenoext_div
+    // wenoext_div with host buffers on a serial plan without coupled patches: the cells whose faces are final
+    // after slab k (doneCells[k], a prefix) are integrated and copied out under the kernels of the slabs that
+    // follow, instead of one launch and 8*nCells*nComp bytes of copy behind the last slab
+    std::vector<int32_t> doneCells;
+    bool divPipeOn = false, divPipeDone = false;
+    wenoext::DivKernelArgs divPipeArgs{};
+    double* divPipeHost = nullptr;
+    std::vector<cudaEvent_t> evDiv;
+    cudaStream_t sDiv = nullptr;
     bool skipD2H = false;           // host-buffer reconstruction whose face field stays on the device (wenoext_div)
     bool volValid = false;          // d_vol holds the cell volumes of an earlier wenoext_div call
     double *d_corr = nullptr, *d_bnd = nullptr, *d_vol = nullptr, *d_div = nullptr;
